@@ -1,0 +1,207 @@
+"""ctypes binding of the CPU oracle (oracle/orb_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+TAPS_CV4 = (18, 34, 48, 56, 48, 34, 18)   # OpenCV 4.x fixed-point 7x7 sigma=2 kernel
+TAPS_CV32 = (18, 34, 49, 55, 49, 34, 18)  # what OpenCV 3.2 would round the float kernel to
+
+
+def build(force=False):
+    """Compile liborb_oracle.so with oracle/Makefile (g++ only)."""
+    src = os.path.join(_HERE, "orb_oracle.cpp")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB_PATH)
+        u8p, i32p, f32p, vp = C.POINTER(C.c_uint8), C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p
+        L.orc_create.restype = vp
+        L.orc_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_destroy.argtypes = [vp]
+        L.orc_set_taps.argtypes = [vp, i32p]
+        L.orc_tables.argtypes = [vp, f32p, f32p, i32p, i32p]
+        L.orc_extract.restype = C.c_int
+        L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
+        L.orc_level_size.argtypes = [vp, C.c_int, i32p, i32p]
+        L.orc_get_level.restype = C.c_int
+        L.orc_get_level.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.orc_get_raw.restype = C.c_int
+        L.orc_get_raw.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.orc_resize.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]
+        L.orc_blur.argtypes = [vp, C.c_int, C.c_int, vp, i32p]
+        L.orc_fast.restype = C.c_int
+        L.orc_fast.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_cosf.restype = C.c_float
+        L.orc_cosf.argtypes = [C.c_float]
+        L.orc_sinf.restype = C.c_float
+        L.orc_sinf.argtypes = [C.c_float]
+        L.orc_sincos_check.restype = C.c_long
+        L.orc_sincos_check.argtypes = [C.c_uint32, C.c_uint32]
+        L.orc_octtree.restype = C.c_int
+        L.orc_octtree.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orc_bf_match.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp]
+        L.orc_stereo_filter.restype = C.c_int
+        L.orc_stereo_filter.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, C.c_float, C.c_float, C.c_float, vp, vp]
+        L.orc_threshold_filter.restype = C.c_int
+        L.orc_threshold_filter.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]
+        L.orc_stereo_pair.restype = C.c_int
+        L.orc_stereo_pair.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
+                                      C.c_int, vp, vp, vp, vp, C.c_int, i32p, i32p, vp, vp, vp, vp]
+        L.orc_run_pairs.restype = C.c_long
+        L.orc_run_pairs.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int,
+                                    C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _img(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    assert a.ndim == 2
+    return a
+
+
+class OracleExtractor:
+    """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:45-111) on the CPU oracle."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, taps=None):
+        self.L = lib()
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.h = self.L.orc_create(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast)
+        if taps is not None:
+            t = (C.c_int * 7)(*taps)
+            self.L.orc_set_taps(self.h, t)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        nl = self.nlevels
+        s = (C.c_float * nl)(); i = (C.c_float * nl)(); q = (C.c_int * nl)(); u = (C.c_int * 16)()
+        self.L.orc_tables(self.h, s, i, q, u)
+        return (np.array(s[:], np.float32), np.array(i[:], np.float32), np.array(q[:], np.int32),
+                np.array(u[:], np.int32))
+
+    def __call__(self, image):
+        image = _img(image)
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = self.L.orc_extract(self.h, _p(image), image.shape[1], image.shape[0], image.strides[0],
+                               _p(kps), _p(desc), cap)
+        assert n >= 0, "oracle capacity exceeded"
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, level, blurred=False):
+        w, h = C.c_int(), C.c_int()
+        self.L.orc_level_size(self.h, level, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        ok = self.L.orc_get_level(self.h, level, 1 if blurred else 0, _p(out))
+        return out if ok else None
+
+    def raw_corners(self, level):
+        cap = 1 << 21
+        out = np.zeros((cap, 3), np.float32)
+        n = self.L.orc_get_raw(self.h, level, _p(out), cap)
+        return out[:n].copy()
+
+
+def resize(src, dw, dh):
+    src = _img(src)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
+    return dst
+
+
+def blur(src, taps=None):
+    src = _img(src)
+    dst = np.zeros_like(src)
+    t = (C.c_int * 7)(*taps) if taps is not None else None
+    lib().orc_blur(_p(src), src.shape[1], src.shape[0], _p(dst), t)
+    return dst
+
+
+def fast(img, roi, thr):
+    """FAST-9/16 + NMS on roi=(x0,y0,x1,y1) -> (n,3) float32 [x, y, response] relative to the ROI."""
+    img = _img(img)
+    cap = img.size // 2 + 16
+    out = np.zeros((cap, 3), np.float32)
+    n = lib().orc_fast(_p(img), img.shape[1], img.shape[0], roi[0], roi[1], roi[2], roi[3], thr, _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_atan2(y, x):
+    return lib().orc_fast_atan2(float(y), float(x))
+
+
+def octtree(xyr, min_x, max_x, min_y, max_y, n_want):
+    xyr = np.ascontiguousarray(xyr, np.float32)
+    cap = n_want * 4 + 16
+    out = np.zeros((cap, 3), np.float32)
+    m = lib().orc_octtree(_p(xyr), len(xyr), min_x, max_x, min_y, max_y, n_want, _p(out), cap)
+    return out[:m].copy()
+
+
+def bf_match(q, t):
+    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    ti = np.full(len(q), -1, np.int32)
+    di = np.full(len(q), 0x7fffffff, np.int32)
+    if len(q):
+        lib().orc_bf_match(_p(q), len(q), _p(t), len(t), _p(ti), _p(di))
+    return ti, di
+
+
+def stereo_filter(train_idx, dist, kp_l, kp_r, ratio, min_match_dist, max_dy):
+    nq, nt = len(kp_l), len(kp_r)
+    o_l = np.zeros(max(nq, 1), np.int32); o_r = np.zeros(max(nq, 1), np.int32)
+    kp_l = np.ascontiguousarray(kp_l); kp_r = np.ascontiguousarray(kp_r)
+    ti = np.ascontiguousarray(train_idx, np.int32); di = np.ascontiguousarray(dist, np.int32)
+    m = lib().orc_stereo_filter(_p(ti), _p(di), nq, nt, _p(kp_l), _p(kp_r), ratio, min_match_dist, max_dy,
+                                _p(o_l), _p(o_r))
+    return o_l[:m].copy(), o_r[:m].copy()
+
+
+def threshold_filter(train_idx, dist, nt, ratio, min_match_dist):
+    nq = len(train_idx)
+    o_q = np.zeros(max(nq, 1), np.int32); o_t = np.zeros(max(nq, 1), np.int32)
+    ti = np.ascontiguousarray(train_idx, np.int32); di = np.ascontiguousarray(dist, np.int32)
+    m = lib().orc_threshold_filter(_p(ti), _p(di), nq, nt, ratio, min_match_dist, _p(o_q), _p(o_t))
+    return o_q[:m].copy(), o_t[:m].copy()
+
+
+def run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads):
+    """CPU baseline driver: cfg = (nfeatures, scaleFactor, nlevels, iniTh, minTh); imgs_* = (P,H,W) u8."""
+    imgs_l = np.ascontiguousarray(imgs_l, np.uint8); imgs_r = np.ascontiguousarray(imgs_r, np.uint8)
+    p, h, w = imgs_l.shape
+    return lib().orc_run_pairs(cfg[0], cfg[1], cfg[2], cfg[3], cfg[4], _p(imgs_l), _p(imgs_r), p, w, h,
+                               ratio, min_match_dist, max_dy, workers, per_pair_threads)
