@@ -1,0 +1,166 @@
+/* b2orb.h — C ABI of the B200-native ORB extraction + Hamming matching front-end.
+ *
+ * Drop-in boundary for the stereo visual front-end hot path of ruguangyou/pose-estimation
+ * (paths below are relative to the reference tree):
+ *   - ORB_SLAM2::ORBextractor            include/ORBextractor.h:45-111, src/ORBextractor.cc:410-470,1043-1105
+ *   - cv::BFMatcher(NORM_HAMMING).match  src/feature-tracker.cpp:161-163, :258, :303, :447, :494
+ *   - FeatureTracker::internalMatch      src/feature-tracker.cpp:140-229 (extract L/R, match, min-dist + row filter)
+ *   - FeatureTracker::externalTrack      src/feature-tracker.cpp:231-328 (matching + distance filter + circular check)
+ *
+ * POD only: plain pointers and sizes, int status codes, no exceptions, no C++/torch/OpenCV types.
+ * Every entry point runs hand-written sm_100a CUDA kernels; there is no CPU fallback — without a
+ * CUDA device b2orb_create fails with B2ORB_ERR_CUDA.
+ *
+ * Threading (mirrors src/feature-tracker.cpp:153-156): one handle owns one device, its CUDA streams
+ * and all workspace; calls on one handle must be serialised by the caller; different handles are
+ * independent (8 handles on 8 GPUs may live in one process).
+ */
+#ifndef B2ORB_H_
+#define B2ORB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2ORB_ABI_VERSION 1
+
+enum {
+    B2ORB_OK = 0,
+    B2ORB_ERR_INVALID = 1,  /* bad argument (NULL, non-positive size, image larger than configured, ...) */
+    B2ORB_ERR_CAPACITY = 2, /* caller buffer or configured batch too small */
+    B2ORB_ERR_CUDA = 3,     /* CUDA runtime error; text in b2orb_last_error() */
+    B2ORB_ERR_NOMEM = 4
+};
+
+/* Same layout as cv::KeyPoint (28 bytes): what ORBextractor::operator() fills
+ * (src/ORBextractor.cc:818-826, 837-847, 1095-1101).  class_id is always -1. */
+typedef struct b2orb_keypoint {
+    float x, y;     /* pt, level-0 pixel coordinates */
+    float size;     /* (int)(31 * scale[octave]) */
+    float angle;    /* degrees in [0,360), cv::fastAtan2 of the intensity centroid */
+    float response; /* FAST score */
+    int32_t octave;
+    int32_t class_id;
+} b2orb_keypoint;
+
+/* Constructor arguments of ORBextractor (src/ORBextractor.cc:410-414) + the FeatureTracker matching
+ * keys (src/feature-tracker.cpp:8-15; config/euroc.yml:106-112) + workspace sizing. */
+typedef struct b2orb_config {
+    int32_t nfeatures;    /* numberOfFeatures */
+    float scale_factor;   /* scaleFactor, must be > 1 */
+    int32_t nlevels;      /* levelPyramid, 1..12 */
+    int32_t ini_th_fast;  /* iniThFAST */
+    int32_t min_th_fast;  /* minThFAST */
+    int32_t max_width;    /* largest image accepted (<= 4096) */
+    int32_t max_height;   /* (<= 4096) */
+    int32_t max_images;   /* images resident per launch set; a stereo pair needs 2 */
+    int32_t blur_taps[7]; /* 7-tap integer Gaussian, sum 256; all zero = OpenCV 4.x {18,34,48,56,48,34,18} */
+    float match_ratio;              /* matchRatio */
+    float min_match_dist;           /* minMatchDist */
+    float max_vertical_pixel_dist;  /* maxVerticalPixelDist */
+} b2orb_config;
+
+typedef struct b2orb_handle b2orb_handle;
+
+int b2orb_abi_version(void);
+int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg);
+void b2orb_destroy(b2orb_handle* h);
+const char* b2orb_last_error(const b2orb_handle* h);
+
+/* Upper bound on keypoints one image can return (nfeatures + 3 per level, DistributeOctTree can
+ * overshoot its per-level quota by up to 3, src/ORBextractor.cc:673-738). */
+int b2orb_keypoint_capacity(const b2orb_handle* h);
+
+/* Getters of include/ORBextractor.h:63-83: out arrays hold nlevels entries. */
+int b2orb_get_tables(const b2orb_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                     int32_t* features_per_level);
+
+/* Pinned host memory helpers (cudaHostAlloc) so callers can stage images for full-rate copies. */
+void* b2orb_host_alloc(size_t bytes);
+void b2orb_host_free(void* p);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors), src/ORBextractor.cc:1043-1105.
+ * image: host, 8-bit single channel, `step` bytes per row.  Writes *n keypoints (<= cap) and *n x 32
+ * descriptor bytes.  Empty image (width or height 0) -> *n = 0 (reference :1046-1047). */
+int b2orb_extract(b2orb_handle* h, const uint8_t* image, int width, int height, int step, b2orb_keypoint* kps,
+                  uint8_t* desc, int cap, int* n);
+
+/* Batched form: `count` images of identical size, image i at images + i*image_stride; outputs at
+ * kps + i*cap, desc + i*cap*32, n[i].  count <= max_images. */
+int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int width, int height, int step,
+                        size_t image_stride, b2orb_keypoint* kps, uint8_t* desc, int cap, int32_t* n);
+
+/* cv::BFMatcher(cv::NORM_HAMMING).match(query, train, matches): one result per query row in query
+ * order; train_idx = nearest train row (lowest index on ties), dist = Hamming distance.
+ * nt == 0 -> train_idx = -1, dist = INT32_MAX.  Host pointers, 32-byte descriptor rows. */
+int b2orb_match(b2orb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, int32_t* train_idx,
+                int32_t* dist);
+
+/* Host-side views of one batch of stereo pairs (all arrays caller-owned, host memory; `cap` entries
+ * per image, pair p's slots start at p*cap).  NULL members are skipped (not copied back). */
+typedef struct b2orb_stereo_out {
+    int32_t cap;              /* >= b2orb_keypoint_capacity() */
+    b2orb_keypoint* kp_l;     /* [npairs*cap] */
+    b2orb_keypoint* kp_r;
+    uint8_t* desc_l;          /* [npairs*cap*32] */
+    uint8_t* desc_r;
+    int32_t* n_l;             /* [npairs] */
+    int32_t* n_r;
+    int32_t* train_idx;       /* [npairs*cap] BFMatcher result L->R */
+    int32_t* dist;            /* [npairs*cap] */
+    int32_t* match_l;         /* [npairs*cap] kept matches (queryIdx), in query order */
+    int32_t* match_r;         /* [npairs*cap] (trainIdx) */
+    int32_t* n_match;         /* [npairs] */
+    /* temporal (externalTrack) part, filled when `temporal` != 0: circular matches between the kept
+     * stereo matches of pair p (cur) and pair p-1 (hist); indices are positions in the kept lists. */
+    int32_t* circ_cur;        /* [npairs*cap] */
+    int32_t* circ_hist;       /* [npairs*cap] */
+    int32_t* n_circ;          /* [npairs] (0 for the first pair after b2orb_reset_history) */
+} b2orb_stereo_out;
+
+/* FeatureTracker::internalMatch (useRANSAC=false, src/feature-tracker.cpp:140-164,208-218) for `npairs`
+ * independent stereo pairs: extract L and R, BF match L->R, keep matches with
+ * dist < max(match_ratio*minDist, min_match_dist) and |yL - yR| < max_vertical_pixel_dist.
+ * With temporal != 0 it also runs the matching parts of externalTrack (:258-259,293-296,303-321) between
+ * consecutive pairs: cur = kept descriptors of pair p, hist = those of pair p-1 (the last pair of the
+ * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers. */
+int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
+                          int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
+
+/* Same work with inputs ALREADY RESIDENT in device memory and results LEFT on the device (read them with
+ * b2orb_stereo_download).  Asynchronous on the handle's stream; b2orb_sync() waits. */
+int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, const uint8_t* d_images_r, int npairs,
+                                 int width, int height, int step, size_t image_stride, int temporal);
+int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* out);
+int b2orb_sync(b2orb_handle* h);
+void b2orb_reset_history(b2orb_handle* h);
+
+/* externalTrack matching parts as one call on host descriptor sets (src/feature-tracker.cpp:258-259,
+ * 293-296, 303-321, useRANSAC=false): match(cur_l, hist_l) and match(cur_r, hist_r), each filtered by
+ * dist < max(ratio*minDist, min_match_dist), then the circular test mapCurHist[q] == trainIdx.
+ * Outputs (cur index, hist index) pairs in query order; n_left / n_right = matches passing the
+ * distance filter on each side (the reference's verbose counters :297, :325). */
+int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* cur_r, int ncur, const uint8_t* hist_l,
+                         const uint8_t* hist_r, int nhist, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ,
+                         int32_t* n_left, int32_t* n_right);
+
+/* Test/debug access to intermediates of the LAST extract call for image slot `slot`:
+ * which = 0 pyramid level, 1 blurred level (dst = w*h bytes, tightly packed). */
+int b2orb_debug_level_size(const b2orb_handle* h, int level, int* w, int* hgt);
+int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8_t* dst);
+/* raw per-cell FAST corners of a level before the quadtree: packed x | y<<12 | response<<24 with x,y
+ * relative to the 16-px border (unordered).  Returns the count through *n. */
+int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* dst, int cap, int* n);
+
+/* Kernel launches issued by this handle since creation (bench.py reports the per-step delta). */
+uint64_t b2orb_launch_count(const b2orb_handle* h);
+/* Device time (ms, CUDA events on the handle's stream) of the last *_device / frontend call. */
+float b2orb_last_device_ms(const b2orb_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2ORB_H_ */

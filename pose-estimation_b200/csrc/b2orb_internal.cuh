@@ -1,0 +1,103 @@
+// Internal declarations shared by the sm_100a kernels and the C-ABI layer (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define B2_MAX_LEVELS 12
+#define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
+#define B2_BORDER 16        // EDGE_THRESHOLD-3 = minBorderX/Y, src/ORBextractor.cc:773-776
+#define B2_HALF_PATCH 15    // HALF_PATCH_SIZE, src/ORBextractor.cc:73
+
+// Per-level geometry, fixed for (config, image size).  Passed to kernels BY VALUE as one
+// __grid_constant__ parameter, so several handles with different configs can coexist.
+struct B2Level {
+    int w, h, pitch;          // level image size, row pitch in bytes (multiple of 16)
+    unsigned off;             // byte offset of the level inside one image's pyramid / blur slab
+    int n_cols, n_rows;       // FAST cell grid (src/ORBextractor.cc:784-787)
+    int w_cell, h_cell;
+    int cell_base;            // first flattened cell index of this level
+    int blur_tile_base;       // first flattened blur tile of this level
+    int blur_tiles_x;
+    int quota;                // mnFeaturesPerLevel[level]
+    int sel_base;             // first slot of this level in the per-image selected-keypoint array
+    int sel_cap;              // quota + 4
+    unsigned cand_off;        // first slot of this level in the per-image candidate array
+    int cand_cap;
+    int node_cap;             // 4*quota + 8
+    unsigned node_off;        // first node slot of this level in the per-image node workspace
+    int n_ini;                // quadtree roots (src/ORBextractor.cc:543)
+    float h_x;                // root width (src/ORBextractor.cc:545)
+    float scale;              // mvScaleFactor[level]
+    float kp_size;            // (float)(int)(31*scale)
+};
+
+struct B2Geom {
+    int nlevels;
+    int ini_th, min_th;
+    int total_cells;          // over all levels
+    int total_blur_tiles;
+    int sel_total;            // per-image selected-keypoint slots (sum of sel_cap)
+    int kp_cap;               // per-image output capacity
+    unsigned cand_total;      // per-image candidate slots
+    unsigned node_total;      // per-image node slots
+    unsigned slab;            // bytes of one image's pyramid (levels 1..) / blur (levels 0..) slab
+    int umax[16];             // src/ORBextractor.cc:454-469
+    int taps[7];
+    B2Level lv[B2_MAX_LEVELS];
+};
+
+// Level-0 pixels are read where the caller (or the H2D copy) put them; levels >= 1 live in the
+// pyramid slab.  All kernels use this one accessor.
+struct B2Images {
+    const uint8_t* lvl0[2];   // image b < split at lvl0[0] + b*stride0, else lvl0[1] + (b-split)*stride0
+    int split;
+    size_t stride0;
+    int pitch0;
+    uint8_t* pyr;             // image b's slab at pyr + b*slab (levels >= 1)
+    uint8_t* blur;            // same layout, all levels
+};
+
+__device__ __forceinline__ const uint8_t* b2_level_ptr(const B2Geom& g, const B2Images& im, int b, int level,
+                                                       int& pitch) {
+    if (level == 0) {
+        pitch = im.pitch0;
+        return b < im.split ? im.lvl0[0] + (size_t)b * im.stride0 : im.lvl0[1] + (size_t)(b - im.split) * im.stride0;
+    }
+    pitch = g.lv[level].pitch;
+    return im.pyr + (size_t)b * g.slab + g.lv[level].off;
+}
+
+// Quadtree node (list entry).  The node array IS the std::list of DistributeOctTree in list order.
+struct B2Node {
+    unsigned short x0, y0, x1, y1;  // UL.x, UL.y, BR.x, BR.y (relative to the 16-px border)
+    unsigned cnt;                   // points inside
+};
+
+// One Hamming matching problem (BFMatcher.match call): rows are 32-byte descriptors.
+struct B2MatchProblem {
+    const uint8_t* q;
+    const uint8_t* t;
+    const int* nq;       // device counts (read at kernel time, so upstream kernels can set them)
+    const int* nt;
+    int* train_idx;
+    int* dist;
+};
+
+// ---- kernel launchers (each file documents the reference lines it restates) --------------------
+void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
+                      const int* yofs, const short* yw, int nimg, cudaStream_t s);
+void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);
+void b2_launch_fast(const B2Geom& g, const B2Images& im, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s);
+void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
+                      B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
+void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,
+                        uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
+void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s);
+void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
+                             const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,
+                             int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, int npairs,
+                             cudaStream_t s);   // left image slot = p, right image slot = npairs + p
+void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
+                        const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
+                        int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s);
+int b2_octree_scratch_words(const B2Geom& g);

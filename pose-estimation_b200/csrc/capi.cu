@@ -1,0 +1,738 @@
+// C-ABI layer (include/b2orb.h): handle, host-side tables of ORBextractor's constructor
+// (src/ORBextractor.cc:410-470), per-size geometry (ComputePyramid sizes :1111-1112, FAST cell grid
+// :773-787, quadtree roots :543-545), workspace, and the launch sequence of one batch.
+// Host C++ only orchestrates; all pixel/descriptor work is in the .cu kernels next to this file.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/b2orb.h"
+#include "b2orb_internal.cuh"
+
+namespace {
+
+inline int cv_round_f(float v) { return (int)lrintf(v); }   // cvRound: round-half-even
+inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
+
+constexpr int kBlurTileW = 64, kBlurTileH = 16;   // must match blur.cu
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace
+
+struct b2orb_handle {
+    b2orb_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    float last_ms = 0.f;
+
+    // ctor tables
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> quota;
+    int umax[16]{};
+
+    // geometry of the current image size
+    int cur_w = 0, cur_h = 0;
+    B2Geom geom{};
+    std::vector<int*> d_xofs, d_yofs;
+    std::vector<short*> d_xw, d_yw;
+
+    // workspace (sized for cfg.max_images images of the current size)
+    int nimg_cap = 0, npair_cap = 0;
+    uint8_t *d_stage = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+    size_t stage_img_bytes = 0;
+    uint32_t* d_cand = nullptr;
+    unsigned short* d_pnode = nullptr;
+    int *d_cand_cnt = nullptr, *d_sel_cnt = nullptr, *d_nkp = nullptr;
+    uint32_t* d_sel = nullptr;
+    unsigned* d_ot_scratch = nullptr;
+    b2orb_keypoint* d_kps = nullptr;
+    uint8_t* d_desc = nullptr;
+    int *d_train = nullptr, *d_dist = nullptr, *d_match_l = nullptr, *d_match_r = nullptr, *d_nmatch = nullptr;
+    uint8_t *d_cur_l = nullptr, *d_cur_r = nullptr;      // slot 0 = history, slot p+1 = pair p
+    int *d_tti_l = nullptr, *d_tdi_l = nullptr, *d_tti_r = nullptr, *d_tdi_r = nullptr;
+    int *d_circ_cur = nullptr, *d_circ_hist = nullptr, *d_ncirc = nullptr, *d_nleft = nullptr, *d_nright = nullptr;
+    B2MatchProblem* d_probs = nullptr;                   // [npair_cap stereo][2*npair_cap temporal][3 generic]
+    // generic matcher scratch (b2orb_match / b2orb_temporal_track)
+    uint8_t *d_gq = nullptr, *d_gt = nullptr, *d_gq2 = nullptr, *d_gt2 = nullptr;
+    int *d_gidx = nullptr, *d_gdist = nullptr, *d_gidx2 = nullptr, *d_gdist2 = nullptr, *d_gcnt = nullptr;
+    int g_cap_q = 0, g_cap_t = 0;
+    int bound_np = -1;                                   // batch size the problem table is bound to
+    std::vector<void*> owned;
+};
+
+namespace {
+
+bool cuda_ok(b2orb_handle* h, cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    char buf[256];
+    snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+    h->err = buf;
+    return false;
+}
+#define B2_CUDA(h, call)                                         \
+    do {                                                         \
+        if (!cuda_ok((h), (call), #call)) return B2ORB_ERR_CUDA; \
+    } while (0)
+
+int fail(b2orb_handle* h, int code, const char* msg) {
+    if (h) h->err = msg;
+    return code;
+}
+
+template <class T>
+bool dev_alloc(b2orb_handle* h, T** p, size_t count) {
+    void* q = nullptr;
+    if (!cuda_ok(h, cudaMalloc(&q, count * sizeof(T) + 256), "cudaMalloc")) return false;
+    cudaMemsetAsync(q, 0, count * sizeof(T) + 256, h->stream);
+    h->owned.push_back(q);
+    *p = static_cast<T*>(q);
+    return true;
+}
+
+void free_workspace(b2orb_handle* h) {
+    for (void* p : h->owned) cudaFree(p);
+    h->owned.clear();
+    h->d_xofs.clear(); h->d_yofs.clear(); h->d_xw.clear(); h->d_yw.clear();
+    h->g_cap_q = h->g_cap_t = 0;
+    h->bound_np = -1;
+}
+
+// ORBextractor::ORBextractor, src/ORBextractor.cc:410-470.
+void build_ctor_tables(b2orb_handle* h) {
+    const b2orb_config& c = h->cfg;
+    const int nl = c.nlevels;
+    const double sf = (double)c.scale_factor;   // member `scaleFactor` is a double initialised from the float arg
+    h->scale.assign(nl, 1.f); h->sigma2.assign(nl, 1.f); h->inv_scale.assign(nl, 1.f); h->inv_sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        h->scale[i] = (float)(h->scale[i - 1] * sf);
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    for (int i = 0; i < nl; ++i) {
+        h->inv_scale[i] = 1.0f / h->scale[i];
+        h->inv_sigma2[i] = 1.0f / h->sigma2[i];
+    }
+    h->quota.assign(nl, 0);
+    const float factor = (float)(1.0f / sf);
+    float desired = c.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        h->quota[l] = cv_round_f(desired);
+        sum += h->quota[l];
+        desired *= factor;
+    }
+    h->quota[nl - 1] = std::max(c.nfeatures - sum, 0);
+    // umax, :454-469
+    int v, v0;
+    const int vmax = (int)std::floor(B2_HALF_PATCH * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(B2_HALF_PATCH * std::sqrt(2.f) / 2);
+    const double hp2 = B2_HALF_PATCH * B2_HALF_PATCH;
+    for (v = 0; v <= vmax; ++v) h->umax[v] = (int)lrint(std::sqrt(hp2 - v * v));
+    for (v = B2_HALF_PATCH, v0 = 0; v >= vmin; --v) {
+        while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+        h->umax[v] = v0;
+        ++v0;
+    }
+}
+
+// cv::resize's per-axis tables (imgproc/resize.cpp): float source coordinate from a double scale,
+// Q11 weights via saturate_cast<short>(w * 2048) (round-half-even).
+void resize_axis_table(int src, int dst, std::vector<int>& ofs, std::vector<short>& w) {
+    ofs.resize(dst);
+    w.resize((size_t)2 * dst);
+    const double scale = (double)src / dst;
+    for (int d = 0; d < dst; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        if (s < 0) { s = 0; f = 0.f; }
+        if (s >= src - 1) { s = src - 1; f = 0.f; }
+        ofs[d] = s;
+        w[2 * d] = (short)lrintf((1.f - f) * 2048.f);
+        w[2 * d + 1] = (short)lrintf(f * 2048.f);
+    }
+}
+
+// Geometry for one image size.  Returns an error string or nullptr.
+const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
+    const b2orb_config& c = h->cfg;
+    memset(&g, 0, sizeof g);
+    g.nlevels = c.nlevels;
+    g.ini_th = c.ini_th_fast;
+    g.min_th = c.min_th_fast;
+    memcpy(g.umax, h->umax, sizeof g.umax);
+    static const int def_taps[7] = {18, 34, 48, 56, 48, 34, 18};
+    bool zero = true;
+    for (int i = 0; i < 7; ++i) zero = zero && c.blur_taps[i] == 0;
+    for (int i = 0; i < 7; ++i) g.taps[i] = zero ? def_taps[i] : c.blur_taps[i];
+    unsigned off = 0, cand_off = 0, node_off = 0;
+    int cells = 0, tiles = 0, sel = 0;
+    for (int l = 0; l < c.nlevels; ++l) {
+        B2Level& L = g.lv[l];
+        // ComputePyramid :1111-1112: Size(cvRound((float)cols*scale), cvRound((float)rows*scale))
+        L.w = cv_round_f((float)w * h->inv_scale[l]);
+        L.h = cv_round_f((float)hgt * h->inv_scale[l]);
+        if (L.w < 1 || L.h < 1) return "pyramid level collapses to zero size";
+        L.pitch = (int)align_up((unsigned)L.w, 32);
+        L.off = off;
+        off += align_up((unsigned)L.pitch * (unsigned)L.h, 256);
+        L.blur_tiles_x = (L.w + kBlurTileW - 1) / kBlurTileW;
+        L.blur_tile_base = tiles;
+        tiles += L.blur_tiles_x * ((L.h + kBlurTileH - 1) / kBlurTileH);
+        L.quota = h->quota[l];
+        L.scale = h->scale[l];
+        L.kp_size = (float)(int)(31 * h->scale[l]);     // :836 `const int scaledPatchSize = PATCH_SIZE*mvScaleFactor[level]`
+        // ComputeKeyPointsOctTree :773-787
+        const int minB = B2_BORDER, maxBX = L.w - B2_BORDER, maxBY = L.h - B2_BORDER;
+        const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+        const int n_cols = width > 0 ? (int)(width / 30.f) : 0, n_rows = height > 0 ? (int)(height / 30.f) : 0;
+        L.cell_base = cells;
+        L.n_ini = 1;
+        L.h_x = 1.f;
+        if (n_cols >= 1 && n_rows >= 1) {   // else: the reference divides by zero; the level yields no keypoints
+            L.n_cols = n_cols;
+            L.n_rows = n_rows;
+            L.w_cell = (int)std::ceil(width / n_cols);
+            L.h_cell = (int)std::ceil(height / n_rows);
+            if (L.w_cell > 64 || L.h_cell > 64) return "FAST cell larger than 64 px";
+            if ((long long)n_cols * n_rows * L.w_cell * L.h_cell >= (1 << 24)) return "level too large for 24-bit order keys";
+            cells += n_cols * n_rows;
+            // DistributeOctTree :543-545
+            L.n_ini = (int)std::round((float)(maxBX - minB) / (maxBY - minB));
+            if (L.n_ini < 1) {   // taller than 2:1 -> the reference divides by zero; no keypoints
+                L.n_ini = 1; L.n_cols = L.n_rows = 0; cells -= n_cols * n_rows;
+            } else if (L.n_ini > 256) return "aspect ratio above 256:1";
+            L.h_x = (float)(maxBX - minB) / L.n_ini;
+        }
+        L.cand_cap = L.n_cols * L.n_rows * ((L.w_cell + 1) / 2) * ((L.h_cell + 1) / 2);
+        L.cand_off = cand_off;
+        cand_off += align_up((unsigned)L.cand_cap, 64);
+        L.node_cap = std::max(L.quota + 3, 4 * L.n_ini) + 1;
+        if (L.node_cap > 60000) return "per-level feature quota too large";
+        L.node_off = node_off;
+        node_off += L.node_cap;
+        L.sel_cap = L.node_cap;
+        L.sel_base = sel;
+        sel += L.sel_cap;
+    }
+    if (w > 4096 + B2_BORDER || hgt > 4096 + B2_BORDER) return "image larger than 4096 px";
+    g.total_cells = cells;
+    g.total_blur_tiles = tiles;
+    g.sel_total = sel;
+    g.kp_cap = sel;
+    g.cand_total = cand_off;
+    g.node_total = node_off;
+    g.slab = align_up(off, 256);
+    return nullptr;
+}
+
+}  // namespace
+
+namespace {
+
+// (Re)build geometry, resize tables and workspace for an image size.  Steady state: no-op.
+int configure(b2orb_handle* h, int w, int hgt) {
+    if (w == h->cur_w && hgt == h->cur_h) return B2ORB_OK;
+    B2Geom g;
+    if (const char* e = build_geometry(h, w, hgt, g)) return fail(h, B2ORB_ERR_INVALID, e);
+    cudaStreamSynchronize(h->stream);
+    free_workspace(h);
+    h->cur_w = h->cur_h = 0;
+    h->geom = g;
+    const int nl = g.nlevels, nimg = h->cfg.max_images, np = std::max(nimg / 2, 1);
+    h->nimg_cap = nimg;
+    h->npair_cap = np;
+    // resize tables per level (level l from level l-1)
+    h->d_xofs.assign(nl, nullptr); h->d_yofs.assign(nl, nullptr); h->d_xw.assign(nl, nullptr); h->d_yw.assign(nl, nullptr);
+    for (int l = 1; l < nl; ++l) {
+        std::vector<int> xo, yo;
+        std::vector<short> xw, yw;
+        resize_axis_table(g.lv[l - 1].w, g.lv[l].w, xo, xw);
+        resize_axis_table(g.lv[l - 1].h, g.lv[l].h, yo, yw);
+        if (!dev_alloc(h, &h->d_xofs[l], xo.size()) || !dev_alloc(h, &h->d_yofs[l], yo.size()) ||
+            !dev_alloc(h, &h->d_xw[l], xw.size()) || !dev_alloc(h, &h->d_yw[l], yw.size()))
+            return B2ORB_ERR_NOMEM;
+        B2_CUDA(h, cudaMemcpyAsync(h->d_xofs[l], xo.data(), xo.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        B2_CUDA(h, cudaMemcpyAsync(h->d_yofs[l], yo.data(), yo.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        B2_CUDA(h, cudaMemcpyAsync(h->d_xw[l], xw.data(), xw.size() * 2, cudaMemcpyHostToDevice, h->stream));
+        B2_CUDA(h, cudaMemcpyAsync(h->d_yw[l], yw.data(), yw.size() * 2, cudaMemcpyHostToDevice, h->stream));
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));   // host vectors die at scope end
+    }
+    h->stage_img_bytes = (size_t)w * hgt;
+    const size_t cap = g.kp_cap;
+    bool ok = dev_alloc(h, &h->d_stage, (size_t)nimg * h->stage_img_bytes) &&
+              dev_alloc(h, &h->d_pyr, (size_t)nimg * g.slab) && dev_alloc(h, &h->d_blur, (size_t)nimg * g.slab) &&
+              dev_alloc(h, &h->d_cand, (size_t)nimg * g.cand_total) &&
+              dev_alloc(h, &h->d_pnode, (size_t)nimg * g.cand_total) &&
+              dev_alloc(h, &h->d_cand_cnt, (size_t)nimg * nl) && dev_alloc(h, &h->d_sel_cnt, (size_t)nimg * nl) &&
+              dev_alloc(h, &h->d_nkp, (size_t)nimg) && dev_alloc(h, &h->d_sel, (size_t)nimg * g.sel_total) &&
+              dev_alloc(h, &h->d_kps, (size_t)nimg * cap) && dev_alloc(h, &h->d_desc, (size_t)nimg * cap * 32) &&
+              dev_alloc(h, &h->d_train, (size_t)np * cap) && dev_alloc(h, &h->d_dist, (size_t)np * cap) &&
+              dev_alloc(h, &h->d_match_l, (size_t)np * cap) && dev_alloc(h, &h->d_match_r, (size_t)np * cap) &&
+              dev_alloc(h, &h->d_nmatch, (size_t)np + 1) && dev_alloc(h, &h->d_cur_l, (size_t)(np + 1) * cap * 32) &&
+              dev_alloc(h, &h->d_cur_r, (size_t)(np + 1) * cap * 32) && dev_alloc(h, &h->d_tti_l, (size_t)np * cap) &&
+              dev_alloc(h, &h->d_tdi_l, (size_t)np * cap) && dev_alloc(h, &h->d_tti_r, (size_t)np * cap) &&
+              dev_alloc(h, &h->d_tdi_r, (size_t)np * cap) && dev_alloc(h, &h->d_circ_cur, (size_t)np * cap) &&
+              dev_alloc(h, &h->d_circ_hist, (size_t)np * cap) && dev_alloc(h, &h->d_ncirc, (size_t)np) &&
+              dev_alloc(h, &h->d_nleft, (size_t)np) && dev_alloc(h, &h->d_nright, (size_t)np) &&
+              dev_alloc(h, &h->d_probs, (size_t)3 * np + 4) && dev_alloc(h, &h->d_gcnt, (size_t)8);
+    if (!ok) return B2ORB_ERR_NOMEM;
+    if ((size_t)b2_octree_scratch_words(g) * 4 > 200 * 1024) {   // quadtree state too big for shared memory
+        if (!dev_alloc(h, &h->d_ot_scratch, (size_t)nimg * g.node_total * 20)) return B2ORB_ERR_NOMEM;
+    } else h->d_ot_scratch = nullptr;
+    // match problem table: [0,np) stereo pair p (left slot p vs right slot n+p is bound per call because the
+    // right slot depends on the batch size) — filled by bind_problems().
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->cur_w = w;
+    h->cur_h = hgt;
+    return B2ORB_OK;
+}
+
+// Stereo problems [0,np): desc(left p) vs desc(right np+p).  Temporal problems [np, 3np): cur slot p+1 vs
+// hist slot p, left then right.
+int bind_problems(b2orb_handle* h, int np) {
+    if (h->bound_np == np) return B2ORB_OK;
+    const size_t cap = h->geom.kp_cap;
+    std::vector<B2MatchProblem> pr((size_t)3 * np);
+    for (int p = 0; p < np; ++p) {
+        pr[p] = {h->d_desc + (size_t)p * cap * 32, h->d_desc + (size_t)(np + p) * cap * 32, h->d_nkp + p,
+                 h->d_nkp + np + p, h->d_train + (size_t)p * cap, h->d_dist + (size_t)p * cap};
+        pr[np + p] = {h->d_cur_l + (size_t)(p + 1) * cap * 32, h->d_cur_l + (size_t)p * cap * 32, h->d_nmatch + p + 1,
+                      h->d_nmatch + p, h->d_tti_l + (size_t)p * cap, h->d_tdi_l + (size_t)p * cap};
+        pr[2 * np + p] = {h->d_cur_r + (size_t)(p + 1) * cap * 32, h->d_cur_r + (size_t)p * cap * 32,
+                          h->d_nmatch + p + 1, h->d_nmatch + p, h->d_tti_r + (size_t)p * cap,
+                          h->d_tdi_r + (size_t)p * cap};
+    }
+    B2_CUDA(h, cudaMemcpyAsync(h->d_probs, pr.data(), pr.size() * sizeof(B2MatchProblem), cudaMemcpyHostToDevice,
+                               h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->bound_np = np;
+    return B2ORB_OK;
+}
+
+// Launch sequence of ORBextractor::operator() for `nimg` resident images (src/ORBextractor.cc:1043-1105).
+int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
+    const B2Geom& g = h->geom;
+    cudaStream_t s = h->stream;
+    for (int l = 1; l < g.nlevels; ++l) {
+        b2_launch_resize(g, im, l, h->d_xofs[l], h->d_xw[l], h->d_yofs[l], h->d_yw[l], nimg, s);
+        ++h->launches;
+    }
+    B2_CUDA(h, cudaMemsetAsync(h->d_cand_cnt, 0, (size_t)nimg * g.nlevels * sizeof(int), s));
+    if (g.total_cells > 0) { b2_launch_fast(g, im, h->d_cand, h->d_cand_cnt, nimg, s); ++h->launches; }
+    b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
+    ++h->launches;
+    b2_launch_blur(g, im, nimg, s);
+    ++h->launches;
+    b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
+    ++h->launches;
+    B2_CUDA(h, cudaGetLastError());
+    return B2ORB_OK;
+}
+
+B2Images make_images(b2orb_handle* h, const uint8_t* a, const uint8_t* b, int split, size_t stride0, int pitch0) {
+    B2Images im;
+    im.lvl0[0] = a;
+    im.lvl0[1] = b;
+    im.split = split;
+    im.stride0 = stride0;
+    im.pitch0 = pitch0;
+    im.pyr = h->d_pyr;
+    im.blur = h->d_blur;
+    return im;
+}
+
+// Host images -> tight staging area (slot order), one copy when the source is tight too.
+int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0) {
+    uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
+    if (step == w && image_stride == (size_t)w * hgt) {
+        B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int i = 0; i < count; ++i)
+            B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, w, src + i * image_stride, step, w, hgt,
+                                         cudaMemcpyHostToDevice, h->stream));
+    }
+    return B2ORB_OK;
+}
+
+int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
+    const B2Geom& g = h->geom;
+    cudaStream_t s = h->stream;
+    int rc = launch_extract(h, im, 2 * np);
+    if (rc) return rc;
+    rc = bind_problems(h, np);   // small H2D; table depends on np only
+    if (rc) return rc;
+    b2_launch_match(h->d_probs, np, g.kp_cap, s);
+    ++h->launches;
+    b2_launch_stereo_filter(h->d_kps, h->d_desc, h->d_nkp, h->d_train, h->d_dist, g.kp_cap, h->cfg.match_ratio,
+                            h->cfg.min_match_dist, h->cfg.max_vertical_pixel_dist, h->d_match_l, h->d_match_r,
+                            h->d_nmatch + 1, h->d_cur_l + (size_t)g.kp_cap * 32, h->d_cur_r + (size_t)g.kp_cap * 32, np,
+                            s);
+    ++h->launches;
+    if (temporal) {
+        b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
+        ++h->launches;
+        b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, h->d_nmatch, g.kp_cap,
+                           h->cfg.match_ratio, h->cfg.min_match_dist, h->d_circ_cur, h->d_circ_hist, h->d_ncirc,
+                           h->d_nleft, h->d_nright, np, s);
+        ++h->launches;
+        // the last pair of this call becomes the history of the next call (slot 0)
+        const size_t row = (size_t)g.kp_cap * 32;
+        B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, h->d_cur_l + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
+        B2_CUDA(h, cudaMemcpyAsync(h->d_cur_r, h->d_cur_r + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
+        B2_CUDA(h, cudaMemcpyAsync(h->d_nmatch, h->d_nmatch + np, sizeof(int), cudaMemcpyDeviceToDevice, s));
+    }
+    B2_CUDA(h, cudaGetLastError());
+    return B2ORB_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// exported C ABI
+// =================================================================================================
+extern "C" {
+
+int b2orb_abi_version(void) { return B2ORB_ABI_VERSION; }
+
+int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
+    if (!out || !cfg) return B2ORB_ERR_INVALID;
+    *out = nullptr;
+    if (cfg->nfeatures < 1 || cfg->nlevels < 1 || cfg->nlevels > B2_MAX_LEVELS || !(cfg->scale_factor > 1.f) ||
+        cfg->ini_th_fast < 1 || cfg->min_th_fast < 1 || cfg->min_th_fast > cfg->ini_th_fast ||
+        cfg->ini_th_fast > 254 || cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_images < 1)
+        return B2ORB_ERR_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return B2ORB_ERR_CUDA;
+    b2orb_handle* h = new (std::nothrow) b2orb_handle();
+    if (!h) return B2ORB_ERR_NOMEM;
+    h->cfg = *cfg;
+    h->device = device;
+    *out = h;   // returned even on failure so the caller can read b2orb_last_error, then destroy
+    if (!cuda_ok(h, cudaSetDevice(device), "cudaSetDevice")) return B2ORB_ERR_CUDA;
+    if (!cuda_ok(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) return B2ORB_ERR_CUDA;
+    cudaEventCreate(&h->ev0);
+    cudaEventCreate(&h->ev1);
+    build_ctor_tables(h);
+    return configure(h, cfg->max_width, cfg->max_height);
+}
+
+void b2orb_destroy(b2orb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_workspace(h);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+const char* b2orb_last_error(const b2orb_handle* h) { return h ? h->err.c_str() : "null handle"; }
+int b2orb_keypoint_capacity(const b2orb_handle* h) { return h ? h->geom.kp_cap : 0; }
+uint64_t b2orb_launch_count(const b2orb_handle* h) { return h ? h->launches : 0; }
+float b2orb_last_device_ms(const b2orb_handle* h) { return h ? h->last_ms : 0.f; }
+
+int b2orb_get_tables(const b2orb_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                     int32_t* features_per_level) {
+    if (!h) return B2ORB_ERR_INVALID;
+    for (int i = 0; i < h->cfg.nlevels; ++i) {
+        if (scale) scale[i] = h->scale[i];
+        if (inv_scale) inv_scale[i] = h->inv_scale[i];
+        if (sigma2) sigma2[i] = h->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->inv_sigma2[i];
+        if (features_per_level) features_per_level[i] = h->quota[i];
+    }
+    return B2ORB_OK;
+}
+
+void* b2orb_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    return cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess ? p : nullptr;
+}
+void b2orb_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+int b2orb_sync(b2orb_handle* h) {
+    if (!h) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return B2ORB_OK;
+}
+
+void b2orb_reset_history(b2orb_handle* h) {
+    if (!h || !h->d_nmatch) return;
+    cudaSetDevice(h->device);
+    cudaMemsetAsync(h->d_nmatch, 0, sizeof(int), h->stream);
+}
+
+int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int width, int height, int step,
+                        size_t image_stride, b2orb_keypoint* kps, uint8_t* desc, int cap, int32_t* n) {
+    if (!h || !n || count < 0) return B2ORB_ERR_INVALID;
+    if (count == 0) return B2ORB_OK;
+    if (width == 0 || height == 0) {   // `if(_image.empty()) return;` src/ORBextractor.cc:1046-1047
+        for (int i = 0; i < count; ++i) n[i] = 0;
+        return B2ORB_OK;
+    }
+    if (!images || !kps || !desc || width < 0 || height < 0 || step < width) return fail(h, B2ORB_ERR_INVALID, "bad image arguments");
+    if (count > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "count exceeds max_images");
+    if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = configure(h, width, height);
+    if (rc) return rc;
+    const int kcap = h->geom.kp_cap;
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = upload(h, images, count, width, height, step, image_stride, 0))) return rc;
+    B2Images im = make_images(h, h->d_stage, h->d_stage, count, h->stage_img_bytes, width);
+    if ((rc = launch_extract(h, im, count))) return rc;
+    B2_CUDA(h, cudaMemcpyAsync(n, h->d_nkp, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    cudaEventRecord(h->ev1, h->stream);
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    for (int i = 0; i < count; ++i) {
+        if (n[i] > cap) return fail(h, B2ORB_ERR_CAPACITY, "keypoint buffer too small");
+        if (n[i] == 0) continue;
+        B2_CUDA(h, cudaMemcpyAsync(kps + (size_t)i * cap, h->d_kps + (size_t)i * kcap, (size_t)n[i] * sizeof(b2orb_keypoint),
+                                   cudaMemcpyDeviceToHost, h->stream));
+        B2_CUDA(h, cudaMemcpyAsync(desc + (size_t)i * cap * 32, h->d_desc + (size_t)i * kcap * 32, (size_t)n[i] * 32,
+                                   cudaMemcpyDeviceToHost, h->stream));
+    }
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    return B2ORB_OK;
+}
+
+int b2orb_extract(b2orb_handle* h, const uint8_t* image, int width, int height, int step, b2orb_keypoint* kps,
+                  uint8_t* desc, int cap, int* n) {
+    if (!n) return B2ORB_ERR_INVALID;
+    int32_t cnt = 0;
+    const int rc = b2orb_extract_batch(h, image, 1, width, height, step, (size_t)step * (size_t)(height > 0 ? height : 0),
+                                       kps, desc, cap, &cnt);
+    *n = cnt;
+    return rc;
+}
+
+int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, const uint8_t* d_images_r, int npairs,
+                                 int width, int height, int step, size_t image_stride, int temporal) {
+    if (!h || !d_images_l || !d_images_r || npairs < 1 || width < 1 || height < 1 || step < width)
+        return fail(h, B2ORB_ERR_INVALID, "bad stereo arguments");
+    if (2 * npairs > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*npairs exceeds max_images");
+    if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = configure(h, width, height);
+    if (rc) return rc;
+    if ((rc = bind_problems(h, npairs))) return rc;
+    cudaEventRecord(h->ev0, h->stream);
+    B2Images im = make_images(h, d_images_l, d_images_r, npairs, image_stride, step);
+    rc = launch_stereo(h, im, npairs, temporal);
+    cudaEventRecord(h->ev1, h->stream);
+    return rc;
+}
+
+int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o) {
+    if (!h || !o || npairs < 1 || 2 * npairs > h->nimg_cap) return B2ORB_ERR_INVALID;
+    const int kcap = h->geom.kp_cap;
+    if (o->cap < kcap) return fail(h, B2ORB_ERR_CAPACITY, "b2orb_stereo_out.cap below b2orb_keypoint_capacity()");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    const size_t np = npairs;
+    // cap == kcap lets every slab go back in one copy; otherwise row-wise 2D copies
+    auto copy2d = [&](void* dst, const void* src, size_t elem, size_t rows) -> cudaError_t {
+        if (!dst) return cudaSuccess;
+        return cudaMemcpy2DAsync(dst, (size_t)o->cap * elem, src, (size_t)kcap * elem, (size_t)kcap * elem, rows,
+                                 cudaMemcpyDeviceToHost, s);
+    };
+    B2_CUDA(h, copy2d(o->kp_l, h->d_kps, sizeof(b2orb_keypoint), np));
+    B2_CUDA(h, copy2d(o->kp_r, h->d_kps + np * kcap, sizeof(b2orb_keypoint), np));
+    B2_CUDA(h, copy2d(o->desc_l, h->d_desc, 32, np));
+    B2_CUDA(h, copy2d(o->desc_r, h->d_desc + np * kcap * 32, 32, np));
+    B2_CUDA(h, copy2d(o->train_idx, h->d_train, 4, np));
+    B2_CUDA(h, copy2d(o->dist, h->d_dist, 4, np));
+    B2_CUDA(h, copy2d(o->match_l, h->d_match_l, 4, np));
+    B2_CUDA(h, copy2d(o->match_r, h->d_match_r, 4, np));
+    B2_CUDA(h, copy2d(o->circ_cur, h->d_circ_cur, 4, np));
+    B2_CUDA(h, copy2d(o->circ_hist, h->d_circ_hist, 4, np));
+    if (o->n_l) B2_CUDA(h, cudaMemcpyAsync(o->n_l, h->d_nkp, np * 4, cudaMemcpyDeviceToHost, s));
+    if (o->n_r) B2_CUDA(h, cudaMemcpyAsync(o->n_r, h->d_nkp + np, np * 4, cudaMemcpyDeviceToHost, s));
+    if (o->n_match) B2_CUDA(h, cudaMemcpyAsync(o->n_match, h->d_nmatch + 1, np * 4, cudaMemcpyDeviceToHost, s));
+    if (o->n_circ) B2_CUDA(h, cudaMemcpyAsync(o->n_circ, h->d_ncirc, np * 4, cudaMemcpyDeviceToHost, s));
+    B2_CUDA(h, cudaStreamSynchronize(s));
+    return B2ORB_OK;
+}
+
+int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
+                          int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out) {
+    if (!h || !images_l || !images_r || !out || npairs < 1 || width < 1 || height < 1 || step < width)
+        return fail(h, B2ORB_ERR_INVALID, "bad stereo arguments");
+    if (2 * npairs > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*npairs exceeds max_images");
+    if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = configure(h, width, height);
+    if (rc) return rc;
+    if ((rc = bind_problems(h, npairs))) return rc;
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0))) return rc;
+    if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs))) return rc;
+    B2Images im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs,
+                              h->stage_img_bytes, width);
+    if ((rc = launch_stereo(h, im, npairs, temporal))) return rc;
+    cudaEventRecord(h->ev1, h->stream);
+    rc = b2orb_stereo_download(h, npairs, out);
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return rc;
+}
+
+// ---- generic matcher entry points (host descriptor sets) ------------------------------------------
+static int ensure_generic(b2orb_handle* h, int nq, int nt) {
+    if (nq > h->g_cap_q) {
+        const int c = std::max(nq, 2 * h->g_cap_q);
+        if (!dev_alloc(h, &h->d_gq, (size_t)c * 32) || !dev_alloc(h, &h->d_gq2, (size_t)c * 32) ||
+            !dev_alloc(h, &h->d_gidx, (size_t)c) || !dev_alloc(h, &h->d_gdist, (size_t)c) ||
+            !dev_alloc(h, &h->d_gidx2, (size_t)c) || !dev_alloc(h, &h->d_gdist2, (size_t)c))
+            return B2ORB_ERR_NOMEM;
+        h->g_cap_q = c;
+    }
+    if (nt > h->g_cap_t) {
+        const int c = std::max(nt, 2 * h->g_cap_t);
+        if (!dev_alloc(h, &h->d_gt, (size_t)c * 32) || !dev_alloc(h, &h->d_gt2, (size_t)c * 32)) return B2ORB_ERR_NOMEM;
+        h->g_cap_t = c;
+    }
+    return B2ORB_OK;
+}
+
+int b2orb_match(b2orb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, int32_t* train_idx,
+                int32_t* dist) {
+    if (!h || nq < 0 || nt < 0) return B2ORB_ERR_INVALID;
+    if (nq == 0) return B2ORB_OK;
+    if (!query || !train_idx || !dist || (nt > 0 && !train)) return fail(h, B2ORB_ERR_INVALID, "bad match arguments");
+    if (nt == 0) {   // BFMatcher on an empty train set returns no matches
+        for (int i = 0; i < nq; ++i) { train_idx[i] = -1; dist[i] = 0x7fffffff; }
+        return B2ORB_OK;
+    }
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = ensure_generic(h, nq, nt);
+    if (rc) return rc;
+    cudaStream_t s = h->stream;
+    const int cnt[2] = {nq, nt};
+    B2MatchProblem pr = {h->d_gq, h->d_gt, h->d_gcnt, h->d_gcnt + 1, h->d_gidx, h->d_gdist};
+    B2MatchProblem* slot = h->d_probs + (size_t)3 * h->npair_cap;
+    cudaEventRecord(h->ev0, s);
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gq, query, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gt, train, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gcnt, cnt, sizeof cnt, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(slot, &pr, sizeof pr, cudaMemcpyHostToDevice, s));
+    b2_launch_match(slot, 1, nq, s);
+    ++h->launches;
+    B2_CUDA(h, cudaGetLastError());
+    B2_CUDA(h, cudaMemcpyAsync(train_idx, h->d_gidx, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    B2_CUDA(h, cudaMemcpyAsync(dist, h->d_gdist, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    cudaEventRecord(h->ev1, s);
+    B2_CUDA(h, cudaStreamSynchronize(s));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return B2ORB_OK;
+}
+
+int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* cur_r, int ncur, const uint8_t* hist_l,
+                         const uint8_t* hist_r, int nhist, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ,
+                         int32_t* n_left, int32_t* n_right) {
+    if (!h || !n_circ || ncur < 0 || nhist < 0) return B2ORB_ERR_INVALID;
+    *n_circ = 0;
+    if (n_left) *n_left = 0;
+    if (n_right) *n_right = 0;
+    if (ncur == 0 || nhist == 0) return B2ORB_OK;   // externalTrack early-out, src/feature-tracker.cpp:237-240
+    if (!cur_l || !cur_r || !hist_l || !hist_r || !circ_cur || !circ_hist) return fail(h, B2ORB_ERR_INVALID, "bad temporal arguments");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = ensure_generic(h, ncur, nhist);
+    if (rc) return rc;
+    cudaStream_t s = h->stream;
+    const int cnt[2] = {ncur, nhist};
+    B2MatchProblem pr[2] = {{h->d_gq, h->d_gt, h->d_gcnt, h->d_gcnt + 1, h->d_gidx, h->d_gdist},
+                            {h->d_gq2, h->d_gt2, h->d_gcnt, h->d_gcnt + 1, h->d_gidx2, h->d_gdist2}};
+    B2MatchProblem* slot = h->d_probs + (size_t)3 * h->npair_cap + 1;
+    int* d_out = h->d_gcnt + 2;   // n_circ, n_left, n_right
+    cudaEventRecord(h->ev0, s);
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gq, cur_l, (size_t)ncur * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gq2, cur_r, (size_t)ncur * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gt, hist_l, (size_t)nhist * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gt2, hist_r, (size_t)nhist * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_gcnt, cnt, sizeof cnt, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(slot, pr, sizeof pr, cudaMemcpyHostToDevice, s));
+    b2_launch_match(slot, 2, ncur, s);
+    ++h->launches;
+    // circular check reuses the cur-side index buffers as outputs' staging: circ lists go to d_gdist/d_gdist2
+    // only after the kernel has read them, so use separate regions: the q buffers are free after matching.
+    int* d_cc = reinterpret_cast<int*>(h->d_gq);
+    int* d_ch = reinterpret_cast<int*>(h->d_gq2);
+    b2_launch_circular(h->d_gidx, h->d_gdist, h->d_gidx2, h->d_gdist2, h->d_gcnt, h->d_gcnt + 1, 0, h->cfg.match_ratio,
+                       h->cfg.min_match_dist, d_cc, d_ch, d_out, d_out + 1, d_out + 2, 1, s);
+    ++h->launches;
+    B2_CUDA(h, cudaGetLastError());
+    int out[3] = {0, 0, 0};
+    B2_CUDA(h, cudaMemcpyAsync(out, d_out, sizeof out, cudaMemcpyDeviceToHost, s));
+    cudaEventRecord(h->ev1, s);
+    B2_CUDA(h, cudaStreamSynchronize(s));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    *n_circ = out[0];
+    if (n_left) *n_left = out[1];
+    if (n_right) *n_right = out[2];
+    if (out[0] > 0) {
+        B2_CUDA(h, cudaMemcpyAsync(circ_cur, d_cc, (size_t)out[0] * 4, cudaMemcpyDeviceToHost, s));
+        B2_CUDA(h, cudaMemcpyAsync(circ_hist, d_ch, (size_t)out[0] * 4, cudaMemcpyDeviceToHost, s));
+        B2_CUDA(h, cudaStreamSynchronize(s));
+    }
+    return B2ORB_OK;
+}
+
+// ---- debug / test access -----------------------------------------------------------------------
+int b2orb_debug_level_size(const b2orb_handle* h, int level, int* w, int* hgt) {
+    if (!h || level < 0 || level >= h->geom.nlevels || !w || !hgt) return B2ORB_ERR_INVALID;
+    *w = h->geom.lv[level].w;
+    *hgt = h->geom.lv[level].h;
+    return B2ORB_OK;
+}
+
+int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8_t* dst) {
+    if (!h || !dst || slot < 0 || slot >= h->nimg_cap || level < 0 || level >= h->geom.nlevels) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    const B2Level& L = h->geom.lv[level];
+    const uint8_t* src;
+    size_t pitch;
+    if (which == 0 && level == 0) {   // level 0 of the last host-input call lives in the staging area
+        src = h->d_stage + (size_t)slot * h->stage_img_bytes;
+        pitch = h->cur_w;
+    } else {
+        src = (which ? h->d_blur : h->d_pyr) + (size_t)slot * h->geom.slab + L.off;
+        pitch = L.pitch;
+    }
+    B2_CUDA(h, cudaMemcpy2DAsync(dst, L.w, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    return B2ORB_OK;
+}
+
+int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* dst, int cap, int* n) {
+    if (!h || !n || slot < 0 || slot >= h->nimg_cap || level < 0 || level >= h->geom.nlevels) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int cnt = 0;
+    B2_CUDA(h, cudaMemcpyAsync(&cnt, h->d_cand_cnt + slot * h->geom.nlevels + level, 4, cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    *n = cnt;
+    const int m = std::min(std::min(cnt, cap), h->geom.lv[level].cand_cap);
+    if (m > 0 && dst) {
+        B2_CUDA(h, cudaMemcpyAsync(dst, h->d_cand + (size_t)slot * h->geom.cand_total + h->geom.lv[level].cand_off,
+                                   (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream));
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    return B2ORB_OK;
+}
+
+}  // extern "C"

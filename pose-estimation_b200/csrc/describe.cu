@@ -1,0 +1,176 @@
+// Orientation + rotated-BRIEF descriptors + keypoint assembly, one warp per selected keypoint.
+//   * IC_Angle, src/ORBextractor.cc:77-104 (K5): m10, m01 over the radius-15 disc (row extents umax) of the
+//     UN-blurred level, angle = cv::fastAtan2((float)m01, (float)m10) — OpenCV's fp32 7th-order polynomial,
+//     evaluated without FMA (__fmul_rn/__fadd_rn; an FMA changes 2 % of results).
+//   * computeOrbDescriptor, src/ORBextractor.cc:108-147 (K7): angle*factorPI, a = cosf, b = sinf (glibc
+//     2.39's algorithm restated in double, verified bit-identical over every float in [0, 2*pi]),
+//     offsets cvRound(x*b + y*a), cvRound(x*a - y*b) with separately rounded products (no FMA) and
+//     round-half-even, 256 comparisons on the BLURRED level, LSB-first bytes.
+//   * keypoint fields, :818-826, 837-847, 1095-1101 (K8): level offset +16, octave, size, pt *= scale.
+// Levels are concatenated in ascending order (:1076-1104); slot offsets come from the per-level counts.
+#include "b2orb_internal.cuh"
+
+namespace {
+
+__device__ const signed char kPattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+struct KeyPointOut {   // == cv::KeyPoint == b2orb_keypoint
+    float x, y, size, angle, response;
+    int octave, class_id;
+};
+
+// cv::fastAtan2 (degrees), fp32, no contraction.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    const float scale = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale,
+                p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
+    const float eps = (float)2.2204460492503131e-16;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// glibc 2.39 sincosf kernel (sysdeps/ieee754/flt-32/sincosf.h): n even -> sine poly, odd -> cosine poly.
+__device__ __forceinline__ float sincos_poly(double x, double x2, int n, bool neg) {
+    const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+                 C4 = 0x1.99343027bf8c3p-16;
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    if ((n & 1) == 0) {
+        const double x3 = __dmul_rn(x, x2);
+        const double s1 = __dadd_rn(S2, __dmul_rn(x2, S3));
+        const double x7 = __dmul_rn(x3, x2);
+        const double s = __dadd_rn(x, __dmul_rn(x3, S1));
+        return __double2float_rn(__dadd_rn(s, __dmul_rn(x7, s1)));
+    }
+    const double sg = neg ? -1.0 : 1.0;
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __dadd_rn(sg * C3, __dmul_rn(x2, sg * C4));
+    const double c1 = __dadd_rn(sg * C0, __dmul_rn(x2, sg * C1));
+    const double x6 = __dmul_rn(x4, x2);
+    const double c = __dadd_rn(c1, __dmul_rn(x4, sg * C2));
+    return __double2float_rn(__dadd_rn(c, __dmul_rn(x6, c2)));
+}
+
+// cosf and sinf of y in [0, 2*pi] exactly as glibc computes them.
+__device__ __forceinline__ void glibc_sincosf(float y, float& sn, float& cs) {
+    const double x = (double)y;
+    const unsigned top = (__float_as_uint(y) >> 20) & 0x7ff;
+    if (top < ((__float_as_uint(0x1.921FB6p-1f) >> 20) & 0x7ff)) {   // |y| < pi/4
+        if (top < ((__float_as_uint(0x1p-12f) >> 20) & 0x7ff)) { sn = y; cs = 1.0f; return; }
+        const double x2 = __dmul_rn(x, x);
+        sn = sincos_poly(x, x2, 0, false);
+        cs = sincos_poly(x, x2, 1, false);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+    const int n = ((int)r + 0x800000) >> 24;                       // (int32_t)r truncates; r >= 0 here
+    const double xr = __dsub_rn(x, __dmul_rn((double)n, 0x1.921FB54442D18p0));
+    const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    const bool neg = (n & 2) != 0;
+    const double xs = __dmul_rn(xr, sgn), x2 = __dmul_rn(xr, xr);
+    sn = sincos_poly(xs, x2, n, neg);
+    cs = sincos_poly(xs, x2, n ^ 1, neg);
+}
+
+constexpr int DS_WARPS = 8;
+
+__global__ void __launch_bounds__(DS_WARPS * 32)
+describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
+                const int* __restrict__ sel_cnt, KeyPointOut* __restrict__ kps, uint8_t* __restrict__ desc,
+                int* __restrict__ n_out) {
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * DS_WARPS + (threadIdx.x >> 5);   // output slot in this image
+    // level of this slot from the per-level counts
+    int level = 0, base = 0, total = 0;
+    bool found = false;
+    for (int l = 0; l < g.nlevels; ++l) {
+        const int c = max(sel_cnt[b * g.nlevels + l], 0);
+        if (!found && slot < total + c) { level = l; base = total; found = true; }
+        total += c;
+    }
+    if (slot == 0 && lane == 0) n_out[b] = min(total, g.kp_cap);
+    if (!found || slot >= g.kp_cap) return;
+    const B2Level& L = g.lv[level];
+    const uint32_t v = sel[(size_t)b * g.sel_total + L.sel_base + (slot - base)];
+    const int cx = (int)(v & 0xFFF) + B2_BORDER, cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
+    const float response = (float)(v >> 24);
+
+    // ---- IC_Angle on the un-blurred level
+    int pitch;
+    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
+    const uint8_t* center = img + (size_t)cy * pitch + cx;
+    int m01 = 0, m10 = 0;
+    const int u = lane - B2_HALF_PATCH;    // lanes 0..30 -> u = -15..15
+    if (lane < 31) {
+        const int au = abs(u);
+        for (int vv = -B2_HALF_PATCH; vv <= B2_HALF_PATCH; ++vv) {
+            if (au <= g.umax[abs(vv)]) {
+                const int val = center[vv * pitch + u];
+                m10 += u * val;
+                m01 += vv * val;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
+        m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // ---- descriptor on the blurred level: lane = output byte
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+    float a, bsn;
+    glibc_sincosf(__fmul_rn(angle, factorPI), bsn, a);
+    const uint8_t* bl = im.blur + (size_t)b * g.slab + L.off + (size_t)cy * L.pitch + cx;
+    const int bp = L.pitch;
+    const signed char* pat = kPattern + lane * 32;
+    unsigned val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        int t[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const float px = (float)pat[4 * j + 2 * e], py = (float)pat[4 * j + 2 * e + 1];
+            const int dy = __float2int_rn(__fadd_rn(__fmul_rn(px, bsn), __fmul_rn(py, a)));
+            const int dx = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bsn)));
+            t[e] = bl[dy * bp + dx];
+        }
+        val |= (unsigned)(t[0] < t[1]) << j;
+    }
+    desc[((size_t)b * g.kp_cap + slot) * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        KeyPointOut k;
+        k.x = (float)cx;
+        k.y = (float)cy;
+        if (level != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }
+        k.size = L.kp_size;
+        k.angle = angle;
+        k.response = response;
+        k.octave = level;
+        k.class_id = -1;
+        kps[(size_t)b * g.kp_cap + slot] = k;
+    }
+}
+
+}  // namespace
+
+void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,
+                        uint8_t* desc, int* n_out, int nimg, cudaStream_t s) {
+    dim3 grid((g.kp_cap + DS_WARPS - 1) / DS_WARPS, nimg);
+    describe_kernel<<<grid, DS_WARPS * 32, 0, s>>>(g, im, sel, sel_cnt, static_cast<KeyPointOut*>(kps), desc, n_out);
+}

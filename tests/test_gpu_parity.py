@@ -1,0 +1,187 @@
+"""GPU parity: the CUDA path (through the C ABI, include/b2orb.h) vs the CPU oracle, bit-exact.
+
+Stage by stage (pyramid, blur, raw FAST corners, quadtree selection, angles, descriptors, keypoints)
+and end to end (stereo match + filters, temporal circular matching) on seeded synthetic inputs at the
+shapes of BASELINE.json's configs.  Bar: bit-exact for every integer/byte/index output AND for the float
+fields (angle, x, y) — the north star allows 1e-4 rad on angles, we assert exact equality.
+"""
+import numpy as np
+import pytest
+
+from tests.conftest import pkg
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fe():
+    return pkg("frontend")
+
+
+def assert_extract_equal(got, ref, tag=""):
+    gk, gd = got
+    rk, rd = ref
+    assert len(gk) == len(rk), f"{tag}: keypoint count {len(gk)} vs {len(rk)}"
+    for f in ("octave", "x", "y", "response", "size", "angle", "class_id"):
+        assert np.array_equal(gk[f], rk[f]), f"{tag}: field {f} differs at {np.flatnonzero(gk[f] != rk[f])[:8]}"
+    assert np.array_equal(gd, rd), f"{tag}: descriptors differ on rows {np.flatnonzero((gd != rd).any(1))[:8]}"
+
+
+CASES = [
+    # name, w, h, nfeatures, ini, min, seed, passes
+    ("euroc", 752, 480, 1000, 20, 7, 0, 3),
+    ("euroc_yml800", 752, 480, 800, 20, 7, 1, 3),
+    ("cfsd", 672, 376, 1000, 20, 7, 2, 3),
+    ("kitti", 1241, 376, 2000, 12, 7, 3, 3),
+    ("lowtex", 400, 300, 500, 20, 7, 4, 8),
+    ("odd", 333, 211, 300, 20, 7, 5, 3),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_extract_stages_match_oracle(case, fe, oracle, synth):
+    _, w, h, nf, ini, mn, seed, passes = case
+    img = synth.canvas(w, h, seed, passes)[:h, :w].copy()
+    ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
+    ref = ex(img)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    got = hd.extract(img)
+    for lvl in range(8):
+        assert np.array_equal(hd.debug_level(0, lvl), ex.level(lvl)), f"pyramid level {lvl}"
+        rb = ex.level(lvl, blurred=True)
+        if rb is not None:
+            assert np.array_equal(hd.debug_level(0, lvl, blurred=True), rb), f"blurred level {lvl}"
+        c = hd.debug_candidates(0, lvl)
+        r = ex.raw_corners(lvl).astype(np.int32)
+        cs = c[np.lexsort((c[:, 0], c[:, 1]))]
+        rs = r[np.lexsort((r[:, 0], r[:, 1]))]
+        assert cs.shape == rs.shape and np.array_equal(cs, rs), f"raw FAST corners level {lvl}"
+    assert_extract_equal(got, ref, case[0])
+    s, i, s2, i2, q = hd.tables()
+    os_, oi, oq, _ = ex.tables()
+    assert np.array_equal(s, os_) and np.array_equal(i, oi) and np.array_equal(q, oq)
+    hd.close()
+
+
+def test_extract_batch_and_resize_of_workspace(fe, oracle, synth):
+    ls, rs = synth.sequence("cfsd", 3, seed=7)
+    hd = fe.Handle(1000, 1.2, 8, 20, 7, 752, 480, max_images=6)
+    res = hd.extract_batch(np.concatenate([ls, rs]))
+    ex = oracle.OracleExtractor(1000, 1.2, 8, 20, 7)
+    for k, img in enumerate(list(ls) + list(rs)):
+        assert_extract_equal(res[k], ex(img), f"batch image {k}")
+    # another size on the same handle (workspace is rebuilt), given as a strided view
+    img = synth.canvas(500, 400, 9)[:400, :500]
+    assert_extract_equal(hd.extract(img), ex(np.ascontiguousarray(img)), "strided 500x400")
+    hd.close()
+
+
+def test_empty_and_degenerate_inputs(fe, oracle):
+    hd = fe.Handle(500, 1.2, 8, 20, 7, 256, 256, max_images=2)
+    k, d = hd.extract(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    flat = np.full((200, 256), 128, np.uint8)            # no corners anywhere
+    k, d = hd.extract(flat)
+    assert len(k) == 0
+    ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
+    rng = np.random.default_rng(3)
+    tiny = rng.integers(0, 256, (70, 90), dtype=np.uint8)  # upper levels have no FAST cells
+    assert_extract_equal(hd.extract(tiny), ex(tiny), "tiny 90x70")
+    hd.close()
+
+
+def test_orbextractor_mirror_matches_oracle(fe, oracle, synth):
+    img = synth.canvas(640, 360, 11)[:360, :640].copy()
+    ext = fe.ORBextractor(700, 1.2, 8, 20, 7)
+    kps, desc = ext(img, None)
+    assert_extract_equal((kps, desc), oracle.OracleExtractor(700, 1.2, 8, 20, 7)(img), "ORBextractor mirror")
+    assert ext.GetLevels() == 8 and abs(ext.GetScaleFactor() - 1.2) < 1e-6
+    assert np.array_equal(ext.GetScaleFactors(), oracle.OracleExtractor(700, 1.2, 8, 20, 7).tables()[0])
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 1), (500, 700), (1000, 1000), (37, 2051), (2000, 129)])
+def test_bf_match_matches_oracle(nq, nt, fe, oracle):
+    rng = np.random.default_rng(nq * 7 + nt)
+    protos = rng.integers(0, 256, (9, 32), dtype=np.uint8)
+    q = protos[rng.integers(0, 9, nq)].copy(); t = protos[rng.integers(0, 9, nt)].copy()
+    q[rng.integers(0, nq, nq // 2 + 1), rng.integers(0, 32, nq // 2 + 1)] ^= 0x10
+    t[rng.integers(0, nt, nt // 2 + 1), rng.integers(0, 32, nt // 2 + 1)] ^= 0x01
+    hd = fe.Handle(500, 1.2, 8, 20, 7, 128, 128, max_images=2)
+    ti, di = hd.match(q, t)
+    oi, od = oracle.bf_match(q, t)
+    assert np.array_equal(ti, oi) and np.array_equal(di, od)
+    ti, di = hd.match(q, np.zeros((0, 32), np.uint8))
+    assert (ti == -1).all()
+    hd.close()
+
+
+@pytest.mark.parametrize("shape,npairs", [("euroc", 3), ("kitti", 2), ("cfsd", 4)])
+def test_stereo_frontend_matches_oracle(shape, npairs, fe, oracle, synth):
+    """internalMatch (extract L/R + BF match + min-dist/row filter) and the temporal circular matching."""
+    w, h, nf, ini, mn = synth.SHAPES[shape]
+    ls, rs = synth.sequence(shape, npairs, seed=21)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    o = hd.stereo_frontend(ls, rs, temporal=True)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
+    prev = None
+    for p in range(npairs):
+        kl, dl = ex(ls[p]); kr, dr = ex(rs[p])
+        nl, nr = int(o["n_l"][p]), int(o["n_r"][p])
+        assert_extract_equal((o["kp_l"][p, :nl], o["desc_l"][p, :nl]), (kl, dl), f"pair {p} left")
+        assert_extract_equal((o["kp_r"][p, :nr], o["desc_r"][p, :nr]), (kr, dr), f"pair {p} right")
+        ti, di = oracle.bf_match(dl, dr)
+        assert np.array_equal(o["train_idx"][p, :nl], ti) and np.array_equal(o["dist"][p, :nl], di)
+        ml, mr = oracle.stereo_filter(ti, di, kl, kr, 2.0, 30.0, 0.1)
+        m = int(o["n_match"][p])
+        assert m == len(ml) and m > 20, f"pair {p}: {m} matches"
+        assert np.array_equal(o["match_l"][p, :m], ml) and np.array_equal(o["match_r"][p, :m], mr)
+        cur_l, cur_r = dl[ml], dr[mr]
+        if prev is None:
+            assert o["n_circ"][p] == 0
+        else:
+            tl, d1 = oracle.bf_match(cur_l, prev[0]); tr, d2 = oracle.bf_match(cur_r, prev[1])
+            ql, hl = oracle.threshold_filter(tl, d1, len(prev[0]), 2.0, 30.0)
+            qr, hr = oracle.threshold_filter(tr, d2, len(prev[1]), 2.0, 30.0)
+            mp = dict(zip(ql.tolist(), hl.tolist()))
+            circ = [(q, t) for q, t in zip(qr.tolist(), hr.tolist()) if mp.get(q) == t]
+            nc = int(o["n_circ"][p])
+            assert nc == len(circ) and nc > 5
+            assert list(zip(o["circ_cur"][p, :nc].tolist(), o["circ_hist"][p, :nc].tolist())) == circ
+        prev = (cur_l, cur_r)
+    # history carries over to the next call: pair 0 of a second call matches against the last pair
+    o2 = hd.stereo_frontend(ls[:1], rs[:1], temporal=True)
+    assert o2["n_circ"][0] > 0
+    hd.reset_history()
+    assert hd.stereo_frontend(ls[:1], rs[:1], temporal=True)["n_circ"][0] == 0
+    hd.close()
+
+
+def test_temporal_track_entry_point(fe, oracle):
+    rng = np.random.default_rng(5)
+    hist_l = rng.integers(0, 256, (300, 32), dtype=np.uint8); hist_r = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    pick = rng.permutation(300)[:200]
+    cur_l, cur_r = hist_l[pick].copy(), hist_r[pick].copy()
+    cur_l[::3, 0] ^= 0x3; cur_r[::5, 1] ^= 0x7; cur_r[::7] = rng.integers(0, 256, (len(cur_r[::7]), 32), dtype=np.uint8)
+    hd = fe.Handle(500, 1.2, 8, 20, 7, 128, 128, max_images=2)
+    cc, ch, nl, nr = hd.temporal_track(cur_l, cur_r, hist_l, hist_r)
+    tl, d1 = oracle.bf_match(cur_l, hist_l); tr, d2 = oracle.bf_match(cur_r, hist_r)
+    ql, hl = oracle.threshold_filter(tl, d1, 300, 2.0, 30.0); qr, hr = oracle.threshold_filter(tr, d2, 300, 2.0, 30.0)
+    mp = dict(zip(ql.tolist(), hl.tolist()))
+    circ = [(q, t) for q, t in zip(qr.tolist(), hr.tolist()) if mp.get(q) == t]
+    assert (nl, nr) == (len(ql), len(qr))
+    assert list(zip(cc.tolist(), ch.tolist())) == circ and len(circ) > 50
+    assert hd.temporal_track(cur_l, cur_r, hist_l[:0], hist_r[:0])[0].size == 0
+    hd.close()
+
+
+def test_error_codes(fe):
+    with pytest.raises(fe.B2Error):
+        fe.Handle(1000, 0.9, 8, 20, 7, 100, 100)          # scaleFactor must be > 1
+    hd = fe.Handle(500, 1.2, 8, 20, 7, 128, 128, max_images=2)
+    with pytest.raises(fe.B2Error) as e:
+        hd.extract(np.zeros((300, 300), np.uint8))        # larger than configured
+    assert e.value.code == fe.ERR_INVALID
+    with pytest.raises(fe.B2Error) as e:
+        hd.extract_batch(np.zeros((3, 100, 100), np.uint8))  # more than max_images
+    assert e.value.code == fe.ERR_CAPACITY
+    hd.close()
