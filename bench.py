@@ -1,0 +1,306 @@
+#!/usr/bin/env python3
+"""bench.py — ORB extract + stereo/temporal Hamming match throughput (BASELINE.json metric).
+
+A "step" = one pass of the hot path over one batch of synthetic stereo pairs (default: KITTI-shaped
+1241x376, 2000 features, stereo + temporal matching = BASELINE.json configs[1]).
+  value : stereo pairs/s with the input images already resident in HBM (b2orb_stereo_frontend_device),
+          timed with CUDA events on the handle's stream, max over ranks.
+  e2e   : the same metric through the host-buffer C-ABI call (b2orb_stereo_frontend): pinned host images in,
+          H2D + kernels + D2H of every result slab inside the timed region (two handles on two host threads
+          so copies overlap kernels, the way the reference drives two extractor instances from two threads).
+  roofline : dominant kernel, algorithmic bytes / live CUDA-event duration vs the measured HBM peak.
+  cpu_baseline : the CPU oracle (port of the reference path) on this box's host cores, bounded sample.
+`--impl reference` times only that CPU port (the reference itself needs OpenCV C++/Eigen/Ceres and cannot be
+built here) with all host threads.
+Multi-GPU (torchrun): every rank runs the same per-GPU workload on its own GPU (weak scaling, no collective on
+the data path); only per-pair count summaries are gathered.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "orb_extract_stereo_match_pairs_per_s"
+UNIT = "stereo pairs/s"
+
+
+def algorithmic_bytes(geom_levels, nfeat, temporal):
+    """B_pair = 2*B_img + B_match; returns (B_pair, per-kernel bytes per PAIR)."""
+    p = [w * h for (w, h) in geom_levels]
+    b_img = p[0] + 2 * sum(p[1:]) + sum(p) + nfeat * (961 + 1369) + nfeat * (32 + 28)
+    b_match = 2 * nfeat * 32 + nfeat * 8
+    per_kernel = {
+        "resize": 2 * (sum(p[:-1]) + sum(p[1:])),          # read level l-1, write level l
+        "fast": 2 * sum(p),                                # read every pyramid pixel once
+        "blur": 2 * 2 * sum(p),                            # read + write every level
+        "describe": 2 * nfeat * (961 + 1369 + 32 + 28),
+        "match_stereo": b_match,
+    }
+    return 2 * b_img + b_match * (3 if temporal else 1), per_kernel
+
+
+def level_sizes(w, h, nlevels=8, sf=1.2):
+    s = np.float32(1.0)
+    out = []
+    for _ in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        s = np.float32(float(s) * float(np.float32(sf)))
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                      stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        sm = [int(r[0]) for r in self.rows if r and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_baseline(synth, orc, shape, cfg, temporal, workers, target_s):
+    """Oracle on host cores, bounded sample sized from a 1-round probe (about `target_s` seconds)."""
+    probe_n = max(workers, 2)
+    ls, rs = synth.sequence(shape, probe_n, seed=1)
+    t = time.perf_counter()
+    orc.run_pairs(cfg, ls, rs, synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST, workers, 1, temporal)
+    dt = time.perf_counter() - t
+    n = int(min(max(probe_n, target_s / max(dt, 1e-3) * probe_n), 64 * workers))
+    n = max(workers, n // workers * workers)
+    ls, rs = synth.sequence(shape, n, seed=1)
+    t = time.perf_counter()
+    orc.run_pairs(cfg, ls, rs, synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST, workers, 1, temporal)
+    dt = time.perf_counter() - t
+    return n / dt, n, dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="kitti", help="shape name from synth.SHAPES")
+    ap.add_argument("--pairs-per-step", type=int, default=128)
+    ap.add_argument("--pool", type=int, default=160, help="distinct synthetic pairs resident (cycled)")
+    ap.add_argument("--no-temporal", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    args = ap.parse_args()
+
+    synth = importlib.import_module("pose-estimation_b200.synth")
+    w, h, nfeat, ini, mn = synth.SHAPES[args.workload]
+    temporal = not args.no_temporal and args.workload.startswith("kitti")
+    cfg = (nfeat, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    config = {"workload": f"{args.workload} {w}x{h} stereo, {nfeat} ORB feats, 8 levels x1.2, ini/min FAST {ini}/{mn}, "
+                          f"BF Hamming stereo{' + temporal circular' if temporal else ''} matching",
+              "pairs_per_step": args.pairs_per_step, "pool_pairs": args.pool, "sharding": f"frames x{world} (no collective)",
+              "l2": "inputs + intermediates per step (>700 MB) exceed the 126 MB L2; the pool of distinct pairs is cycled"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        from oracle import oracle as orc
+        workers = os.cpu_count() or 1
+        per_step = max(workers, 2)
+        ls, rs = synth.sequence(args.workload, per_step, seed=1)
+        run = lambda: orc.run_pairs(cfg, ls, rs, synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST,
+                                    workers, 1, temporal)
+        steps, warm = args.steps, args.warmup
+        for _ in range(warm):
+            run()
+        t = time.perf_counter()
+        for _ in range(steps):
+            run()
+        dt = time.perf_counter() - t
+        v = per_step * steps / dt
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": dict(config, pairs_per_step=per_step),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": workers, "kind": "port",
+                             "sample": f"{per_step} pairs/step x {steps} steps, pairs sharded over {workers} host threads"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference needs OpenCV C++/Eigen/Ceres (absent): CPU oracle port of the same path timed instead"}))
+        return 0
+
+    import torch
+    fe = importlib.import_module("pose-estimation_b200.frontend")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B, pool = args.pairs_per_step, max(args.pool, args.pairs_per_step)
+    ls, rs = synth.sequence(args.workload, pool, seed=rank)
+    d_l = torch.from_numpy(ls).cuda()
+    d_r = torch.from_numpy(rs).cuda()
+    torch.cuda.synchronize()
+    hd = fe.Handle(*cfg, w, h, max_images=2 * B, device=local)
+    stream = torch.cuda.ExternalStream(hd.stream, device=torch.device("cuda", local))
+    img_bytes = w * h
+
+    def step_device(k):
+        off = (k * 37) % (pool - B + 1)
+        hd.stereo_frontend_device(d_l.data_ptr() + off * img_bytes, d_r.data_ptr() + off * img_bytes, B, w, h, w,
+                                  img_bytes, temporal)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- value: inputs resident in HBM ----------------
+    for k in range(args.warmup):
+        step_device(k)
+    hd.sync()
+    hd.profile_enable(True)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = hd.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for k in range(args.steps):
+        step_device(args.warmup + k)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = hd.launch_count - l0
+    prof = hd.profile_read()
+    hd.profile_enable(False)
+    tms = torch.tensor([ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max = float(tms.item())
+    value = world * B * args.steps / (ms_max * 1e-3)
+
+    # ---------------- e2e: host buffers through the C ABI, copies inside ----------------
+    nh = 2
+    Be = max(B // 2, 1)
+    handles = [fe.Handle(*cfg, w, h, max_images=2 * Be, device=local) for _ in range(nh)]
+    pin_l = fe.pinned_empty(ls.shape); pin_l[...] = ls
+    pin_r = fe.pinned_empty(rs.shape); pin_r[...] = rs
+    outs = [hh.alloc_stereo_out(Be, pinned=True) for hh in handles]
+    cap = handles[0].keypoint_capacity
+    d2h_per_pair = 2 * cap * (28 + 32) + 6 * cap * 4 + 4 * 4
+    e2e_steps = max(args.steps // 2, 4)
+    counts = []
+
+    def worker(i, nsteps, record):
+        hh, out = handles[i], outs[i]
+        for k in range(nsteps):
+            off = ((2 * k + i) * 37) % (pool - Be + 1)
+            hh.L.b2orb_stereo_frontend(hh.h, pin_l[off:].ctypes.data, pin_r[off:].ctypes.data, Be, w, h, w, img_bytes,
+                                       1 if temporal else 0, out[1])
+            if record:
+                counts.append((int(out[0]["n_l"].sum()), int(out[0]["n_match"].sum()), int(out[0]["n_circ"].sum())))
+
+    def run_e2e(nsteps, record):
+        ts = [threading.Thread(target=worker, args=(i, nsteps, record)) for i in range(nh)]
+        for t in ts: t.start()
+        for t in ts: t.join()
+
+    run_e2e(2, False)
+    barrier()
+    t0 = time.perf_counter()
+    run_e2e(e2e_steps, True)
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    te = torch.tensor([t_e2e], device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * nh * Be * e2e_steps / float(te.item())
+    clocks = sampler.stop() if sampler else None
+
+    # per-GPU result summaries are the only thing gathered (north star: no collective on the hot path)
+    summ = torch.tensor([sum(c[0] for c in counts), sum(c[1] for c in counts), sum(c[2] for c in counts)], device="cuda")
+    if world > 1:
+        gathered = [torch.zeros_like(summ) for _ in range(world)]
+        dist.all_gather(gathered, summ)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---------------- roofline of the dominant kernel ----------------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    b_pair, per_kernel = algorithmic_bytes(level_sizes(w, h), nfeat, temporal)
+    tot_ms = sum(v[0] for v in prof.values())
+    dom = max(prof, key=lambda k: prof[k][0])
+    shares = {k: round(v[0] / tot_ms, 4) for k, v in prof.items() if v[1]}
+    dom_ms_per_launch = prof[dom][0] / max(prof[dom][1], 1)
+    launches_per_step = prof[dom][1] / args.steps
+    # per_kernel is bytes per PAIR (both eyes); one step covers B pairs in `launches_per_step` launches of that kernel
+    dom_bytes = per_kernel.get(dom, 0) * B / max(launches_per_step, 1)
+    achieved = dom_bytes / (dom_ms_per_launch * 1e-3) / 1e9 if dom_ms_per_launch > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic", "config": config,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * img_bytes * Be, "d2h_bytes_per_step": d2h_per_pair * Be,
+                "pairs_per_call": Be, "host_threads": nh, "steps": e2e_steps * nh},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms_per_launch,
+                     "kernel_time_shares": shares},
+        "pipeline": {"algorithmic_bytes_per_pair": b_pair, "achieved_gbs": b_pair * value / world / 1e9,
+                     "frac_of_hbm_peak": b_pair * value / world / 1e9 / peak},
+        "results": {"keypoints_left": int(summ[0]), "stereo_matches": int(summ[1]), "circular_matches": int(summ[2])},
+    }
+    if not args.no_cpu_baseline and world >= 1:
+        from oracle import oracle as orc
+        workers = os.cpu_count() or 1
+        v, n, dt = cpu_baseline(synth, orc, args.workload, cfg, temporal, workers, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": workers, "kind": "port",
+                                "sample": f"{n} pairs of the same workload in {dt:.1f} s, pairs sharded over {workers} host threads"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -155,6 +155,19 @@ int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8
  * relative to the 16-px border (unordered).  Returns the count through *n. */
 int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* dst, int cap, int* n);
 
+/* The handle's CUDA stream (a cudaStream_t) so callers can record their own events on it. */
+void* b2orb_stream(const b2orb_handle* h);
+
+/* Per-kernel device timing: when enabled, CUDA events are recorded on the handle's stream between
+ * launches (no extra synchronisation); b2orb_profile_read() synchronises, then returns the
+ * accumulated milliseconds and launch counts per kernel id since b2orb_profile_enable(h, 1). */
+enum {
+    B2ORB_K_RESIZE = 0, B2ORB_K_FAST, B2ORB_K_OCTREE, B2ORB_K_BLUR, B2ORB_K_DESCRIBE, B2ORB_K_MATCH_STEREO,
+    B2ORB_K_STEREO_FILTER, B2ORB_K_MATCH_TEMPORAL, B2ORB_K_CIRCULAR, B2ORB_NUM_KERNELS
+};
+void b2orb_profile_enable(b2orb_handle* h, int on);
+int b2orb_profile_read(b2orb_handle* h, double* ms /*[B2ORB_NUM_KERNELS]*/, uint64_t* launches /*[B2ORB_NUM_KERNELS]*/);
+
 /* Kernel launches issued by this handle since creation (bench.py reports the per-step delta). */
 uint64_t b2orb_launch_count(const b2orb_handle* h);
 /* Device time (ms, CUDA events on the handle's stream) of the last *_device / frontend call. */

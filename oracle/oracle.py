@@ -73,7 +73,7 @@ def lib():
                                       C.c_int, vp, vp, vp, vp, C.c_int, i32p, i32p, vp, vp, vp, vp]
         L.orc_run_pairs.restype = C.c_long
         L.orc_run_pairs.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int,
-                                    C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
+                                    C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int]
         _lib = L
     return _lib
 
@@ -199,9 +199,9 @@ def threshold_filter(train_idx, dist, nt, ratio, min_match_dist):
     return o_q[:m].copy(), o_t[:m].copy()
 
 
-def run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads):
+def run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads, temporal=False):
     """CPU baseline driver: cfg = (nfeatures, scaleFactor, nlevels, iniTh, minTh); imgs_* = (P,H,W) u8."""
     imgs_l = np.ascontiguousarray(imgs_l, np.uint8); imgs_r = np.ascontiguousarray(imgs_r, np.uint8)
     p, h, w = imgs_l.shape
     return lib().orc_run_pairs(cfg[0], cfg[1], cfg[2], cfg[3], cfg[4], _p(imgs_l), _p(imgs_r), p, w, h,
-                               ratio, min_match_dist, max_dy, workers, per_pair_threads)
+                               ratio, min_match_dist, max_dy, workers, per_pair_threads, 1 if temporal else 0)

@@ -67,6 +67,13 @@ struct b2orb_handle {
     int *d_gidx = nullptr, *d_gdist = nullptr, *d_gidx2 = nullptr, *d_gdist2 = nullptr, *d_gcnt = nullptr;
     int g_cap_q = 0, g_cap_t = 0;
     int bound_np = -1;                                   // batch size the problem table is bound to
+    // optional per-kernel timing (b2orb_profile_*): events recorded between launches on the handle's stream
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_ev;                    // pool
+    std::vector<int> prof_tag;                           // tag of the launch that FOLLOWS event i (-1 = none)
+    size_t prof_used = 0;
+    double prof_ms[B2ORB_NUM_KERNELS] = {};
+    uint64_t prof_cnt[B2ORB_NUM_KERNELS] = {};
     std::vector<void*> owned;
 };
 
@@ -87,6 +94,19 @@ bool cuda_ok(b2orb_handle* h, cudaError_t e, const char* what) {
 int fail(b2orb_handle* h, int code, const char* msg) {
     if (h) h->err = msg;
     return code;
+}
+
+// Profiling marker: an event before the launch tagged `tag`; prof_end() closes the last interval.
+void prof_mark(b2orb_handle* h, int tag) {
+    if (!h->profiling) return;
+    if (h->prof_used == h->prof_ev.size()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        h->prof_ev.push_back(e);
+        h->prof_tag.push_back(-1);
+    }
+    h->prof_tag[h->prof_used] = tag;
+    cudaEventRecord(h->prof_ev[h->prof_used++], h->stream);
 }
 
 template <class T>
@@ -324,17 +344,24 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     const B2Geom& g = h->geom;
     cudaStream_t s = h->stream;
     for (int l = 1; l < g.nlevels; ++l) {
+        prof_mark(h, B2ORB_K_RESIZE);
         b2_launch_resize(g, im, l, h->d_xofs[l], h->d_xw[l], h->d_yofs[l], h->d_yw[l], nimg, s);
         ++h->launches;
     }
+    prof_mark(h, -1);
     B2_CUDA(h, cudaMemsetAsync(h->d_cand_cnt, 0, (size_t)nimg * g.nlevels * sizeof(int), s));
+    prof_mark(h, B2ORB_K_FAST);
     if (g.total_cells > 0) { b2_launch_fast(g, im, h->d_cand, h->d_cand_cnt, nimg, s); ++h->launches; }
+    prof_mark(h, B2ORB_K_OCTREE);
     b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
     ++h->launches;
+    prof_mark(h, B2ORB_K_BLUR);
     b2_launch_blur(g, im, nimg, s);
     ++h->launches;
+    prof_mark(h, B2ORB_K_DESCRIBE);
     b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
     ++h->launches;
+    prof_mark(h, -1);
     B2_CUDA(h, cudaGetLastError());
     return B2ORB_OK;
 }
@@ -371,20 +398,26 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
     if (rc) return rc;
     rc = bind_problems(h, np);   // small H2D; table depends on np only
     if (rc) return rc;
+    prof_mark(h, B2ORB_K_MATCH_STEREO);
     b2_launch_match(h->d_probs, np, g.kp_cap, s);
     ++h->launches;
+    prof_mark(h, B2ORB_K_STEREO_FILTER);
     b2_launch_stereo_filter(h->d_kps, h->d_desc, h->d_nkp, h->d_train, h->d_dist, g.kp_cap, h->cfg.match_ratio,
                             h->cfg.min_match_dist, h->cfg.max_vertical_pixel_dist, h->d_match_l, h->d_match_r,
                             h->d_nmatch + 1, h->d_cur_l + (size_t)g.kp_cap * 32, h->d_cur_r + (size_t)g.kp_cap * 32, np,
                             s);
     ++h->launches;
+    prof_mark(h, -1);
     if (temporal) {
+        prof_mark(h, B2ORB_K_MATCH_TEMPORAL);
         b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
         ++h->launches;
+        prof_mark(h, B2ORB_K_CIRCULAR);
         b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, h->d_nmatch, g.kp_cap,
                            h->cfg.match_ratio, h->cfg.min_match_dist, h->d_circ_cur, h->d_circ_hist, h->d_ncirc,
                            h->d_nleft, h->d_nright, np, s);
         ++h->launches;
+        prof_mark(h, -1);
         // the last pair of this call becomes the history of the next call (slot 0)
         const size_t row = (size_t)g.kp_cap * 32;
         B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, h->d_cur_l + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
@@ -431,6 +464,7 @@ void b2orb_destroy(b2orb_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_workspace(h);
+    for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -690,6 +724,34 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
         B2_CUDA(h, cudaMemcpyAsync(circ_hist, d_ch, (size_t)out[0] * 4, cudaMemcpyDeviceToHost, s));
         B2_CUDA(h, cudaStreamSynchronize(s));
     }
+    return B2ORB_OK;
+}
+
+// ---- stream + per-kernel timing ------------------------------------------------------------------
+void* b2orb_stream(const b2orb_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+void b2orb_profile_enable(b2orb_handle* h, int on) {
+    if (!h) return;
+    h->profiling = on != 0;
+    h->prof_used = 0;
+    for (int k = 0; k < B2ORB_NUM_KERNELS; ++k) { h->prof_ms[k] = 0; h->prof_cnt[k] = 0; }
+}
+
+int b2orb_profile_read(b2orb_handle* h, double* ms, uint64_t* launches) {
+    if (!h || !ms || !launches) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (size_t i = 0; i + 1 < h->prof_used; ++i) {
+        const int tag = h->prof_tag[i];
+        if (tag < 0) continue;
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, h->prof_ev[i], h->prof_ev[i + 1]) == cudaSuccess) {
+            h->prof_ms[tag] += t;
+            h->prof_cnt[tag] += 1;
+        }
+    }
+    h->prof_used = 0;
+    for (int k = 0; k < B2ORB_NUM_KERNELS; ++k) { ms[k] = h->prof_ms[k]; launches[k] = h->prof_cnt[k]; }
     return B2ORB_OK;
 }
 

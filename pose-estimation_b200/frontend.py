@@ -22,6 +22,8 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 
 OK, ERR_INVALID, ERR_CAPACITY, ERR_CUDA, ERR_NOMEM = 0, 1, 2, 3, 4
+KERNEL_NAMES = ("resize", "fast", "octree", "blur", "describe", "match_stereo", "stereo_filter", "match_temporal",
+                "circular")
 
 
 class B2Config(C.Structure):
@@ -92,6 +94,11 @@ def lib():
         L.b2orb_debug_get_level.argtypes = [vp, i32, i32, i32, vp]
         L.b2orb_debug_get_candidates.restype = i32
         L.b2orb_debug_get_candidates.argtypes = [vp, i32, i32, vp, i32, C.POINTER(i32)]
+        L.b2orb_stream.restype = vp
+        L.b2orb_stream.argtypes = [vp]
+        L.b2orb_profile_enable.argtypes = [vp, i32]
+        L.b2orb_profile_read.restype = i32
+        L.b2orb_profile_read.argtypes = [vp, vp, vp]
         L.b2orb_launch_count.restype = C.c_uint64
         L.b2orb_launch_count.argtypes = [vp]
         L.b2orb_last_device_ms.restype = f32
@@ -173,6 +180,18 @@ class Handle:
     @property
     def last_device_ms(self):
         return float(self.L.b2orb_last_device_ms(self.h))
+
+    @property
+    def stream(self):
+        return self.L.b2orb_stream(self.h)
+
+    def profile_enable(self, on=True):
+        self.L.b2orb_profile_enable(self.h, 1 if on else 0)
+
+    def profile_read(self):
+        ms = np.zeros(len(KERNEL_NAMES), np.float64); cnt = np.zeros(len(KERNEL_NAMES), np.uint64)
+        self.check(self.L.b2orb_profile_read(self.h, _p(ms), _p(cnt)))
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(KERNEL_NAMES)}
 
     def tables(self):
         nl = self.nlevels
