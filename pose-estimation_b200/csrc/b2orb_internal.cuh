@@ -6,6 +6,8 @@
 #define B2_MAX_LEVELS 12
 #define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
 #define B2_BORDER 16        // EDGE_THRESHOLD-3 = minBorderX/Y, src/ORBextractor.cc:773-776
+#define B2_FAST_BAND 32     // corner-map rows per FAST score task (fast.cu)
+#define B2_BLUR_BAND 32     // output rows per blur task (blur.cu)
 #define B2_HALF_PATCH 15    // HALF_PATCH_SIZE, src/ORBextractor.cc:73
 
 // Per-level geometry, fixed for (config, image size).  Passed to kernels BY VALUE as one
@@ -16,8 +18,10 @@ struct B2Level {
     int n_cols, n_rows;       // FAST cell grid (src/ORBextractor.cc:784-787)
     int w_cell, h_cell;
     int cell_base;            // first flattened cell index of this level
-    int blur_tile_base;       // first flattened blur tile of this level
-    int blur_tiles_x;
+    int fast_task_base;       // first flattened FAST score task (band, strip) of this level
+    int fast_strips;          // 112-px strips per row band (fast.cu)
+    int blur_task_base;       // first flattened blur task (band, strip) of this level
+    int blur_strips;          // 128-px strips per row band
     int quota;                // mnFeaturesPerLevel[level]
     int sel_base;             // first slot of this level in the per-image selected-keypoint array
     int sel_cap;              // quota + 4
@@ -35,7 +39,8 @@ struct B2Geom {
     int nlevels;
     int ini_th, min_th;
     int total_cells;          // over all levels
-    int total_blur_tiles;
+    int total_blur_tasks;
+    int total_fast_tasks;
     int sel_total;            // per-image selected-keypoint slots (sum of sel_cap)
     int kp_cap;               // per-image output capacity
     unsigned cand_total;      // per-image candidate slots
@@ -43,6 +48,7 @@ struct B2Geom {
     unsigned slab;            // bytes of one image's pyramid (levels 1..) / blur (levels 0..) slab
     int umax[16];             // src/ORBextractor.cc:454-469
     int taps[7];
+    unsigned tapv[10];        // blur.cu: u8x4 tap vectors for the 4 output pixels of a lane (host-built)
     B2Level lv[B2_MAX_LEVELS];
 };
 
@@ -87,7 +93,8 @@ struct B2MatchProblem {
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);
-void b2_launch_fast(const B2Geom& g, const B2Images& im, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s);
+void b2_launch_fast(const B2Geom& g, const B2Images& im, uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg,
+                    cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
                       B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,

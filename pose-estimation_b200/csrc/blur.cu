@@ -1,71 +1,170 @@
 // 7x7 Gaussian blur of every pyramid level — GaussianBlur(workingMat, workingMat, Size(7,7), 2, 2,
 // BORDER_REFLECT_101), src/ORBextractor.cc:1085-1086 (K6).  OpenCV's 8-bit fixed-point path: separable
-// integer taps (sum 256); horizontal pass exact in Q8 (<= 65280, u16), vertical pass accumulates in Q16 and
-// rounds with (acc + 32768) >> 16.  One launch covers all levels of all images: blockIdx.x walks a
-// flattened (level, tile) list, blockIdx.y is the image.
+// integer taps (sum 256); horizontal pass exact in Q8 (<= 65280), vertical pass accumulates in Q16 and
+// rounds with (acc + 32768) >> 16.  Both passes are exact integer sums with ONE rounding at the end, so any
+// evaluation order is bit-identical.
+//
+// The kernel is instruction-issue bound, not HBM bound, so it is organised around instructions per pixel:
+// one WARP owns a 128-px wide strip (4 px per lane) and marches down a band of rows.  Per input row a lane
+// does one 32-bit load, gets its left/right neighbour words by shuffle, and computes the 4 horizontal sums
+// with 10 IDP.4A (u8x4 dot products against shifted tap vectors — no byte unpacking at all).  The vertical
+// pass keeps the last 7 horizontal rows in registers (7-phase unrolled rotation) and uses tap symmetry:
+// 3 IADD + 4 IMAD per pixel, which also balances the ALU and FMA pipes.  Results are packed with 3 PRMT and
+// stored as one 32-bit word.  Rows are prefetched BL_PF deep in registers.  Image borders (reflect-101) are
+// folded into per-lane PRMT selectors computed once per strip; interior strips skip that code entirely.
+// One launch covers all levels of all images: blockIdx.x walks a flattened (level, band, strip) task list.
 #include "b2orb_internal.cuh"
 
 namespace {
 
-constexpr int BT_W = 64, BT_H = 16, BT_THREADS = 256;
-constexpr int IN_W = BT_W + 6, IN_H = BT_H + 6, IN_P = 72;
+constexpr int BL_WARPS = 4;                 // independent warp tasks per CTA
+constexpr int BL_PF = 5;                    // rows in flight per warp (register ring of 7)
 
-__device__ __forceinline__ int reflect101(int i, int n) {
-    // BORDER_REFLECT_101: -i -> i, (n-1)+i -> (n-1)-i; loops only for images narrower than the halo
-    while (i < 0 || i >= n) i = (i < 0) ? -i : 2 * (n - 1) - i;
-    return i;
+__device__ __forceinline__ int reflect101_once(int i, int n) {
+    // BORDER_REFLECT_101: -i -> i, (n-1)+i -> (n-1)-i.  One bounce is exact for n >= 4 (halo is 3); smaller
+    // levels never carry keypoints, there the clamp only keeps the access in bounds.
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * (n - 1) - i;
+    return min(max(i, 0), n - 1);
 }
 
-__global__ void __launch_bounds__(BT_THREADS)
+template <bool EDGE>
+__device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int spitch, uint8_t* __restrict__ dst,
+                                          int dpitch, int w, int h, int x, int y0, int rows, int lane, bool first_strip,
+                                          const B2Geom& g) {
+    // ---- per-lane load plan -------------------------------------------------------------------
+    const int wpitch = spitch;                                 // rows are readable up to the pitch
+    const int xo = min(x, wpitch - 4);                         // own word (clamped: lanes right of the row)
+    // lane 0 fetches the word left of the strip, lane 31 the word right of it
+    int xe = -1;
+    if (lane == 0 && !first_strip) xe = x - 4;
+    if (lane == 31) xe = min(x + 4, wpitch - 4);
+
+    // ---- border selectors (EDGE strips only) --------------------------------------------------
+    // Column c = x-4+j (j = 0..11) must read reflect101(c).  Needed columns always resolve inside the lane's
+    // own three raw words (R0 | R1 | R2 = columns x-4 .. x+7); W0 and W1 pick from (R0,R1) or (R1,R2).
+    unsigned s0 = 0x3210, s1 = 0x7654, s2 = 0x7654;
+    bool w0_hi = false, w2_lo = false;                         // W0 from (R1,R2) / W2 from (R0,R1) instead
+    if (EDGE) {
+        int idx[12];
+#pragma unroll
+        for (int j = 0; j < 12; ++j) {
+            const int c = x - 4 + j;
+            int rc = c;
+            if (c < 0) rc = -c;
+            if (c >= w) rc = 2 * (w - 1) - c;
+            rc = min(max(rc, 0), w - 1);
+            int k = rc - (x - 4);                              // position inside R0|R1|R2
+            idx[j] = min(max(k, 0), 11);                       // out of reach == never needed for a valid output
+        }
+        // W0: columns j = 0..3
+        w0_hi = idx[1] >= 4 || idx[2] >= 4 || idx[3] >= 4;     // left image edge: sources are in R1 (and R2)
+        s0 = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int k = w0_hi ? idx[j] - 4 : idx[j];
+            s0 |= (unsigned)min(max(k, 0), 7) << (4 * j);
+        }
+        // W1: columns j = 4..7 from (R0,R1)
+        s1 = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s1 |= (unsigned)min(idx[4 + j], 7) << (4 * j);
+        // W2: columns j = 8..11 from (R1,R2) unless a needed source lies in R0
+        w2_lo = idx[8] < 4 || idx[9] < 4 || idx[10] < 4;
+        s2 = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int k = w2_lo ? idx[8 + j] : idx[8 + j] - 4;
+            s2 |= (unsigned)min(max(k, 0), 7) << (4 * j);
+        }
+    }
+
+    // ---- row pipeline -------------------------------------------------------------------------
+    const int nsteps = rows + 6;
+    unsigned raw[7], rex[7];
+    int hw[7][4];
+#pragma unroll
+    for (int i = 0; i < BL_PF; ++i) {
+        if (i < nsteps) {
+            const uint8_t* rp = src + (size_t)reflect101_once(y0 - 3 + i, h) * spitch;
+            raw[i] = *reinterpret_cast<const unsigned*>(rp + xo);
+            rex[i] = xe >= 0 ? *reinterpret_cast<const unsigned*>(rp + xe) : 0u;
+        }
+    }
+    for (int base = 0; base < nsteps; base += 7) {
+#pragma unroll
+        for (int p = 0; p < 7; ++p) {
+            const int r = base + p;
+            if (r < nsteps) {
+                // prefetch row r + BL_PF into ring slot (p + BL_PF) % 7
+                if (r + BL_PF < nsteps) {
+                    const uint8_t* rp = src + (size_t)reflect101_once(y0 - 3 + r + BL_PF, h) * spitch;
+                    raw[(p + BL_PF) % 7] = *reinterpret_cast<const unsigned*>(rp + xo);
+                    rex[(p + BL_PF) % 7] = xe >= 0 ? *reinterpret_cast<const unsigned*>(rp + xe) : 0u;
+                }
+                const unsigned R1 = raw[p];
+                unsigned R0 = __shfl_up_sync(0xFFFFFFFFu, R1, 1);
+                unsigned R2 = __shfl_down_sync(0xFFFFFFFFu, R1, 1);
+                if (lane == 0) R0 = rex[p];
+                if (lane == 31) R2 = rex[p];
+                unsigned W0 = R0, W1 = R1, W2 = R2;
+                if (EDGE) {
+                    W0 = __byte_perm(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
+                    W1 = __byte_perm(R0, R1, s1);
+                    W2 = __byte_perm(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
+                }
+                // horizontal pass: 4 pixels, 10 dot products
+                hw[p][0] = __dp4a(W1, g.tapv[1], __dp4a(W0, g.tapv[0], 0u));
+                hw[p][1] = __dp4a(W2, g.tapv[4], __dp4a(W1, g.tapv[3], __dp4a(W0, g.tapv[2], 0u)));
+                hw[p][2] = __dp4a(W2, g.tapv[7], __dp4a(W1, g.tapv[6], __dp4a(W0, g.tapv[5], 0u)));
+                hw[p][3] = __dp4a(W2, g.tapv[9], __dp4a(W1, g.tapv[8], 0u));
+                if (r >= 6) {
+                    // vertical pass for output row y0 + r - 6 (window rows r-6 .. r, centre r-3)
+                    unsigned o[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int e0 = hw[p][j] + hw[(p + 1) % 7][j];
+                        const int e1 = hw[(p + 6) % 7][j] + hw[(p + 2) % 7][j];
+                        const int e2 = hw[(p + 5) % 7][j] + hw[(p + 3) % 7][j];
+                        o[j] = (unsigned)(g.taps[0] * e0 + g.taps[1] * e1 + g.taps[2] * e2 + g.taps[3] * hw[(p + 4) % 7][j] + 32768);
+                    }
+                    // bits 16..23 of each accumulator are the result (taps sum to 256 -> never above 255)
+                    const unsigned lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
+                    const unsigned packed = __byte_perm(lo, hi, 0x5410);
+                    if (x < w) *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * dpitch + x) = packed;
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(BL_WARPS * 32)
 blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
-    __shared__ uint8_t s_in[IN_H][IN_P];
-    __shared__ uint16_t s_h[IN_H][BT_W];
+    const int lane = threadIdx.x & 31;
+    const int task = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    if (task >= g.total_blur_tasks) return;
     const int b = blockIdx.y;
     int level = 0;
-    while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].blur_tile_base) ++level;
+    while (level + 1 < g.nlevels && task >= g.lv[level + 1].blur_task_base) ++level;
     const B2Level& L = g.lv[level];
-    const int t = blockIdx.x - L.blur_tile_base;
-    const int x0 = (t % L.blur_tiles_x) * BT_W, y0 = (t / L.blur_tiles_x) * BT_H;
+    const int t = task - L.blur_task_base;
+    const int band = t / L.blur_strips, strip = t - band * L.blur_strips;
     int spitch;
     const uint8_t* src = b2_level_ptr(g, im, b, level, spitch);
-    const int w = L.w, h = L.h;
-    const int tid = threadIdx.x;
+    uint8_t* dst = im.blur + (size_t)b * g.slab + L.off;
+    const int x = strip * 128 + lane * 4;
+    const int y0 = band * B2_BLUR_BAND;
+    const int rows = min(B2_BLUR_BAND, L.h - y0);
 
-    for (int i = tid; i < IN_H * IN_W; i += BT_THREADS) {
-        const int r = i / IN_W, c = i - r * IN_W;
-        const int yy = (h == 1) ? 0 : reflect101(y0 + r - 3, h);
-        const int xx = (w == 1) ? 0 : reflect101(x0 + c - 3, w);
-        s_in[r][c] = src[(size_t)yy * spitch + xx];
-    }
-    __syncthreads();
-    const int k0 = g.taps[0], k1 = g.taps[1], k2 = g.taps[2], k3 = g.taps[3], k4 = g.taps[4], k5 = g.taps[5],
-              k6 = g.taps[6];
-    for (int i = tid; i < IN_H * BT_W; i += BT_THREADS) {
-        const int r = i / BT_W, c = i - r * BT_W;
-        const uint8_t* p = &s_in[r][c];
-        s_h[r][c] = (uint16_t)(k0 * p[0] + k1 * p[1] + k2 * p[2] + k3 * p[3] + k4 * p[4] + k5 * p[5] + k6 * p[6]);
-    }
-    __syncthreads();
-    const int r = tid / (BT_W / 4), c0 = (tid % (BT_W / 4)) * 4;
-    const int y = y0 + r, x = x0 + c0;
-    if (y < h && x < w) {
-        uint32_t packed = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int c = c0 + k;
-            unsigned acc = k0 * s_h[r][c] + k1 * s_h[r + 1][c] + k2 * s_h[r + 2][c] + k3 * s_h[r + 3][c] +
-                           k4 * s_h[r + 4][c] + k5 * s_h[r + 5][c] + k6 * s_h[r + 6][c];
-            unsigned v = min((acc + 32768u) >> 16, 255u);
-            packed |= v << (8 * k);
-        }
-        uint8_t* dst = im.blur + (size_t)b * g.slab + L.off + (size_t)y * L.pitch + x;
-        *reinterpret_cast<uint32_t*>(dst) = packed;  // pitch padding absorbs the tail
-    }
+    // a strip needs the border code if it touches column 0 or its last lane's halo reaches beyond w-1
+    const bool edge = strip == 0 || strip * 128 + 128 + 3 > L.w - 1;
+    if (edge) blur_task<true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, strip == 0, g);
+    else blur_task<false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, false, g);
 }
 
 }  // namespace
 
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s) {
-    dim3 grid(g.total_blur_tiles, nimg);
-    blur_kernel<<<grid, BT_THREADS, 0, s>>>(g, im);
+    dim3 grid((g.total_blur_tasks + BL_WARPS - 1) / BL_WARPS, nimg);
+    blur_kernel<<<grid, BL_WARPS * 32, 0, s>>>(g, im);
 }

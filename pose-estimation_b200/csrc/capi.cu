@@ -4,6 +4,7 @@
 // Host C++ only orchestrates; all pixel/descriptor work is in the .cu kernels next to this file.
 #include <cmath>
 #include <cstdio>
+#include <cstdint>
 #include <cstring>
 #include <new>
 #include <string>
@@ -17,7 +18,6 @@ namespace {
 inline int cv_round_f(float v) { return (int)lrintf(v); }   // cvRound: round-half-even
 inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
 
-constexpr int kBlurTileW = 64, kBlurTileH = 16;   // must match blur.cu
 
 struct DevBuf {
     void* p = nullptr;
@@ -48,8 +48,9 @@ struct b2orb_handle {
 
     // workspace (sized for cfg.max_images images of the current size)
     int nimg_cap = 0, npair_cap = 0;
-    uint8_t *d_stage = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+    uint8_t *d_stage = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
     size_t stage_img_bytes = 0;
+    int stage_pitch = 0;                                 // level-0 rows in the staging area: 32-byte aligned pitch
     uint32_t* d_cand = nullptr;
     unsigned short* d_pnode = nullptr;
     int *d_cand_cnt = nullptr, *d_sel_cnt = nullptr, *d_nkp = nullptr;
@@ -194,8 +195,15 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     bool zero = true;
     for (int i = 0; i < 7; ++i) zero = zero && c.blur_taps[i] == 0;
     for (int i = 0; i < 7; ++i) g.taps[i] = zero ? def_taps[i] : c.blur_taps[i];
+    {   // blur.cu: output pixel j of a lane sees columns x+j-3 .. x+j+3 of the words W0|W1|W2 = columns x-4 .. x+7
+        const int k0 = g.taps[0], k1 = g.taps[1], k2 = g.taps[2], k3 = g.taps[3];
+        auto tv = [](int a, int b, int c2, int d) { return (unsigned)a | ((unsigned)b << 8) | ((unsigned)c2 << 16) | ((unsigned)d << 24); };
+        const unsigned v[10] = {tv(0, k0, k1, k2), tv(k3, k2, k1, k0), tv(0, 0, k0, k1), tv(k2, k3, k2, k1), tv(k0, 0, 0, 0),
+                                tv(0, 0, 0, k0), tv(k1, k2, k3, k2), tv(k1, k0, 0, 0), tv(k0, k1, k2, k3), tv(k2, k1, k0, 0)};
+        memcpy(g.tapv, v, sizeof v);
+    }
     unsigned off = 0, cand_off = 0, node_off = 0;
-    int cells = 0, tiles = 0, sel = 0;
+    int cells = 0, tiles = 0, sel = 0, ftasks = 0;
     for (int l = 0; l < c.nlevels; ++l) {
         B2Level& L = g.lv[l];
         // ComputePyramid :1111-1112: Size(cvRound((float)cols*scale), cvRound((float)rows*scale))
@@ -205,9 +213,9 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         L.pitch = (int)align_up((unsigned)L.w, 32);
         L.off = off;
         off += align_up((unsigned)L.pitch * (unsigned)L.h, 256);
-        L.blur_tiles_x = (L.w + kBlurTileW - 1) / kBlurTileW;
-        L.blur_tile_base = tiles;
-        tiles += L.blur_tiles_x * ((L.h + kBlurTileH - 1) / kBlurTileH);
+        L.blur_strips = (L.w + 127) / 128;
+        L.blur_task_base = tiles;
+        tiles += L.blur_strips * ((L.h + B2_BLUR_BAND - 1) / B2_BLUR_BAND);
         L.quota = h->quota[l];
         L.scale = h->scale[l];
         L.kp_size = (float)(int)(31 * h->scale[l]);     // :836 `const int scaledPatchSize = PATCH_SIZE*mvScaleFactor[level]`
@@ -216,6 +224,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
         const int n_cols = width > 0 ? (int)(width / 30.f) : 0, n_rows = height > 0 ? (int)(height / 30.f) : 0;
         L.cell_base = cells;
+        L.fast_task_base = ftasks;   // levels without cells own zero tasks but must keep the list monotonic
         L.n_ini = 1;
         L.h_x = 1.f;
         if (n_cols >= 1 && n_rows >= 1) {   // else: the reference divides by zero; the level yields no keypoints
@@ -226,10 +235,13 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
             if (L.w_cell > 64 || L.h_cell > 64) return "FAST cell larger than 64 px";
             if ((long long)n_cols * n_rows * L.w_cell * L.h_cell >= (1 << 24)) return "level too large for 24-bit order keys";
             cells += n_cols * n_rows;
+            L.fast_strips = (L.w - 2 * B2_BORDER + 111) / 112;
+            ftasks += L.fast_strips * ((L.h - 2 * B2_EDGE + B2_FAST_BAND - 1) / B2_FAST_BAND);
             // DistributeOctTree :543-545
             L.n_ini = (int)std::round((float)(maxBX - minB) / (maxBY - minB));
             if (L.n_ini < 1) {   // taller than 2:1 -> the reference divides by zero; no keypoints
                 L.n_ini = 1; L.n_cols = L.n_rows = 0; cells -= n_cols * n_rows;
+                ftasks = L.fast_task_base; L.fast_strips = 0;
             } else if (L.n_ini > 256) return "aspect ratio above 256:1";
             L.h_x = (float)(maxBX - minB) / L.n_ini;
         }
@@ -246,7 +258,8 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     }
     if (w > 4096 + B2_BORDER || hgt > 4096 + B2_BORDER) return "image larger than 4096 px";
     g.total_cells = cells;
-    g.total_blur_tiles = tiles;
+    g.total_blur_tasks = tiles;
+    g.total_fast_tasks = ftasks;
     g.sel_total = sel;
     g.kp_cap = sel;
     g.cand_total = cand_off;
@@ -287,10 +300,12 @@ int configure(b2orb_handle* h, int w, int hgt) {
         B2_CUDA(h, cudaMemcpyAsync(h->d_yw[l], yw.data(), yw.size() * 2, cudaMemcpyHostToDevice, h->stream));
         B2_CUDA(h, cudaStreamSynchronize(h->stream));   // host vectors die at scope end
     }
-    h->stage_img_bytes = (size_t)w * hgt;
+    h->stage_pitch = (int)align_up((unsigned)w, 32);
+    h->stage_img_bytes = (size_t)h->stage_pitch * hgt;
     const size_t cap = g.kp_cap;
     bool ok = dev_alloc(h, &h->d_stage, (size_t)nimg * h->stage_img_bytes) &&
               dev_alloc(h, &h->d_pyr, (size_t)nimg * g.slab) && dev_alloc(h, &h->d_blur, (size_t)nimg * g.slab) &&
+              dev_alloc(h, &h->d_score, (size_t)nimg * g.slab) &&
               dev_alloc(h, &h->d_cand, (size_t)nimg * g.cand_total) &&
               dev_alloc(h, &h->d_pnode, (size_t)nimg * g.cand_total) &&
               dev_alloc(h, &h->d_cand_cnt, (size_t)nimg * nl) && dev_alloc(h, &h->d_sel_cnt, (size_t)nimg * nl) &&
@@ -351,7 +366,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     prof_mark(h, -1);
     B2_CUDA(h, cudaMemsetAsync(h->d_cand_cnt, 0, (size_t)nimg * g.nlevels * sizeof(int), s));
     prof_mark(h, B2ORB_K_FAST);
-    if (g.total_cells > 0) { b2_launch_fast(g, im, h->d_cand, h->d_cand_cnt, nimg, s); ++h->launches; }
+    if (g.total_cells > 0) { b2_launch_fast(g, im, h->d_score, h->d_cand, h->d_cand_cnt, nimg, s); h->launches += 2; }
     prof_mark(h, B2ORB_K_OCTREE);
     b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
     ++h->launches;
@@ -378,15 +393,17 @@ B2Images make_images(b2orb_handle* h, const uint8_t* a, const uint8_t* b, int sp
     return im;
 }
 
-// Host images -> tight staging area (slot order), one copy when the source is tight too.
-int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0) {
+// Host (or device) images -> staging area with an aligned row pitch (kernels read level 0 with 32-bit / 128-bit
+// accesses).  Contiguous batches go as ONE 2-D copy.
+int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
+           cudaMemcpyKind kind = cudaMemcpyHostToDevice) {
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
-    if (step == w && image_stride == (size_t)w * hgt) {
-        B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, h->stream));
+    if (image_stride == (size_t)step * hgt) {
+        B2_CUDA(h, cudaMemcpy2DAsync(dst, h->stage_pitch, src, step, w, (size_t)count * hgt, kind, h->stream));
     } else {
         for (int i = 0; i < count; ++i)
-            B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, w, src + i * image_stride, step, w, hgt,
-                                         cudaMemcpyHostToDevice, h->stream));
+            B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, h->stage_pitch, src + i * image_stride, step, w,
+                                         hgt, kind, h->stream));
     }
     return B2ORB_OK;
 }
@@ -444,6 +461,15 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
         cfg->ini_th_fast < 1 || cfg->min_th_fast < 1 || cfg->min_th_fast > cfg->ini_th_fast ||
         cfg->ini_th_fast > 254 || cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_images < 1)
         return B2ORB_ERR_INVALID;
+    {   // blur taps: all zero (default) or a symmetric u8 kernel with sum 256 (exact Q8 x Q8 arithmetic, blur.cu)
+        int sum = 0; bool zero = true, ok = true;
+        for (int i = 0; i < 7; ++i) {
+            zero = zero && cfg->blur_taps[i] == 0;
+            ok = ok && cfg->blur_taps[i] >= 0 && cfg->blur_taps[i] <= 255 && cfg->blur_taps[i] == cfg->blur_taps[6 - i];
+            sum += cfg->blur_taps[i];
+        }
+        if (!zero && (!ok || sum != 256)) return B2ORB_ERR_INVALID;
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return B2ORB_ERR_CUDA;
     b2orb_handle* h = new (std::nothrow) b2orb_handle();
@@ -528,7 +554,7 @@ int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int w
     const int kcap = h->geom.kp_cap;
     cudaEventRecord(h->ev0, h->stream);
     if ((rc = upload(h, images, count, width, height, step, image_stride, 0))) return rc;
-    B2Images im = make_images(h, h->d_stage, h->d_stage, count, h->stage_img_bytes, width);
+    B2Images im = make_images(h, h->d_stage, h->d_stage, count, h->stage_img_bytes, h->stage_pitch);
     if ((rc = launch_extract(h, im, count))) return rc;
     B2_CUDA(h, cudaMemcpyAsync(n, h->d_nkp, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     cudaEventRecord(h->ev1, h->stream);
@@ -567,7 +593,16 @@ int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, con
     if (rc) return rc;
     if ((rc = bind_problems(h, npairs))) return rc;
     cudaEventRecord(h->ev0, h->stream);
-    B2Images im = make_images(h, d_images_l, d_images_r, npairs, image_stride, step);
+    B2Images im;
+    const auto aligned = [](const void* p, size_t a, size_t b) { return ((uintptr_t)p | a | b) % 16 == 0; };
+    if (aligned(d_images_l, (size_t)step, image_stride) && aligned(d_images_r, (size_t)step, image_stride)) {
+        im = make_images(h, d_images_l, d_images_r, npairs, image_stride, step);   // read in place
+    } else {   // kernels need 16-byte aligned rows: repack into the staging area (device-to-device)
+        if ((rc = upload(h, d_images_l, npairs, width, height, step, image_stride, 0, cudaMemcpyDeviceToDevice))) return rc;
+        if ((rc = upload(h, d_images_r, npairs, width, height, step, image_stride, npairs, cudaMemcpyDeviceToDevice))) return rc;
+        im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs, h->stage_img_bytes,
+                         h->stage_pitch);
+    }
     rc = launch_stereo(h, im, npairs, temporal);
     cudaEventRecord(h->ev1, h->stream);
     return rc;
@@ -618,7 +653,7 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0))) return rc;
     if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs))) return rc;
     B2Images im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs,
-                              h->stage_img_bytes, width);
+                              h->stage_img_bytes, h->stage_pitch);
     if ((rc = launch_stereo(h, im, npairs, temporal))) return rc;
     cudaEventRecord(h->ev1, h->stream);
     rc = b2orb_stereo_download(h, npairs, out);
@@ -771,7 +806,7 @@ int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8
     size_t pitch;
     if (which == 0 && level == 0) {   // level 0 of the last host-input call lives in the staging area
         src = h->d_stage + (size_t)slot * h->stage_img_bytes;
-        pitch = h->cur_w;
+        pitch = h->stage_pitch;
     } else {
         src = (which ? h->d_blur : h->d_pyr) + (size_t)slot * h->geom.slab + L.off;
         pitch = L.pitch;

@@ -9,167 +9,254 @@
 //     neighbours that are not corners or lie outside the ROI's detect area count as 0 — equivalently
 //     b(p) > b(q) for the neighbours q inside the cell's own detect area;
 //   * detect areas of neighbouring cells tile the bordered rectangle without overlap.
-// One CTA owns one cell: it stages the cell + 3-px halo in shared memory as u16x2 pixel pairs (pixel x
-// and pixel x + half-cell-width share a 32-bit word, so consecutive lanes hit consecutive banks), computes
-// b for two pixels per instruction with the native VIMNMX/VIMNMX3 .U16x2 min/max, does the cell-local
-// non-max suppression, votes on the threshold (any survivor with b > ini ? ini : min) and appends the
-// survivors to the level's candidate list.  Candidate order is irrelevant downstream: the quadtree breaks
-// response ties with a key that reproduces the reference's cell-row-major order.
+//
+// Two kernels, both organised around instructions per pixel (the stage is ALU-pipe bound, not HBM bound):
+//
+// fast_score_kernel — one WARP owns a 112-px strip (lanes 2..29 produce 4 px each, lanes 0/1/30/31 only feed
+//   the halo of the score and of the fused NMS) and marches down a band of rows.  Per image row a lane loads one 32-bit word, splits it into two
+//   u16x2 "pixel pairs" (x,x+2) and (x+1,x+3) and gets the six neighbouring pairs by shuffle, so the 16 ring
+//   pixels of TWO output pixels are always one register each; the last 7 rows of pairs live in registers
+//   (7-phase unrolled rotation).  b is evaluated on packed pairs with VIMNMX/VIMNMX3.U16x2:
+//       Rmax = max_arcs min_arc r,  Rmin = min_arcs max_arc r,  b = max(Rmax, c) - min(Rmin, c)
+//   (at most one side can be positive), arcs taken two at a time: max(min9[k], min9[k+1]) =
+//   min(min8[k+1..k+8], max(r[k], r[k+9])) — 36 min/max per side per pixel pair.  The 3x3 non-max suppression
+//   with the cell-boundary rule is fused in (3-row window of packed scores, column masks per lane, row masks
+//   per step) and the kernel writes a sparse corner map M: M = b where the pixel survives NMS inside its
+//   cell and b > minThFAST, else 0.
+// fast_cells_kernel — one warp per cell scans its part of M, votes on the threshold (any survivor with
+//   b > ini ? ini : min — src/ORBextractor.cc:809-816) and appends the survivors to the level's candidate
+//   list.  Candidate order is irrelevant downstream: the quadtree breaks response ties with a key that
+//   reproduces the reference's cell-row-major order.
 #include "b2orb_internal.cuh"
 
 namespace {
 
-constexpr int FT_THREADS = 128;
-constexpr int FT_MAX_CELL = 64;                         // cells are < 60 px on a side (ceil(W'/floor(W'/30)))
-constexpr int FT_MAX_HALF = FT_MAX_CELL / 2;
-constexpr int FT_TILE_WORDS = (FT_MAX_CELL + 6) * (FT_MAX_HALF + 6);
-constexpr int FT_ITEMS_PER_THREAD = 32;                 // >= ceil(64*64 / 128)
+constexpr int FS_WARPS = 4;
+constexpr int FS_PF = 4;        // rows in flight per warp
 
-__device__ __forceinline__ uint32_t umin2(uint32_t a, uint32_t b) { return __vminu2(a, b); }
-__device__ __forceinline__ uint32_t umax2(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
-__device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u16x2(a, b, c); }
-__device__ __forceinline__ uint32_t umax3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
+__device__ __forceinline__ unsigned vmin2(unsigned a, unsigned b) { return __vminu2(a, b); }
+__device__ __forceinline__ unsigned vmax2(unsigned a, unsigned b) { return __vmaxu2(a, b); }
+__device__ __forceinline__ unsigned vmin3(unsigned a, unsigned b, unsigned c) { return __vimin3_u16x2(a, b, c); }
+__device__ __forceinline__ unsigned vmax3(unsigned a, unsigned b, unsigned c) { return __vimax3_u16x2(a, b, c); }
 
-// b for the two pixels packed in `c` (u16 lanes), ring pixels in r[0..15] (same packing).
-// Biased differences d' = 256 + I(p) - I(q) keep both lanes positive so one 32-bit subtract serves
-// both; max over arcs of min over 9 uses sliding min3-of-min3.
-__device__ __forceinline__ uint32_t fast_b_pair(uint32_t c, const uint32_t (&r)[16]) {
-    uint32_t d[16], m3[16], M3[16];
-    const uint32_t cb = c + 0x01000100u;
+// b for the two pixels packed in c (u16 lanes), ring pixels v[0..15] in circle order (same packing).
+__device__ __forceinline__ unsigned fast_b_pair(const unsigned (&v)[16], unsigned c) {
+    unsigned qn[8], qx[8];     // min / max of v[j], v[j+1] for odd j = 2i+1
 #pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = cb - r[k];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        m3[k] = umin3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        M3[k] = umax3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    for (int i = 0; i < 8; ++i) {
+        qn[i] = vmin2(v[2 * i + 1], v[(2 * i + 2) & 15]);
+        qx[i] = vmax2(v[2 * i + 1], v[(2 * i + 2) & 15]);
     }
-    uint32_t A = 0, B = 0xFFFFFFFFu;  // A = max_arcs min9(d'), B = min_arcs max9(d')
+    unsigned rn[8], rx[8];     // min / max of v[j .. j+3]
 #pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        uint32_t a0 = umin3(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
-        uint32_t a1 = umin3(m3[(k + 1) & 15], m3[(k + 4) & 15], m3[(k + 7) & 15]);
-        A = umax3(A, a0, a1);
-        uint32_t b0 = umax3(M3[k], M3[(k + 3) & 15], M3[(k + 6) & 15]);
-        uint32_t b1 = umax3(M3[(k + 1) & 15], M3[(k + 4) & 15], M3[(k + 7) & 15]);
-        B = umin3(B, b0, b1);
+    for (int i = 0; i < 8; ++i) {
+        rn[i] = vmin2(qn[i], qn[(i + 1) & 7]);
+        rx[i] = vmax2(qx[i], qx[(i + 1) & 7]);
     }
-    // b = max(A' - 256, 256 - B', 0) per lane
-    const uint32_t bright = __vsubus2(A, 0x01000100u);
-    const uint32_t dark = __vsubus2(0x01000100u, B);
-    return umax2(bright, dark);
+    unsigned pn[8], px[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        // arcs k = 2i and k+1 share v[k+1 .. k+8] = rn[i], rn[i+2]; the ends are v[k] and v[k+9]
+        const unsigned a = v[2 * i], e = v[(2 * i + 9) & 15];
+        pn[i] = vmin3(rn[i], rn[(i + 2) & 7], vmax2(a, e));   // max(min9[k], min9[k+1])
+        px[i] = vmax3(rx[i], rx[(i + 2) & 7], vmin2(a, e));   // min(max9[k], max9[k+1])
+    }
+    const unsigned rmax = vmax3(vmax3(pn[0], pn[1], pn[2]), vmax3(pn[3], pn[4], pn[5]), vmax2(pn[6], pn[7]));
+    const unsigned rmin = vmin3(vmin3(px[0], px[1], px[2]), vmin3(px[3], px[4], px[5]), vmin2(px[6], px[7]));
+    return vmax2(rmax, c) - vmin2(rmin, c);   // per-lane non-negative: no borrow between the halves
 }
 
-__global__ void __launch_bounds__(FT_THREADS)
-fast_cells_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint32_t* __restrict__ cand,
-                  int* __restrict__ cand_cnt) {
-    __shared__ uint32_t s_tile[FT_TILE_WORDS];                    // packed pixel pairs, cell + halo
-    __shared__ uint8_t s_score[(FT_MAX_CELL + 2) * (FT_MAX_CELL + 4)];  // b per pixel, 1-px zero ring
-    __shared__ int s_base;
+// out = (b > nb) ? b : 0 per u16 lane, all values < 256
+__device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
+    const unsigned d = b + 0x00FF00FFu - nb;                 // bit 8 of each lane: b > nb
+    const unsigned one = __byte_perm(d, 0u, 0x4341);         // (d.b1, 0, d.b3, 0): 0 or 1 per lane
+    return b & (one * 255u);
+}
 
+__global__ void __launch_bounds__(FS_WARPS * 32)
+fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* __restrict__ score) {
+    const int lane = threadIdx.x & 31;
+    const int task = blockIdx.x * FS_WARPS + (threadIdx.x >> 5);
+    if (task >= g.total_fast_tasks) return;
     const int b = blockIdx.y;
     int level = 0;
-    while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].cell_base) ++level;
+    while (level + 1 < g.nlevels && task >= g.lv[level + 1].fast_task_base) ++level;
     const B2Level& L = g.lv[level];
-    const int cell = blockIdx.x - L.cell_base;
+    const int t = task - L.fast_task_base;
+    const int band = t / L.fast_strips, strip = t - band * L.fast_strips;
+    int pitch;
+    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
+    uint8_t* M = score + (size_t)b * g.slab + L.off;
+    const int w = L.w, h = L.h;
+    const int x = B2_BORDER - 8 + strip * 112 + lane * 4;      // lanes 2..29 own columns x .. x+3
+    const int ya = B2_EDGE + band * B2_FAST_BAND;              // M rows [ya, yb)
+    const int yb = min(ya + B2_FAST_BAND, h - B2_EDGE);
+    const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
+    const int xo = min(x, pitch - 4);
+    const uint8_t* col = img + xo;
+
+    // column masks of this lane's pixels (x, x+2 | x+1, x+3): inside [19, w-19), left / right neighbour in the same cell
+    unsigned inE = 0, inO = 0, mlE = 0, mlO = 0, mrE = 0, mrO = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int X = x + j;
+        const bool in = X >= B2_EDGE && X < w - B2_EDGE;
+        const int cx = (X - B2_EDGE) % L.w_cell;
+        const bool left = in && cx != 0;
+        const bool right = in && cx != L.w_cell - 1 && X + 1 < w - B2_EDGE;
+        const unsigned lanebits = (j & 2) ? 0xFFFF0000u : 0x0000FFFFu;
+        if (j & 1) { if (in) inO |= lanebits; if (left) mlO |= lanebits; if (right) mrO |= lanebits; }
+        else       { if (in) inE |= lanebits; if (left) mlE |= lanebits; if (right) mrE |= lanebits; }
+    }
+    const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
+    const bool store_lane = lane >= 2 && lane <= 29 && x < w - B2_BORDER;   // b valid on lanes 1..30, NMS on 2..29
+
+    unsigned raw[7];
+    unsigned P[7][8];            // pairs (p[a], p[a+2]) for a = x-3 .. x+4, last 7 rows
+#pragma unroll
+    for (int i = 0; i < FS_PF; ++i)
+        if (i < nsteps) raw[i] = *reinterpret_cast<const unsigned*>(col + (size_t)(ya - 4 + i) * pitch);
+
+    // NMS state: rows s-2 (rm only), s-1 (pending centre), s (newest)
+    unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
+
+    for (int base = 0; base < nsteps; base += 7) {
+#pragma unroll
+        for (int p = 0; p < 7; ++p) {
+            const int r = base + p;
+            if (r < nsteps) {
+                if (r + FS_PF < nsteps)
+                    raw[(p + FS_PF) % 7] = *reinterpret_cast<const unsigned*>(col + (size_t)(ya - 4 + r + FS_PF) * pitch);
+                // ---- pairs of this pixel row
+                const unsigned R1 = raw[p];
+                const unsigned E1 = __byte_perm(R1, 0u, 0x4240), O1 = __byte_perm(R1, 0u, 0x4341);
+                const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);
+                const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);
+                P[p][0] = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
+                P[p][1] = __shfl_up_sync(0xFFFFFFFFu, c2, 1);
+                P[p][2] = __shfl_up_sync(0xFFFFFFFFu, c3, 1);
+                P[p][3] = E1; P[p][4] = O1; P[p][5] = c2; P[p][6] = c3; P[p][7] = E2;
+                if (r >= 6) {
+                    // ---- b of score row s = ya - 7 + r (pixel rows r-6 .. r; centre r-3)
+                    const int s3 = p, s2 = (p + 6) % 7, s1 = (p + 5) % 7, s0 = (p + 4) % 7, t1 = (p + 3) % 7,
+                              t2 = (p + 2) % 7, t3 = (p + 1) % 7;      // rows +3 .. -3
+                    unsigned bE, bO;
+                    {
+                        const unsigned v[16] = {P[s3][3], P[s3][4], P[s2][5], P[s1][6], P[s0][6], P[t1][6], P[t2][5], P[t3][4],
+                                                P[t3][3], P[t3][2], P[t2][1], P[t1][0], P[s0][0], P[s1][0], P[s2][1], P[s3][2]};
+                        bE = fast_b_pair(v, P[s0][3]);
+                    }
+                    {
+                        const unsigned v[16] = {P[s3][4], P[s3][5], P[s2][6], P[s1][7], P[s0][7], P[t1][7], P[t2][6], P[t3][5],
+                                                P[t3][4], P[t3][3], P[t2][2], P[t1][1], P[s0][1], P[s1][1], P[s2][2], P[s3][3]};
+                        bO = fast_b_pair(v, P[s0][4]);
+                    }
+                    // ---- horizontal neighbours of the packed scores, masked to the pixel's own cell
+                    const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1);
+                    const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;   // (b[x-1], b[x+1])
+                    const unsigned rE = bO & mrE;                             // (b[x+1], b[x+3])
+                    const unsigned lO = bE & mlO;                             // (b[x],   b[x+2])
+                    const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;   // (b[x+2], b[x+4])
+                    const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);
+                    if (r >= 8) {
+                        // ---- NMS of row y = ya - 8 + r: rows above (a), itself (b), below (new)
+                        const int y = ya - 8 + r;
+                        const int cy = (y - B2_EDGE) % L.h_cell;
+                        const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;
+                        const unsigned dn = (cy != L.h_cell - 1 && y + 1 < h - B2_EDGE) ? 0xFFFFFFFFu : 0u;
+                        const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));
+                        const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));
+                        const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;
+                        if (store_lane)
+                            *reinterpret_cast<unsigned*>(M + (size_t)y * L.pitch + x) = __byte_perm(oE, oO, 0x6240);
+                    }
+                    rmE_a = rmE_b; rmO_a = rmO_b;
+                    rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;
+                    sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+constexpr int FC_WARPS = 4;
+constexpr int FC_BUF = 1024;     // >= ceil(64/2) * ceil(64/2) survivors of one cell (NMS keeps <= 1 of 4)
+
+__global__ void __launch_bounds__(FC_WARPS * 32)
+fast_cells_kernel(const __grid_constant__ B2Geom g, const uint8_t* __restrict__ score, uint32_t* __restrict__ cand,
+                  int* __restrict__ cand_cnt) {
+    __shared__ uint32_t s_buf[FC_WARPS][FC_BUF];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int cellid = blockIdx.x * FC_WARPS + wid;
+    if (cellid >= g.total_cells) return;
+    const int b = blockIdx.y;
+    int level = 0;
+    while (level + 1 < g.nlevels && cellid >= g.lv[level + 1].cell_base) ++level;
+    const B2Level& L = g.lv[level];
+    const int cell = cellid - L.cell_base;
     const int ci = cell / L.n_cols, cj = cell - ci * L.n_cols;
     // detect area of this cell in level coordinates (ROI inset by 3, clipped to maxBorder-3 = dim-19)
     const int x0 = B2_EDGE + cj * L.w_cell, y0 = B2_EDGE + ci * L.h_cell;
     const int x1 = min(x0 + L.w_cell, L.w - B2_EDGE), y1 = min(y0 + L.h_cell, L.h - B2_EDGE);
-    const int cw = x1 - x0, ch = y1 - y0;
-    if (cw <= 0 || ch <= 0) return;
-    const int half = (cw + 1) >> 1;
-    const int tw = half + 6;            // packed tile width in words
-    const int sp = cw + 2;              // score tile pitch
-    int pitch;
-    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
-    const int tid = threadIdx.x;
-
-    // stage: word (r,c) = I[y0-3+r][x0-3+c] | I[y0-3+r][x0-3+c+half] << 16
-    const uint8_t* org = img + (size_t)(y0 - 3) * pitch + (x0 - 3);
-    const int xlim = L.w - (x0 - 3);    // columns beyond the image are never used for a valid pixel
-    for (int i = tid; i < (ch + 6) * tw; i += FT_THREADS) {
-        const int r = i / tw, c = i - r * tw;
-        const uint8_t* p = org + (size_t)r * pitch + c;
-        const uint32_t lo = p[0];
-        const uint32_t hi = (c + half < xlim) ? p[half] : 0u;
-        s_tile[i] = lo | (hi << 16);
-    }
-    for (int i = tid; i < (ch + 2) * sp; i += FT_THREADS) s_score[i] = 0;
-    __syncthreads();
-
-    // b for every pixel of the detect area, two at a time
-    for (int i = tid; i < ch * half; i += FT_THREADS) {
-        const int r = i / half, c = i - r * half;
-        const uint32_t* t = &s_tile[(r + 3) * tw + (c + 3)];
-        uint32_t ring[16];
-        ring[0] = t[3 * tw];       ring[1] = t[3 * tw + 1];   ring[2] = t[2 * tw + 2];   ring[3] = t[tw + 3];
-        ring[4] = t[3];            ring[5] = t[-tw + 3];      ring[6] = t[-2 * tw + 2];  ring[7] = t[-3 * tw + 1];
-        ring[8] = t[-3 * tw];      ring[9] = t[-3 * tw - 1];  ring[10] = t[-2 * tw - 2]; ring[11] = t[-tw - 3];
-        ring[12] = t[-3];          ring[13] = t[tw - 3];      ring[14] = t[2 * tw - 2];  ring[15] = t[3 * tw - 1];
-        const uint32_t bb = fast_b_pair(t[0], ring);
-        s_score[(r + 1) * sp + (c + 1)] = (uint8_t)(bb & 0xFFFFu);
-        if (c + half < cw) s_score[(r + 1) * sp + (c + half + 1)] = (uint8_t)(bb >> 16);
-    }
-    __syncthreads();
-
-    // cell-local strict 3x3 non-max suppression; survivors above each threshold as per-thread bit masks
-    uint32_t m_ini = 0, m_min = 0;
-    const int npx = ch * cw;
-#pragma unroll 1
-    for (int k = 0; k < FT_ITEMS_PER_THREAD; ++k) {
-        const int i = tid + k * FT_THREADS;
-        if (i >= npx) break;
-        const int r = i / cw, c = i - r * cw;
-        const uint8_t* s = &s_score[(r + 1) * sp + (c + 1)];
-        const int v = s[0];
-        if (v > g.min_th) {
-            const bool mx = v > s[-1] && v > s[1] && v > s[-sp - 1] && v > s[-sp] && v > s[-sp + 1] &&
-                            v > s[sp - 1] && v > s[sp] && v > s[sp + 1];
-            if (mx) {
-                m_min |= 1u << k;
-                if (v > g.ini_th) m_ini |= 1u << k;
+    if (x1 <= x0 || y1 <= y0) return;
+    const uint8_t* M = score + (size_t)b * g.slab + L.off;
+    uint32_t* buf = s_buf[wid];
+    const int ini = g.ini_th;
+    int n = 0;
+    bool any_ini = false;
+    for (int y = y0; y < y1; ++y) {
+        const uint8_t* row = M + (size_t)y * L.pitch;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int xx = x0 + half * 32 + lane;
+            const unsigned v = xx < x1 ? row[xx] : 0u;
+            const unsigned bal = __ballot_sync(0xFFFFFFFFu, v != 0);
+            any_ini |= __any_sync(0xFFFFFFFFu, (int)v > ini);
+            if (v) {
+                const int pos = n + __popc(bal & ((1u << lane) - 1));
+                if (pos < FC_BUF) buf[pos] = (unsigned)(xx - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((v - 1u) << 24);
             }
+            n += __popc(bal);
+            if (x0 + 32 >= x1) break;
         }
     }
-    const int any_ini = __syncthreads_or(m_ini != 0);
-    uint32_t m = any_ini ? m_ini : m_min;   // src/ORBextractor.cc:809-816: min threshold only if ini found nothing
-
-    // append survivors: block-aggregated reservation, then one write per survivor
-    const int mine = __popc(m);
-    // warp scan + cross-warp offsets
-    __shared__ int s_warp[FT_THREADS / 32];
-    const int lane = tid & 31, wid = tid >> 5;
-    int incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += n;
+    __syncwarp();
+    n = min(n, FC_BUF);
+    // src/ORBextractor.cc:809-816: the min threshold applies only if the ini threshold found nothing in this cell
+    const unsigned thr = any_ini ? (unsigned)ini : 0u;     // entries hold b-1; keep b > thr  <=>  b-1 >= thr
+    int kept = 0;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const bool k = i < n && (buf[i] >> 24) >= thr;
+        kept += __popc(__ballot_sync(0xFFFFFFFFu, k));
     }
-    if (lane == 31) s_warp[wid] = incl;
-    __syncthreads();
-    if (tid == 0) {
-        int tot = 0;
-        for (int wdx = 0; wdx < FT_THREADS / 32; ++wdx) { int v = s_warp[wdx]; s_warp[wdx] = tot; tot += v; }
-        s_base = tot ? atomicAdd(&cand_cnt[b * g.nlevels + level], tot) : 0;
-    }
-    __syncthreads();
-    int pos = s_base + s_warp[wid] + incl - mine;
+    if (kept == 0) return;
+    int basepos = 0;
+    if (lane == 0) basepos = atomicAdd(&cand_cnt[b * g.nlevels + level], kept);
+    basepos = __shfl_sync(0xFFFFFFFFu, basepos, 0);
     uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
-    while (m) {
-        const int k = __ffs(m) - 1;
-        m &= m - 1;
-        const int i = tid + k * FT_THREADS;
-        const int r = i / cw, c = i - r * cw;
-        const uint32_t v = s_score[(r + 1) * sp + (c + 1)];
-        const uint32_t xr = x0 + c - B2_BORDER, yr = y0 + r - B2_BORDER;   // relative to minBorderX/Y
-        if (pos < L.cand_cap) out[pos] = xr | (yr << 12) | ((v - 1u) << 24);
-        ++pos;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const uint32_t e = i < n ? buf[i] : 0u;
+        const bool k = i < n && (e >> 24) >= thr;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, k);
+        if (k) {
+            const int pos = basepos + __popc(bal & ((1u << lane) - 1));
+            if (pos < L.cand_cap) out[pos] = e;
+        }
+        basepos += __popc(bal);
     }
 }
 
 }  // namespace
 
-void b2_launch_fast(const B2Geom& g, const B2Images& im, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s) {
-    dim3 grid(g.total_cells, nimg);
-    fast_cells_kernel<<<grid, FT_THREADS, 0, s>>>(g, im, cand, cand_cnt);
+void b2_launch_fast(const B2Geom& g, const B2Images& im, uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg,
+                    cudaStream_t s) {
+    if (g.total_fast_tasks > 0) {
+        dim3 grid((g.total_fast_tasks + FS_WARPS - 1) / FS_WARPS, nimg);
+        fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, score);
+    }
+    dim3 grid2((g.total_cells + FC_WARPS - 1) / FC_WARPS, nimg);
+    fast_cells_kernel<<<grid2, FC_WARPS * 32, 0, s>>>(g, score, cand, cand_cnt);
 }
