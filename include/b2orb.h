@@ -163,7 +163,7 @@ void* b2orb_stream(const b2orb_handle* h);
  * accumulated milliseconds and launch counts per kernel id since b2orb_profile_enable(h, 1). */
 enum {
     B2ORB_K_RESIZE = 0, B2ORB_K_FAST, B2ORB_K_OCTREE, B2ORB_K_BLUR, B2ORB_K_DESCRIBE, B2ORB_K_MATCH_STEREO,
-    B2ORB_K_STEREO_FILTER, B2ORB_K_MATCH_TEMPORAL, B2ORB_K_CIRCULAR, B2ORB_NUM_KERNELS
+    B2ORB_K_STEREO_FILTER, B2ORB_K_MATCH_TEMPORAL, B2ORB_K_CIRCULAR, B2ORB_K_FAST_CELLS, B2ORB_K_INGEST, B2ORB_NUM_KERNELS
 };
 void b2orb_profile_enable(b2orb_handle* h, int on);
 int b2orb_profile_read(b2orb_handle* h, double* ms /*[B2ORB_NUM_KERNELS]*/, uint64_t* launches /*[B2ORB_NUM_KERNELS]*/);

@@ -92,9 +92,11 @@ struct B2MatchProblem {
 // ---- kernel launchers (each file documents the reference lines it restates) --------------------
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s);
+void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
+                      int h, int count, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);
-void b2_launch_fast(const B2Geom& g, const B2Images& im, uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg,
-                    cudaStream_t s);
+void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint8_t* score, int nimg, cudaStream_t s);
+void b2_launch_fast_cells(const B2Geom& g, const uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
                       B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,

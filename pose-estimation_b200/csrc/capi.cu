@@ -48,7 +48,7 @@ struct b2orb_handle {
 
     // workspace (sized for cfg.max_images images of the current size)
     int nimg_cap = 0, npair_cap = 0;
-    uint8_t *d_stage = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
+    uint8_t *d_stage = nullptr, *d_raw = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
     size_t stage_img_bytes = 0;
     int stage_pitch = 0;                                 // level-0 rows in the staging area: 32-byte aligned pitch
     uint32_t* d_cand = nullptr;
@@ -304,6 +304,7 @@ int configure(b2orb_handle* h, int w, int hgt) {
     h->stage_img_bytes = (size_t)h->stage_pitch * hgt;
     const size_t cap = g.kp_cap;
     bool ok = dev_alloc(h, &h->d_stage, (size_t)nimg * h->stage_img_bytes) &&
+              dev_alloc(h, &h->d_raw, (size_t)nimg * w * hgt) &&
               dev_alloc(h, &h->d_pyr, (size_t)nimg * g.slab) && dev_alloc(h, &h->d_blur, (size_t)nimg * g.slab) &&
               dev_alloc(h, &h->d_score, (size_t)nimg * g.slab) &&
               dev_alloc(h, &h->d_cand, (size_t)nimg * g.cand_total) &&
@@ -366,7 +367,12 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     prof_mark(h, -1);
     B2_CUDA(h, cudaMemsetAsync(h->d_cand_cnt, 0, (size_t)nimg * g.nlevels * sizeof(int), s));
     prof_mark(h, B2ORB_K_FAST);
-    if (g.total_cells > 0) { b2_launch_fast(g, im, h->d_score, h->d_cand, h->d_cand_cnt, nimg, s); h->launches += 2; }
+    if (g.total_cells > 0) {
+        b2_launch_fast_score(g, im, h->d_score, nimg, s);
+        prof_mark(h, B2ORB_K_FAST_CELLS);
+        b2_launch_fast_cells(g, h->d_score, h->d_cand, h->d_cand_cnt, nimg, s);
+        h->launches += 2;
+    }
     prof_mark(h, B2ORB_K_OCTREE);
     b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
     ++h->launches;
@@ -394,16 +400,31 @@ B2Images make_images(b2orb_handle* h, const uint8_t* a, const uint8_t* b, int sp
 }
 
 // Host (or device) images -> staging area with an aligned row pitch (kernels read level 0 with 32-bit / 128-bit
-// accesses).  Contiguous batches go as ONE 2-D copy.
+// accesses).  Host images whose rows are already aligned go straight in; tight rows of odd width (1241 ...) are
+// copied linearly (a pitched 2-D DMA of odd-width rows runs at half the PCIe rate) and re-pitched by a kernel.
 int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
-           cudaMemcpyKind kind = cudaMemcpyHostToDevice) {
+           bool on_device = false) {
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
-    if (image_stride == (size_t)step * hgt) {
-        B2_CUDA(h, cudaMemcpy2DAsync(dst, h->stage_pitch, src, step, w, (size_t)count * hgt, kind, h->stream));
+    if (on_device) {
+        prof_mark(h, B2ORB_K_INGEST);
+        b2_launch_repack(src, step, image_stride, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
+        ++h->launches;
+        prof_mark(h, -1);
+        return B2ORB_OK;
+    }
+    if (step == h->stage_pitch && image_stride == (size_t)step * hgt) {
+        B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * step * hgt, cudaMemcpyHostToDevice, h->stream));
+    } else if (step == w && image_stride == (size_t)w * hgt) {
+        uint8_t* raw = h->d_raw + (size_t)slot0 * w * hgt;
+        B2_CUDA(h, cudaMemcpyAsync(raw, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, h->stream));
+        prof_mark(h, B2ORB_K_INGEST);
+        b2_launch_repack(raw, w, (size_t)w * hgt, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
+        ++h->launches;
+        prof_mark(h, -1);
     } else {
         for (int i = 0; i < count; ++i)
             B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, h->stage_pitch, src + i * image_stride, step, w,
-                                         hgt, kind, h->stream));
+                                         hgt, cudaMemcpyHostToDevice, h->stream));
     }
     return B2ORB_OK;
 }
@@ -598,8 +619,8 @@ int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, con
     if (aligned(d_images_l, (size_t)step, image_stride) && aligned(d_images_r, (size_t)step, image_stride)) {
         im = make_images(h, d_images_l, d_images_r, npairs, image_stride, step);   // read in place
     } else {   // kernels need 16-byte aligned rows: repack into the staging area (device-to-device)
-        if ((rc = upload(h, d_images_l, npairs, width, height, step, image_stride, 0, cudaMemcpyDeviceToDevice))) return rc;
-        if ((rc = upload(h, d_images_r, npairs, width, height, step, image_stride, npairs, cudaMemcpyDeviceToDevice))) return rc;
+        if ((rc = upload(h, d_images_l, npairs, width, height, step, image_stride, 0, true))) return rc;
+        if ((rc = upload(h, d_images_r, npairs, width, height, step, image_stride, npairs, true))) return rc;
         im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs, h->stage_img_bytes,
                          h->stage_pitch);
     }

@@ -113,70 +113,88 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
 
     unsigned raw[7];
     unsigned P[7][8];            // pairs (p[a], p[a+2]) for a = x-3 .. x+4, last 7 rows
+    // Rows are addressed by a 32-bit offset that is clamped to the last row of the band, so the prefetch needs no
+    // branch; pixel row r of the band sits at col0 + r * pitch.
+    const uint8_t* col0 = col + (size_t)(ya - 4) * pitch;
+    const unsigned offmax = (unsigned)(nsteps - 1) * (unsigned)pitch;
+    unsigned off = 0;
 #pragma unroll
-    for (int i = 0; i < FS_PF; ++i)
-        if (i < nsteps) raw[i] = *reinterpret_cast<const unsigned*>(col + (size_t)(ya - 4 + i) * pitch);
+    for (int i = 0; i < FS_PF; ++i) {
+        raw[i] = *reinterpret_cast<const unsigned*>(col0 + min(off, offmax));
+        off += pitch;
+    }
+#define B2_FAST_PAIRS(p)                                                                                        \
+    {                                                                                                           \
+        const unsigned R1 = raw[p];                                                                             \
+        raw[((p) + FS_PF) % 7] = *reinterpret_cast<const unsigned*>(col0 + min(off, offmax));                   \
+        off += pitch;                                                                                           \
+        const unsigned E1 = __byte_perm(R1, 0u, 0x4240), O1 = __byte_perm(R1, 0u, 0x4341);                      \
+        const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);    \
+        const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                      \
+        P[p][0] = __shfl_up_sync(0xFFFFFFFFu, O1, 1);                                                           \
+        P[p][1] = __shfl_up_sync(0xFFFFFFFFu, c2, 1);                                                           \
+        P[p][2] = __shfl_up_sync(0xFFFFFFFFu, c3, 1);                                                           \
+        P[p][3] = E1; P[p][4] = O1; P[p][5] = c2; P[p][6] = c3; P[p][7] = E2;                                   \
+    }
+    // prologue: pixel rows 0..5 only fill the window
+#pragma unroll
+    for (int p = 0; p < 6; ++p) B2_FAST_PAIRS(p)
 
     // NMS state: rows s-2 (rm only), s-1 (pending centre), s (newest)
     unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
+    uint8_t* mrow = M + (size_t)ya * L.pitch + x;             // output row of step r = 8
+    int y = ya;
+    int cy = (band * B2_FAST_BAND) % L.h_cell;                 // row of y inside its cell
+    const int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
 
-    for (int base = 0; base < nsteps; base += 7) {
+#define B2_FAST_STEP(p, OUT)                                                                                   \
+    {                                                                                                           \
+        B2_FAST_PAIRS(p)                                                                                     \
+        const int s3 = p, s2 = (p + 6) % 7, s1 = (p + 5) % 7, s0 = (p + 4) % 7, t1 = (p + 3) % 7,            \
+                  t2 = (p + 2) % 7, t3 = (p + 1) % 7;                                                        \
+        unsigned bE, bO;                                                                                     \
+        {                                                                                                    \
+            const unsigned v[16] = {P[s3][3], P[s3][4], P[s2][5], P[s1][6], P[s0][6], P[t1][6], P[t2][5], P[t3][4], \
+                                    P[t3][3], P[t3][2], P[t2][1], P[t1][0], P[s0][0], P[s1][0], P[s2][1], P[s3][2]}; \
+            bE = fast_b_pair(v, P[s0][3]);                                                                   \
+        }                                                                                                    \
+        {                                                                                                    \
+            const unsigned v[16] = {P[s3][4], P[s3][5], P[s2][6], P[s1][7], P[s0][7], P[t1][7], P[t2][6], P[t3][5], \
+                                    P[t3][4], P[t3][3], P[t2][2], P[t1][1], P[s0][1], P[s1][1], P[s2][2], P[s3][3]}; \
+            bO = fast_b_pair(v, P[s0][4]);                                                                   \
+        }                                                                                                    \
+        const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1); \
+        const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;                                              \
+        const unsigned rE = bO & mrE;                                                                        \
+        const unsigned lO = bE & mlO;                                                                        \
+        const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;                                              \
+        const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);                                     \
+        if (OUT) {                                                                                           \
+            const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;                                                  \
+            const unsigned dn = (cy != hcell1 && y != ylast) ? 0xFFFFFFFFu : 0u;                             \
+            const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));                            \
+            const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));                            \
+            const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;     \
+            if (store_lane) *reinterpret_cast<unsigned*>(mrow) = __byte_perm(oE, oO, 0x6240);                \
+            mrow += L.pitch;                                                                                 \
+            ++y;                                                                                             \
+            cy = cy == hcell1 ? 0 : cy + 1;                                                                  \
+        }                                                                                                    \
+        rmE_a = rmE_b; rmO_a = rmO_b;                                                                        \
+        rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;                                                      \
+        sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);                                                        \
+    }
+    // score rows ya-1 and ya only prime the NMS window (pixel rows r = 6, 7); outputs start at r = 8
+    if (6 < nsteps) B2_FAST_STEP(6, false)
+    if (7 < nsteps) B2_FAST_STEP(0, false)
+    for (int base = 8; base < nsteps; base += 7) {
 #pragma unroll
-        for (int p = 0; p < 7; ++p) {
-            const int r = base + p;
-            if (r < nsteps) {
-                if (r + FS_PF < nsteps)
-                    raw[(p + FS_PF) % 7] = *reinterpret_cast<const unsigned*>(col + (size_t)(ya - 4 + r + FS_PF) * pitch);
-                // ---- pairs of this pixel row
-                const unsigned R1 = raw[p];
-                const unsigned E1 = __byte_perm(R1, 0u, 0x4240), O1 = __byte_perm(R1, 0u, 0x4341);
-                const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);
-                const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);
-                P[p][0] = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
-                P[p][1] = __shfl_up_sync(0xFFFFFFFFu, c2, 1);
-                P[p][2] = __shfl_up_sync(0xFFFFFFFFu, c3, 1);
-                P[p][3] = E1; P[p][4] = O1; P[p][5] = c2; P[p][6] = c3; P[p][7] = E2;
-                if (r >= 6) {
-                    // ---- b of score row s = ya - 7 + r (pixel rows r-6 .. r; centre r-3)
-                    const int s3 = p, s2 = (p + 6) % 7, s1 = (p + 5) % 7, s0 = (p + 4) % 7, t1 = (p + 3) % 7,
-                              t2 = (p + 2) % 7, t3 = (p + 1) % 7;      // rows +3 .. -3
-                    unsigned bE, bO;
-                    {
-                        const unsigned v[16] = {P[s3][3], P[s3][4], P[s2][5], P[s1][6], P[s0][6], P[t1][6], P[t2][5], P[t3][4],
-                                                P[t3][3], P[t3][2], P[t2][1], P[t1][0], P[s0][0], P[s1][0], P[s2][1], P[s3][2]};
-                        bE = fast_b_pair(v, P[s0][3]);
-                    }
-                    {
-                        const unsigned v[16] = {P[s3][4], P[s3][5], P[s2][6], P[s1][7], P[s0][7], P[t1][7], P[t2][6], P[t3][5],
-                                                P[t3][4], P[t3][3], P[t2][2], P[t1][1], P[s0][1], P[s1][1], P[s2][2], P[s3][3]};
-                        bO = fast_b_pair(v, P[s0][4]);
-                    }
-                    // ---- horizontal neighbours of the packed scores, masked to the pixel's own cell
-                    const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1);
-                    const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;   // (b[x-1], b[x+1])
-                    const unsigned rE = bO & mrE;                             // (b[x+1], b[x+3])
-                    const unsigned lO = bE & mlO;                             // (b[x],   b[x+2])
-                    const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;   // (b[x+2], b[x+4])
-                    const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);
-                    if (r >= 8) {
-                        // ---- NMS of row y = ya - 8 + r: rows above (a), itself (b), below (new)
-                        const int y = ya - 8 + r;
-                        const int cy = (y - B2_EDGE) % L.h_cell;
-                        const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;
-                        const unsigned dn = (cy != L.h_cell - 1 && y + 1 < h - B2_EDGE) ? 0xFFFFFFFFu : 0u;
-                        const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));
-                        const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));
-                        const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;
-                        if (store_lane)
-                            *reinterpret_cast<unsigned*>(M + (size_t)y * L.pitch + x) = __byte_perm(oE, oO, 0x6240);
-                    }
-                    rmE_a = rmE_b; rmO_a = rmO_b;
-                    rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;
-                    sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);
-                }
-            }
+        for (int q = 0; q < 7; ++q) {
+            if (base + q < nsteps) B2_FAST_STEP((1 + q) % 7, true)
         }
     }
+#undef B2_FAST_STEP
+#undef B2_FAST_PAIRS
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -203,24 +221,40 @@ fast_cells_kernel(const __grid_constant__ B2Geom g, const uint8_t* __restrict__ 
     const uint8_t* M = score + (size_t)b * g.slab + L.off;
     uint32_t* buf = s_buf[wid];
     const int ini = g.ini_th;
-    int n = 0;
-    bool any_ini = false;
-    for (int y = y0; y < y1; ++y) {
-        const uint8_t* row = M + (size_t)y * L.pitch;
+    __shared__ int s_cnt[FC_WARPS];
+    if (lane == 0) s_cnt[wid] = 0;
+    __syncwarp();
+    // Word-wise scan: a lane owns one aligned 32-bit column of the cell (4 px) and, when the cell is at most 16
+    // words wide, every other row.  M is sparse (NMS keeps <= 1 px of 4), so the append path is rarely taken;
+    // buffer order is irrelevant (the quadtree re-derives the reference order from coordinates).
+    const int xa = x0 & ~3;
+    const int wpr = (((x1 + 3) & ~3) - xa) >> 2;               // words per cell row, <= 17
+    const int rpi = wpr <= 16 ? 2 : 1;                          // rows per iteration
+    const int wc = rpi == 2 ? (lane & 15) : lane;
+    const int rsub = rpi == 2 ? (lane >> 4) : 0;
+    unsigned bytemask = 0;
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int xx = x0 + half * 32 + lane;
-            const unsigned v = xx < x1 ? row[xx] : 0u;
-            const unsigned bal = __ballot_sync(0xFFFFFFFFu, v != 0);
-            any_ini |= __any_sync(0xFFFFFFFFu, (int)v > ini);
-            if (v) {
-                const int pos = n + __popc(bal & ((1u << lane) - 1));
-                if (pos < FC_BUF) buf[pos] = (unsigned)(xx - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((v - 1u) << 24);
-            }
-            n += __popc(bal);
-            if (x0 + 32 >= x1) break;
+    for (int j = 0; j < 4; ++j) {
+        const int X = xa + 4 * wc + j;
+        if (wc < wpr && X >= x0 && X < x1) bytemask |= 0xFFu << (8 * j);
+    }
+    bool mine_ini = false;
+    const uint8_t* colp = M + xa + 4 * wc;
+    for (int y = y0 + rsub; y < y1; y += rpi) {
+        unsigned v = bytemask ? (*reinterpret_cast<const unsigned*>(colp + (size_t)y * L.pitch) & bytemask) : 0u;
+        while (v) {
+            const int j = (__ffs(v) - 1) >> 3;
+            const unsigned bv = (v >> (8 * j)) & 0xFFu;
+            v &= ~(0xFFu << (8 * j));
+            mine_ini |= (int)bv > ini;
+            const int pos = atomicAdd(&s_cnt[wid], 1);
+            if (pos < FC_BUF)
+                buf[pos] = (unsigned)(xa + 4 * wc + j - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((bv - 1u) << 24);
         }
     }
+    const bool any_ini = __any_sync(0xFFFFFFFFu, mine_ini);
+    __syncwarp();
+    int n = s_cnt[wid];
     __syncwarp();
     n = min(n, FC_BUF);
     // src/ORBextractor.cc:809-816: the min threshold applies only if the ini threshold found nothing in this cell
@@ -251,12 +285,14 @@ fast_cells_kernel(const __grid_constant__ B2Geom g, const uint8_t* __restrict__ 
 
 }  // namespace
 
-void b2_launch_fast(const B2Geom& g, const B2Images& im, uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg,
-                    cudaStream_t s) {
-    if (g.total_fast_tasks > 0) {
-        dim3 grid((g.total_fast_tasks + FS_WARPS - 1) / FS_WARPS, nimg);
-        fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, score);
-    }
-    dim3 grid2((g.total_cells + FC_WARPS - 1) / FC_WARPS, nimg);
-    fast_cells_kernel<<<grid2, FC_WARPS * 32, 0, s>>>(g, score, cand, cand_cnt);
+void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint8_t* score, int nimg, cudaStream_t s) {
+    if (g.total_fast_tasks <= 0) return;
+    dim3 grid((g.total_fast_tasks + FS_WARPS - 1) / FS_WARPS, nimg);
+    fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, score);
+}
+
+void b2_launch_fast_cells(const B2Geom& g, const uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s) {
+    if (g.total_cells <= 0) return;
+    dim3 grid((g.total_cells + FC_WARPS - 1) / FC_WARPS, nimg);
+    fast_cells_kernel<<<grid, FC_WARPS * 32, 0, s>>>(g, score, cand, cand_cnt);
 }

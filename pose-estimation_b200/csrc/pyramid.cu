@@ -47,6 +47,23 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, co
     *reinterpret_cast<uint32_t*>(dst + dx0) = packed;  // pitch is a multiple of 16: padding bytes are ours
 }
 
+// Level-0 ingest: images with arbitrary row step (e.g. tight 1241-byte rows) -> staging area whose rows start on
+// 32-byte boundaries, which is what every other kernel's 32/128-bit accesses assume.  One thread per output word.
+__global__ void __launch_bounds__(256)
+repack_kernel(const uint8_t* __restrict__ src, int step, size_t stride, uint8_t* __restrict__ dst, int dpitch,
+              size_t dstride, int w, int h) {
+    const int words = dpitch >> 2;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= words * h) return;
+    const int y = i / words, xw = (i - y * words) * 4;
+    const uint8_t* s = src + blockIdx.y * stride + (size_t)y * step + xw;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (xw + k < w) v |= (uint32_t)s[k] << (8 * k);
+    *reinterpret_cast<uint32_t*>(dst + blockIdx.y * dstride + (size_t)y * dpitch + xw) = v;
+}
+
 }  // namespace
 
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
@@ -55,4 +72,10 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
     dim3 block(RS_TX, RS_TY);
     dim3 grid((L.w + RS_TX * 4 - 1) / (RS_TX * 4), (L.h + RS_TY - 1) / RS_TY, nimg);
     resize_kernel<<<grid, block, 0, s>>>(g, im, level, xofs, xw, yofs, yw);
+}
+
+void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
+                      int h, int count, cudaStream_t s) {
+    dim3 grid(((dpitch >> 2) * h + 255) / 256, count);
+    repack_kernel<<<grid, 256, 0, s>>>(src, step, stride, dst, dpitch, dstride, w, h);
 }

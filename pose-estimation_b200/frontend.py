@@ -23,7 +23,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 
 OK, ERR_INVALID, ERR_CAPACITY, ERR_CUDA, ERR_NOMEM = 0, 1, 2, 3, 4
 KERNEL_NAMES = ("resize", "fast", "octree", "blur", "describe", "match_stereo", "stereo_filter", "match_temporal",
-                "circular")
+                "circular", "fast_cells", "ingest")
 
 
 class B2Config(C.Structure):
