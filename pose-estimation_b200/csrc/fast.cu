@@ -199,6 +199,7 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
 
 // ---------------------------------------------------------------------------------------------------
 constexpr int FC_WARPS = 4;
+constexpr int FC_CHUNK = 8;
 constexpr int FC_BUF = 1024;     // >= ceil(64/2) * ceil(64/2) survivors of one cell (NMS keeps <= 1 of 4)
 
 __global__ void __launch_bounds__(FC_WARPS * 32)
@@ -240,16 +241,27 @@ fast_cells_kernel(const __grid_constant__ B2Geom g, const uint8_t* __restrict__ 
     }
     bool mine_ini = false;
     const uint8_t* colp = M + xa + 4 * wc;
-    for (int y = y0 + rsub; y < y1; y += rpi) {
-        unsigned v = bytemask ? (*reinterpret_cast<const unsigned*>(colp + (size_t)y * L.pitch) & bytemask) : 0u;
-        while (v) {
-            const int j = (__ffs(v) - 1) >> 3;
-            const unsigned bv = (v >> (8 * j)) & 0xFFu;
-            v &= ~(0xFFu << (8 * j));
-            mine_ini |= (int)bv > ini;
-            const int pos = atomicAdd(&s_cnt[wid], 1);
-            if (pos < FC_BUF)
-                buf[pos] = (unsigned)(xa + 4 * wc + j - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((bv - 1u) << 24);
+    // loads are issued FC_CHUNK rows at a time so their latencies overlap; the (rare) append path runs afterwards
+    for (int yc = y0 + rsub; yc < y1; yc += rpi * FC_CHUNK) {
+        unsigned vv[FC_CHUNK];
+#pragma unroll
+        for (int k = 0; k < FC_CHUNK; ++k) {
+            const int y = yc + k * rpi;
+            vv[k] = (bytemask && y < y1) ? (*reinterpret_cast<const unsigned*>(colp + (size_t)y * L.pitch) & bytemask) : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < FC_CHUNK; ++k) {
+            unsigned v = vv[k];
+            const int y = yc + k * rpi;
+            while (v) {
+                const int j = (__ffs(v) - 1) >> 3;
+                const unsigned bv = (v >> (8 * j)) & 0xFFu;
+                v &= ~(0xFFu << (8 * j));
+                mine_ini |= (int)bv > ini;
+                const int pos = atomicAdd(&s_cnt[wid], 1);
+                if (pos < FC_BUF)
+                    buf[pos] = (unsigned)(xa + 4 * wc + j - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((bv - 1u) << 24);
+            }
         }
     }
     const bool any_ini = __any_sync(0xFFFFFFFFu, mine_ini);
