@@ -50,7 +50,7 @@ typedef struct b2orb_keypoint {
  * keys (src/feature-tracker.cpp:8-15; config/euroc.yml:106-112) + workspace sizing. */
 typedef struct b2orb_config {
     int32_t nfeatures;    /* numberOfFeatures */
-    float scale_factor;   /* scaleFactor, must be > 1 */
+    float scale_factor;   /* scaleFactor, 1 < s <= 3 */
     int32_t nlevels;      /* levelPyramid, 1..12 */
     int32_t ini_th_fast;  /* iniThFAST */
     int32_t min_th_fast;  /* minThFAST */

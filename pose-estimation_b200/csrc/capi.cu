@@ -478,7 +478,7 @@ int b2orb_abi_version(void) { return B2ORB_ABI_VERSION; }
 int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
     if (!out || !cfg) return B2ORB_ERR_INVALID;
     *out = nullptr;
-    if (cfg->nfeatures < 1 || cfg->nlevels < 1 || cfg->nlevels > B2_MAX_LEVELS || !(cfg->scale_factor > 1.f) ||
+    if (cfg->nfeatures < 1 || cfg->nlevels < 1 || cfg->nlevels > B2_MAX_LEVELS || !(cfg->scale_factor > 1.f) || cfg->scale_factor > 3.f ||
         cfg->ini_th_fast < 1 || cfg->min_th_fast < 1 || cfg->min_th_fast > cfg->ini_th_fast ||
         cfg->ini_th_fast > 254 || cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_images < 1)
         return B2ORB_ERR_INVALID;
