@@ -99,8 +99,9 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint8_t* score, i
 void b2_launch_fast_cells(const B2Geom& g, const uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
                       B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
-void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,
-                        uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
+void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,
+                        const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
+#define B2_IC_WORDS (4 * 16 * 9 * 2)   // IC_Angle weight table, describe.cu
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s);
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
                              const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,

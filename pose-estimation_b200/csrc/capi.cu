@@ -56,6 +56,7 @@ struct b2orb_handle {
     int *d_cand_cnt = nullptr, *d_sel_cnt = nullptr, *d_nkp = nullptr;
     uint32_t* d_sel = nullptr;
     unsigned* d_ot_scratch = nullptr;
+    unsigned* d_ic_table = nullptr;                      // IC_Angle dp4a weights (describe.cu)
     b2orb_keypoint* d_kps = nullptr;
     uint8_t* d_desc = nullptr;
     int *d_train = nullptr, *d_dist = nullptr, *d_match_l = nullptr, *d_match_r = nullptr, *d_nmatch = nullptr;
@@ -300,6 +301,28 @@ int configure(b2orb_handle* h, int w, int hgt) {
         B2_CUDA(h, cudaMemcpyAsync(h->d_yw[l], yw.data(), yw.size() * 2, cudaMemcpyHostToDevice, h->stream));
         B2_CUDA(h, cudaStreamSynchronize(h->stream));   // host vectors die at scope end
     }
+    {   // IC_Angle weight words (describe.cu): row |v| of the radius-15 disc, read as 9 aligned words starting at
+        // column (cx-15) & ~3; byte i of word k is u = 4k + i - 15 - a, a = (cx-15) & 3.  wu = u inside the disc
+        // (|u| <= umax[|v|], src/ORBextractor.cc:83-100), wm = 1 inside the disc.
+        std::vector<unsigned> tab(B2_IC_WORDS);
+        for (int a = 0; a < 4; ++a)
+            for (int dd = 0; dd < 16; ++dd)
+                for (int k = 0; k < 9; ++k) {
+                    unsigned wu = 0, wm = 0;
+                    for (int i = 0; i < 4; ++i) {
+                        const int u = 4 * k + i - 15 - a;
+                        if (std::abs(u) <= h->umax[dd]) {
+                            wu |= (unsigned)(uint8_t)(int8_t)u << (8 * i);
+                            wm |= 1u << (8 * i);
+                        }
+                    }
+                    tab[((a * 16 + dd) * 9 + k) * 2] = wu;
+                    tab[((a * 16 + dd) * 9 + k) * 2 + 1] = wm;
+                }
+        if (!dev_alloc(h, &h->d_ic_table, tab.size())) return B2ORB_ERR_NOMEM;
+        B2_CUDA(h, cudaMemcpyAsync(h->d_ic_table, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
     h->stage_pitch = (int)align_up((unsigned)w, 32);
     h->stage_img_bytes = (size_t)h->stage_pitch * hgt;
     const size_t cap = g.kp_cap;
@@ -380,7 +403,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     b2_launch_blur(g, im, nimg, s);
     ++h->launches;
     prof_mark(h, B2ORB_K_DESCRIBE);
-    b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
+    b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_ic_table, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
     ++h->launches;
     prof_mark(h, -1);
     B2_CUDA(h, cudaGetLastError());

@@ -86,91 +86,159 @@ __device__ __forceinline__ void glibc_sincosf(float y, float& sn, float& cs) {
 }
 
 constexpr int DS_WARPS = 8;
+constexpr int IC_WORDS = 4 * 16 * 9 * 2;   // [alignment][|v|][word][wu, wm]
 
-__global__ void __launch_bounds__(DS_WARPS * 32)
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned bytes x signed bytes
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+
+constexpr int DS_KPW = 4;            // keypoints per warp (amortises the weight-table copy)
+constexpr int WA_ROWS = 31, WA_WORDS = 9;    // un-blurred window: rows cy-15..cy+15, 36 bytes from (cx-15) & ~3
+constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..cy+18, 40 bytes from (cx-18) & ~3
+
+// The descriptor's 512 single-byte gathers and the orientation's 31 short rows are L1-wavefront bound when done
+// straight from global memory (ncu: lg/mio throttle), so each warp first copies the two windows of its keypoint into
+// shared memory with coalesced 32-bit loads and gathers from there.
+__global__ void __launch_bounds__(DS_WARPS * 32, 3)
 describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
-                const int* __restrict__ sel_cnt, KeyPointOut* __restrict__ kps, uint8_t* __restrict__ desc,
-                int* __restrict__ n_out) {
+                const int* __restrict__ sel_cnt, const unsigned* __restrict__ ic_table, KeyPointOut* __restrict__ kps,
+                uint8_t* __restrict__ desc, int* __restrict__ n_out) {
+    __shared__ unsigned s_ic[IC_WORDS];
+    __shared__ unsigned s_wa[DS_WARPS][WA_ROWS * WA_WORDS];
+    __shared__ unsigned s_wb[DS_WARPS][WB_ROWS * WB_WORDS + 2];
+    // rotated-BRIEF pattern as floats, transposed to [coordinate][lane]: one conflict-free LDS per use instead of a
+    // scattered global byte load + I2F (the quarter-rate XU pipe was the limiter)
+    __shared__ float s_pat[32 * 32];
+    for (int i = threadIdx.x; i < IC_WORDS; i += DS_WARPS * 32) s_ic[i] = ic_table[i];
+    for (int i = threadIdx.x; i < 1024; i += DS_WARPS * 32) s_pat[(i & 31) * 32 + (i >> 5)] = (float)kPattern[i];
+    __syncthreads();
     const int b = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * DS_WARPS + (threadIdx.x >> 5);   // output slot in this image
-    // level of this slot from the per-level counts
-    int level = 0, base = 0, total = 0;
-    bool found = false;
-    for (int l = 0; l < g.nlevels; ++l) {
-        const int c = max(sel_cnt[b * g.nlevels + l], 0);
-        if (!found && slot < total + c) { level = l; base = total; found = true; }
-        total += c;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // per-level counts -> prefix (same for every keypoint of this image)
+    int cnt_l = 0;
+    if (lane < g.nlevels) cnt_l = max(sel_cnt[b * g.nlevels + lane], 0);
+    int pre = cnt_l;                                   // inclusive prefix over levels
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, pre, o);
+        if (lane >= o) pre += v;
     }
-    if (slot == 0 && lane == 0) n_out[b] = min(total, g.kp_cap);
-    if (!found || slot >= g.kp_cap) return;
-    const B2Level& L = g.lv[level];
-    const uint32_t v = sel[(size_t)b * g.sel_total + L.sel_base + (slot - base)];
-    const int cx = (int)(v & 0xFFF) + B2_BORDER, cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
-    const float response = (float)(v >> 24);
+    const int total = __shfl_sync(0xFFFFFFFFu, pre, 15);   // nlevels <= 12: lane 15 holds the sum
+    if (blockIdx.x == 0 && threadIdx.x == 0) n_out[b] = min(total, g.kp_cap);
+    unsigned* wa = s_wa[wid];
+    unsigned* wb = s_wb[wid];
+    const uint8_t* wb8 = reinterpret_cast<const uint8_t*>(wb);
 
-    // ---- IC_Angle on the un-blurred level
-    int pitch;
-    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
-    const uint8_t* center = img + (size_t)cy * pitch + cx;
-    int m01 = 0, m10 = 0;
-    const int u = lane - B2_HALF_PATCH;    // lanes 0..30 -> u = -15..15
-    if (lane < 31) {
-        const int au = abs(u);
-        for (int vv = -B2_HALF_PATCH; vv <= B2_HALF_PATCH; ++vv) {
-            if (au <= g.umax[abs(vv)]) {
-                const int val = center[vv * pitch + u];
-                m10 += u * val;
-                m01 += vv * val;
+    for (int it = 0; it < DS_KPW; ++it) {
+        const int slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;   // output slot in this image
+        if (slot >= total || slot >= g.kp_cap) break;
+        // level = number of levels whose inclusive prefix is <= slot
+        const int level = __popc(__ballot_sync(0xFFFFFFFFu, lane < g.nlevels && pre <= slot));
+        const int base = level ? __shfl_sync(0xFFFFFFFFu, pre, level - 1) : 0;
+        const B2Level& L = g.lv[level];
+        const uint32_t v = sel[(size_t)b * g.sel_total + L.sel_base + (slot - base)];
+        const int cx = (int)(v & 0xFFF) + B2_BORDER, cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
+        const float response = (float)(v >> 24);
+        int pitch;
+        const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
+        const uint8_t* bl = im.blur + (size_t)b * g.slab + L.off;
+        const int bp = L.pitch;
+
+        // ---- stage both windows (all loads first, then the stores)
+        const int ax = (cx - B2_HALF_PATCH) & ~3, a = (cx - B2_HALF_PATCH) & 3;
+        const int bx = (cx - 18) & ~3, ab = (cx - 18) & 3;
+        unsigned ra[9], rb[12];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const int i = lane + 32 * k;
+            const int r = i / WA_WORDS, c = i - r * WA_WORDS;
+            ra[k] = (i < WA_ROWS * WA_WORDS && (c < 8 || a >= 2))
+                        ? *reinterpret_cast<const unsigned*>(img + (size_t)(cy - B2_HALF_PATCH + r) * pitch + ax + 4 * c) : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            const int i = lane + 32 * k;
+            const int r = i / WB_WORDS, c = i - r * WB_WORDS;
+            rb[k] = i < WB_ROWS * WB_WORDS ? *reinterpret_cast<const unsigned*>(bl + (size_t)(cy - 18 + r) * bp + bx + 4 * c) : 0u;
+        }
+        __syncwarp();                                   // previous keypoint's gathers are done
+#pragma unroll
+        for (int k = 0; k < 9; ++k)
+            if (lane + 32 * k < WA_ROWS * WA_WORDS) wa[lane + 32 * k] = ra[k];
+#pragma unroll
+        for (int k = 0; k < 12; ++k)
+            if (lane + 32 * k < WB_ROWS * WB_WORDS) wb[lane + 32 * k] = rb[k];
+        __syncwarp();
+
+        // ---- IC_Angle (src/ORBextractor.cc:77-104): lane = patch row v = lane-15, IDP.4A against per-(alignment, |v|)
+        // weights: wu = u inside the disc |u| <= umax[|v|] (-> m10), wm = 1 inside the disc (-> row sum -> m01)
+        int m01 = 0, m10 = 0;
+        if (lane < 31) {
+            const int vv = lane - B2_HALF_PATCH;
+            const unsigned* tw = s_ic + ((a * 16 + abs(vv)) * 9) * 2;
+            const unsigned* row = wa + lane * WA_WORDS;
+            int rs = 0;
+#pragma unroll
+            for (int k = 0; k < 9; ++k) {
+                const unsigned px = row[k];
+                m10 = dp4a_us(px, (int)tw[2 * k], m10);
+                rs = (int)__dp4a(px, tw[2 * k + 1], (unsigned)rs);
             }
+            m01 = vv * rs;
         }
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
-        m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
+        for (int o = 16; o > 0; o >>= 1) {
+            m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
+            m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
+        }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // ---- descriptor on the blurred level: lane = output byte
-    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
-    float a, bsn;
-    glibc_sincosf(__fmul_rn(angle, factorPI), bsn, a);
-    const uint8_t* bl = im.blur + (size_t)b * g.slab + L.off + (size_t)cy * L.pitch + cx;
-    const int bp = L.pitch;
-    const signed char* pat = kPattern + lane * 32;
-    unsigned val = 0;
+        // ---- descriptor on the blurred window: lane = output byte (src/ORBextractor.cc:108-147)
+        const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+        float ca, sn;
+        glibc_sincosf(__fmul_rn(angle, factorPI), sn, ca);
+        const uint8_t* centre = wb8 + 18 * (WB_WORDS * 4) + 18 + ab;
+        const float* pat = s_pat + lane;
+        unsigned val = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        int t[2];
+        for (int j = 0; j < 8; ++j) {
+            int t[2];
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const float px = (float)pat[4 * j + 2 * e], py = (float)pat[4 * j + 2 * e + 1];
-            const int dy = __float2int_rn(__fadd_rn(__fmul_rn(px, bsn), __fmul_rn(py, a)));
-            const int dx = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bsn)));
-            t[e] = bl[dy * bp + dx];
+            for (int e = 0; e < 2; ++e) {
+                const float px = pat[(4 * j + 2 * e) * 32], py = pat[(4 * j + 2 * e + 1) * 32];
+                // cvRound == round-half-even; |value| <= 18.4, so adding 1.5 * 2^23 rounds exactly like cvtss2si
+                // and leaves the integer in the low mantissa bits (FADD + IADD instead of an XU-pipe F2I)
+                const float fy = __fadd_rn(__fadd_rn(__fmul_rn(px, sn), __fmul_rn(py, ca)), 12582912.f);
+                const float fx = __fadd_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sn)), 12582912.f);
+                const int dy = __float_as_int(fy) - 0x4B400000, dx = __float_as_int(fx) - 0x4B400000;
+                t[e] = centre[dy * (WB_WORDS * 4) + dx];
+            }
+            val |= (unsigned)(t[0] < t[1]) << j;
         }
-        val |= (unsigned)(t[0] < t[1]) << j;
-    }
-    desc[((size_t)b * g.kp_cap + slot) * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        KeyPointOut k;
-        k.x = (float)cx;
-        k.y = (float)cy;
-        if (level != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }
-        k.size = L.kp_size;
-        k.angle = angle;
-        k.response = response;
-        k.octave = level;
-        k.class_id = -1;
-        kps[(size_t)b * g.kp_cap + slot] = k;
+        desc[((size_t)b * g.kp_cap + slot) * 32 + lane] = (uint8_t)val;
+        if (lane == 0) {
+            KeyPointOut k;
+            k.x = (float)cx;
+            k.y = (float)cy;
+            if (level != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }
+            k.size = L.kp_size;
+            k.angle = angle;
+            k.response = response;
+            k.octave = level;
+            k.class_id = -1;
+            kps[(size_t)b * g.kp_cap + slot] = k;
+        }
     }
 }
 
 }  // namespace
 
-void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt, void* kps,
-                        uint8_t* desc, int* n_out, int nimg, cudaStream_t s) {
-    dim3 grid((g.kp_cap + DS_WARPS - 1) / DS_WARPS, nimg);
-    describe_kernel<<<grid, DS_WARPS * 32, 0, s>>>(g, im, sel, sel_cnt, static_cast<KeyPointOut*>(kps), desc, n_out);
+void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,
+                        const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s) {
+    const int per_cta = DS_WARPS * DS_KPW;
+    dim3 grid((g.kp_cap + per_cta - 1) / per_cta, nimg);
+    describe_kernel<<<grid, DS_WARPS * 32, 0, s>>>(g, im, sel, sel_cnt, ic_table, static_cast<KeyPointOut*>(kps), desc, n_out);
 }
