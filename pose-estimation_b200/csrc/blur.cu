@@ -18,7 +18,20 @@
 namespace {
 
 constexpr int BL_WARPS = 4;                 // independent warp tasks per CTA
-constexpr int BL_PF = 5;                    // rows in flight per warp (register ring of 7)
+constexpr int BL_PF = 6;                    // rows in flight per warp
+constexpr int BL_SLOTS = 8;                 // shared-memory ring (>= BL_PF + 2: a slot is rewritten two steps after its last read)
+constexpr int BL_ROWB = 160;                // staged bytes per row: columns [x0-16, x0+144)
+
+// Rows are staged with cp.async (LDGSTS): unlike plain loads, whose completion is tracked by 6 shared scoreboard
+// slots (ncu showed the 5-deep register prefetch waiting on the NEWEST load), async-copy groups complete in
+// order and wait_group N leaves exactly N rows in flight.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ int reflect101_once(int i, int n) {
     // BORDER_REFLECT_101: -i -> i, (n-1)+i -> (n-1)-i.  One bounce is exact for n >= 4 (halo is 3); smaller
@@ -30,15 +43,15 @@ __device__ __forceinline__ int reflect101_once(int i, int n) {
 
 template <bool EDGE>
 __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int spitch, uint8_t* __restrict__ dst,
-                                          int dpitch, int w, int h, int x, int y0, int rows, int lane, bool first_strip,
+                                          int dpitch, int w, int h, int x, int y0, int rows, int lane, uint8_t* ring,
                                           const B2Geom& g) {
-    // ---- per-lane load plan -------------------------------------------------------------------
-    const int wpitch = spitch;                                 // rows are readable up to the pitch
-    const int xo = min(x, wpitch - 4);                         // own word (clamped: lanes right of the row)
-    // lane 0 fetches the word left of the strip, lane 31 the word right of it
-    int xe = -1;
-    if (lane == 0 && !first_strip) xe = x - 4;
-    if (lane == 31) xe = min(x + 4, wpitch - 4);
+    // ---- per-lane load plan: lane c < 10 copies the 16-byte chunk c of every row (skipped outside the row) ----
+    const int x0 = x - lane * 4;                               // strip origin (multiple of 128)
+    const int cb = x0 - 16 + lane * 16;                        // first column of this lane's chunk
+    const bool copier = lane < BL_ROWB / 16 && cb >= 0 && cb + 16 <= spitch;
+    const uint8_t* csrc = src + (copier ? cb : 0);
+    uint8_t* cdst = ring + lane * 16;
+    const unsigned* myw = reinterpret_cast<const unsigned*>(ring + 16 + lane * 4);   // own word inside a ring row
 
     // ---- border selectors (EDGE strips only) --------------------------------------------------
     // Column c = x-4+j (j = 0..11) must read reflect101(c).  Needed columns always resolve inside the lane's
@@ -81,32 +94,26 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
 
     // ---- row pipeline -------------------------------------------------------------------------
     const int nsteps = rows + 6;
-    unsigned raw[7], rex[7];
     int hw[7][4];
 #pragma unroll
     for (int i = 0; i < BL_PF; ++i) {
-        if (i < nsteps) {
-            const uint8_t* rp = src + (size_t)reflect101_once(y0 - 3 + i, h) * spitch;
-            raw[i] = *reinterpret_cast<const unsigned*>(rp + xo);
-            rex[i] = xe >= 0 ? *reinterpret_cast<const unsigned*>(rp + xe) : 0u;
-        }
+        if (i < nsteps && copier) cp_async16(cdst + i * BL_ROWB, csrc + (size_t)reflect101_once(y0 - 3 + i, h) * spitch);
+        cp_async_commit();
     }
     for (int base = 0; base < nsteps; base += 7) {
 #pragma unroll
         for (int p = 0; p < 7; ++p) {
             const int r = base + p;
             if (r < nsteps) {
-                // prefetch row r + BL_PF into ring slot (p + BL_PF) % 7
-                if (r + BL_PF < nsteps) {
-                    const uint8_t* rp = src + (size_t)reflect101_once(y0 - 3 + r + BL_PF, h) * spitch;
-                    raw[(p + BL_PF) % 7] = *reinterpret_cast<const unsigned*>(rp + xo);
-                    rex[(p + BL_PF) % 7] = xe >= 0 ? *reinterpret_cast<const unsigned*>(rp + xe) : 0u;
-                }
-                const unsigned R1 = raw[p];
-                unsigned R0 = __shfl_up_sync(0xFFFFFFFFu, R1, 1);
-                unsigned R2 = __shfl_down_sync(0xFFFFFFFFu, R1, 1);
-                if (lane == 0) R0 = rex[p];
-                if (lane == 31) R2 = rex[p];
+                // prefetch row r + BL_PF (always commit, possibly an empty group, so the wait count stays fixed)
+                if (r + BL_PF < nsteps && copier)
+                    cp_async16(cdst + ((r + BL_PF) & (BL_SLOTS - 1)) * BL_ROWB,
+                               csrc + (size_t)reflect101_once(y0 - 3 + r + BL_PF, h) * spitch);
+                cp_async_commit();
+                cp_async_wait<BL_PF>();                        // row r has landed (for this lane's chunk)
+                __syncwarp();                                  // ... and for every other lane's
+                const unsigned* rw = myw + (r & (BL_SLOTS - 1)) * (BL_ROWB / 4);
+                const unsigned R0 = rw[-1], R1 = rw[0], R2 = rw[1];
                 unsigned W0 = R0, W1 = R1, W2 = R2;
                 if (EDGE) {
                     W0 = __byte_perm(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
@@ -140,6 +147,7 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
 
 __global__ void __launch_bounds__(BL_WARPS * 32)
 blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
+    __shared__ __align__(16) uint8_t s_ring[BL_WARPS][BL_SLOTS * BL_ROWB];
     const int lane = threadIdx.x & 31;
     const int task = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
     if (task >= g.total_blur_tasks) return;
@@ -158,8 +166,9 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
 
     // a strip needs the border code if it touches column 0 or its last lane's halo reaches beyond w-1
     const bool edge = strip == 0 || strip * 128 + 128 + 3 > L.w - 1;
-    if (edge) blur_task<true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, strip == 0, g);
-    else blur_task<false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, false, g);
+    uint8_t* ring = s_ring[threadIdx.x >> 5];
+    if (edge) blur_task<true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+    else blur_task<false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
 }
 
 }  // namespace
