@@ -22,6 +22,7 @@ namespace {
 
 constexpr int OT_THREADS = 512;
 constexpr int OT_MAX_ROOTS = 256;
+constexpr int OT_ILP = 4;
 
 struct OtShared {
     unsigned warp_sums[OT_THREADS / 32];
@@ -100,12 +101,22 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
     }
     __syncthreads();
     // 2. child point counts of every candidate
-    for (int p = tid; p < M; p += OT_THREADS) {
-        const int n = pnode[p];
-        const B2Node nd = cur[n];
-        if (nd.cnt > 1) {
-            const uint32_t v = pts[p];
-            atomicAdd(&cc[4 * n + quadrant(nd, v & 0xFFF, (v >> 12) & 0xFFF)], 1u);
+    // (point loops are batched OT_ILP deep: the passes are chains of dependent L2 loads, so the loads of several
+    //  points are issued before any of them is used)
+    for (int p0 = tid; p0 < M; p0 += OT_ILP * OT_THREADS) {
+        int nn[OT_ILP];
+        uint32_t vv[OT_ILP];
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            const int p = p0 + k * OT_THREADS;
+            nn[k] = p < M ? (int)pnode[p] : -1;
+            vv[k] = p < M ? pts[p] : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            if (nn[k] < 0) continue;
+            const B2Node nd = cur[nn[k]];
+            if (nd.cnt > 1) atomicAdd(&cc[4 * nn[k] + quadrant(nd, vv[k] & 0xFFF, (vv[k] >> 12) & 0xFFF)], 1u);
         }
     }
     __syncthreads();
@@ -205,13 +216,22 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
     if (multi) atomicAdd(&sh.n_multi, multi);
     __syncthreads();
     // 7. move the points
-    for (int p = tid; p < M; p += OT_THREADS) {
-        const int n = pnode[p];
-        const int np = newpos[n];
-        if (np >= 0) pnode[p] = (unsigned short)np;
-        else {
-            const uint32_t v = pts[p];
-            pnode[p] = (unsigned short)cpos[4 * n + quadrant(cur[n], v & 0xFFF, (v >> 12) & 0xFFF)];
+    for (int p0 = tid; p0 < M; p0 += OT_ILP * OT_THREADS) {
+        int nn[OT_ILP];
+        uint32_t vv[OT_ILP];
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            const int p = p0 + k * OT_THREADS;
+            nn[k] = p < M ? (int)pnode[p] : -1;
+            vv[k] = p < M ? pts[p] : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            if (nn[k] < 0) continue;
+            const int n = nn[k];
+            const int np = newpos[n];
+            pnode[p0 + k * OT_THREADS] =
+                (unsigned short)(np >= 0 ? np : cpos[4 * n + quadrant(cur[n], vv[k] & 0xFFF, (vv[k] >> 12) & 0xFFF)]);
         }
     }
     __syncthreads();
@@ -318,12 +338,24 @@ octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ can
     for (int i = tid; i < sh.lsz; i += OT_THREADS) best[i] = 0;
     __syncthreads();
     const int wc = L.w_cell, hc = L.h_cell, ncol = L.n_cols;
-    for (int p = tid; p < M; p += OT_THREADS) {
-        const uint32_t v = pts[p];
-        const int x = (int)(v & 0xFFF) - 3, y = (int)((v >> 12) & 0xFFF) - 3;
-        const int cj = x / wc, ci = y / hc;
-        const unsigned key = (unsigned)(((ci * ncol + cj) * hc + (y - ci * hc)) * wc + (x - cj * wc));
-        atomicMax(&best[pnode[p]], (v & 0xFF000000u) | (0x00FFFFFFu - key));
+    for (int p0 = tid; p0 < M; p0 += OT_ILP * OT_THREADS) {
+        int nn[OT_ILP];
+        uint32_t vv[OT_ILP];
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            const int p = p0 + k * OT_THREADS;
+            nn[k] = p < M ? (int)pnode[p] : -1;
+            vv[k] = p < M ? pts[p] : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < OT_ILP; ++k) {
+            if (nn[k] < 0) continue;
+            const uint32_t v = vv[k];
+            const int x = (int)(v & 0xFFF) - 3, y = (int)((v >> 12) & 0xFFF) - 3;
+            const int cj = x / wc, ci = y / hc;
+            const unsigned key = (unsigned)(((ci * ncol + cj) * hc + (y - ci * hc)) * wc + (x - cj * wc));
+            atomicMax(&best[nn[k]], (v & 0xFF000000u) | (0x00FFFFFFu - key));
+        }
     }
     __syncthreads();
     for (int i = tid; i < lsz; i += OT_THREADS) {

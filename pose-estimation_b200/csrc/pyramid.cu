@@ -9,89 +9,128 @@
 namespace {
 
 constexpr int RS_WARPS = 4;     // independent warp tasks per CTA
-constexpr int RS_BAND = 32;     // output rows per task
+constexpr int RS_PF = 4;        // source rows in flight per warp
+constexpr int RS_SLOTS = 8;     // shared-memory ring (>= RS_PF + 2)
+constexpr int RS_ROWB = 512;    // staged bytes per source row: one 16-byte chunk per lane (scale <= 3 -> <= 26 chunks)
+
+__device__ __forceinline__ void rs_cp_async16(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void rs_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void rs_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // One WARP owns a 128-px wide strip of the destination level (4 px per lane) and walks down RS_BAND output rows.
+// The source rows it needs are streamed through a cp.async shared-memory ring (deep, in-order prefetch).
 // Horizontal pass of one source row for the lane's 4 pixels: the two source bytes of pixel j are cut out of two
 // aligned words with one PRMT (selector fixed per lane) and combined with one IDP.2A against the packed Q11
-// weights (a0 | a1 << 16).  A source row is interpolated once and reused by the 1-2 output rows that need it
-// (H0/H1 registers).  Vertical pass: two IMAD.HI with the weights pre-shifted by 16, one add, and the rounding
-// shift is folded into a multiply by 64 so the result byte can be picked with PRMT.
+// weights (a0 | a1 << 16).  Every source row is interpolated once and used by the 1-2 output rows that need it.
+// Vertical pass: two IMAD.HI with the weights pre-shifted by 16, one add; the rounding shift is folded into a
+// multiply by 64 so the result byte can be picked with PRMT.
 __global__ void __launch_bounds__(RS_WARPS * 32)
-resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, const int* __restrict__ xofs,
-              const short* __restrict__ xw, const int* __restrict__ yofs, const short* __restrict__ yw) {
+resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, int band_rows,
+              const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
+              const short* __restrict__ yw) {
+    __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
     const B2Level& L = g.lv[level];
     const int lane = threadIdx.x & 31;
     const int strips = (L.w + 127) >> 7;
     const int task = blockIdx.x * RS_WARPS + (threadIdx.x >> 5);
     const int band = task / strips, strip = task - band * strips;
-    const int dy0 = band * RS_BAND;
+    const int dy0 = band * band_rows;
     if (dy0 >= L.h) return;
-    const int dy1 = min(dy0 + RS_BAND, L.h);
+    const int dy1 = min(dy0 + band_rows, L.h);
     const int b = blockIdx.y;
     int spitch;
     const uint8_t* src = b2_level_ptr(g, im, b, level - 1, spitch);
     const int sh = g.lv[level - 1].h;
     uint8_t* dst = im.pyr + (size_t)b * g.slab + L.off;
     const int dx0 = strip * 128 + lane * 4;
+    uint8_t* ring = s_ring[threadIdx.x >> 5];
+
+    // source span of the strip, 16-byte aligned; lane c copies chunk c of every source row
+    const int gx0 = xofs[strip * 128] & ~15;
+    const int gx1 = xofs[min(strip * 128 + 127, L.w - 1)] + 2;           // one past the last byte used
+    const int cb = gx0 + lane * 16;
+    const bool copier = cb < gx1 && cb + 16 <= spitch;
+    const uint8_t* csrc = src + (copier ? cb : 0);
+    uint8_t* cdst = ring + lane * 16;
 
     // per-lane horizontal plan
     unsigned A[4], sel[4];
-    int base01, base23;
+    int o01, o23;                                                         // ring-row byte offsets of the two word pairs
     {
         int sx[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int dx = min(dx0 + j, L.w - 1);
-            sx[j] = xofs[dx];
+            sx[j] = xofs[dx] - gx0;
             A[j] = (unsigned)(unsigned short)xw[2 * dx] | ((unsigned)(unsigned short)xw[2 * dx + 1] << 16);
         }
-        base01 = sx[0] & ~3;
-        base23 = sx[2] & ~3;
-        // downscaling by <= 2 per level: sx[1] - base01 <= 5 and sx[3] - base23 <= 5, so both bytes of a pixel
-        // sit in the 8 bytes starting at its base (a larger step would need more words: rejected at create)
+        o01 = sx[0] & ~3;
+        o23 = sx[2] & ~3;
+        // scale <= 3: sx[1] - o01 <= 6 and sx[3] - o23 <= 6, so both bytes of a pixel sit in the 8 bytes at its base
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const int o = min(sx[j] - (j < 2 ? base01 : base23), 6);
+            const int o = min(sx[j] - (j < 2 ? o01 : o23), 6);
             sel[j] = (unsigned)o | ((unsigned)(o + 1) << 4);
         }
+        o01 = min(o01, RS_ROWB - 8);
+        o23 = min(o23, RS_ROWB - 8);
     }
-    const int o0a = base01, o0b = min(base01 + 4, spitch - 4), o1a = base23, o1b = min(base23 + 4, spitch - 4);
 
-    int cur0 = -1, cur1 = -1;
-    unsigned H0[4], H1[4];
-    auto hrow = [&](int s, unsigned (&H)[4]) {
-        const uint8_t* r = src + (size_t)s * spitch;
-        const unsigned w0 = *reinterpret_cast<const unsigned*>(r + o0a), w1 = *reinterpret_cast<const unsigned*>(r + o0b);
-        const unsigned v0 = *reinterpret_cast<const unsigned*>(r + o1a), v1 = *reinterpret_cast<const unsigned*>(r + o1b);
-        H[0] = __dp2a_lo(A[0], __byte_perm(w0, w1, sel[0]), 0u) >> 4;
-        H[1] = __dp2a_lo(A[1], __byte_perm(w0, w1, sel[1]), 0u) >> 4;
-        H[2] = __dp2a_lo(A[2], __byte_perm(v0, v1, sel[2]), 0u) >> 4;
-        H[3] = __dp2a_lo(A[3], __byte_perm(v0, v1, sel[3]), 0u) >> 4;
-    };
-    for (int dy = dy0; dy < dy1; ++dy) {
-        const int sy = yofs[dy];
-        const int s1 = min(sy + 1, sh - 1);
-        const unsigned b0 = (unsigned)yw[2 * dy] << 16, b1 = (unsigned)yw[2 * dy + 1] << 16;
-        if (sy != cur0) {
-            if (sy == cur1) {
+    const int s_first = yofs[dy0];
+    const int s_last = min(yofs[dy1 - 1] + 1, sh - 1);
+    const int nrows = s_last - s_first + 1;
+#pragma unroll
+    for (int i = 0; i < RS_PF; ++i) {
+        if (i < nrows && copier) rs_cp_async16(cdst + i * RS_ROWB, csrc + (size_t)(s_first + i) * spitch);
+        rs_commit();
+    }
+    unsigned H0[4] = {0, 0, 0, 0}, H1[4] = {0, 0, 0, 0};
+    int dy = dy0;
+    int sy = s_first;                                                     // yofs[dy]
+    unsigned b0 = (unsigned)yw[2 * dy] << 16, b1 = (unsigned)yw[2 * dy + 1] << 16;
+    for (int i = 0; i < nrows; ++i) {
+        const int s = s_first + i;
+        if (i + RS_PF < nrows && copier)
+            rs_cp_async16(cdst + ((i + RS_PF) & (RS_SLOTS - 1)) * RS_ROWB, csrc + (size_t)(s + RS_PF) * spitch);
+        rs_commit();
+        rs_wait<RS_PF>();
+        __syncwarp();
+        const uint8_t* row = ring + (i & (RS_SLOTS - 1)) * RS_ROWB;
+        const uint2 wa = make_uint2(*reinterpret_cast<const unsigned*>(row + o01), *reinterpret_cast<const unsigned*>(row + o01 + 4));
+        const uint2 wb = make_uint2(*reinterpret_cast<const unsigned*>(row + o23), *reinterpret_cast<const unsigned*>(row + o23 + 4));
+#pragma unroll
+        for (int j = 0; j < 4; ++j) H0[j] = H1[j];
+        H1[0] = __dp2a_lo(A[0], __byte_perm(wa.x, wa.y, sel[0]), 0u) >> 4;
+        H1[1] = __dp2a_lo(A[1], __byte_perm(wa.x, wa.y, sel[1]), 0u) >> 4;
+        H1[2] = __dp2a_lo(A[2], __byte_perm(wb.x, wb.y, sel[2]), 0u) >> 4;
+        H1[3] = __dp2a_lo(A[3], __byte_perm(wb.x, wb.y, sel[3]), 0u) >> 4;
+        // emit the output rows whose pair is (s-1, s); on the last source row also those clamped to (s, s)
+#pragma unroll 1
+        for (int pass = 0; pass < 2; ++pass) {
+            const int want = pass == 0 ? s - 1 : s;
+            if (pass == 1) {
+                if (s != sh - 1) break;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) H0[j] = H1[j];
-            } else hrow(sy, H0);
-            cur0 = sy;
-        }
-        if (s1 != cur1) {
-            if (s1 == cur0) {
+            }
+            while (dy < dy1 && sy == want) {
+                unsigned u[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) H1[j] = H0[j];
-            } else hrow(s1, H1);
-            cur1 = s1;
+                for (int j = 0; j < 4; ++j) u[j] = (__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) * 64u;   // byte 1 = (..)>>2
+                const unsigned lo = __byte_perm(u[0], u[1], 0x0051), hi = __byte_perm(u[2], u[3], 0x0051);
+                if (dx0 < L.w) *reinterpret_cast<unsigned*>(dst + (size_t)dy * L.pitch + dx0) = __byte_perm(lo, hi, 0x5410);
+                ++dy;
+                if (dy < dy1) {
+                    sy = yofs[dy];
+                    b0 = (unsigned)yw[2 * dy] << 16;
+                    b1 = (unsigned)yw[2 * dy + 1] << 16;
+                }
+            }
         }
-        unsigned u[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) u[j] = (__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) * 64u;   // byte 1 = (..)>>2
-        const unsigned lo = __byte_perm(u[0], u[1], 0x0051), hi = __byte_perm(u[2], u[3], 0x0051);
-        if (dx0 < L.w) *reinterpret_cast<unsigned*>(dst + (size_t)dy * L.pitch + dx0) = __byte_perm(lo, hi, 0x5410);
     }
 }
 
@@ -117,9 +156,14 @@ repack_kernel(const uint8_t* __restrict__ src, int step, size_t stride, uint8_t*
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s) {
     const B2Level& L = g.lv[level];
-    const int tasks = ((L.w + 127) / 128) * ((L.h + RS_BAND - 1) / RS_BAND);
+    // A task is one latency chain (a row every few hundred cycles), so the band shrinks until the launch has
+    // enough warps to fill the machine (148 SMs x 48 warps); 32 rows amortise the per-task setup best.
+    const int strips = (L.w + 127) / 128;
+    int band = 32;
+    while (band > 4 && (long long)strips * ((L.h + band - 1) / band) * nimg < 148 * 48) band >>= 1;
+    const int tasks = strips * ((L.h + band - 1) / band);
     dim3 grid((tasks + RS_WARPS - 1) / RS_WARPS, nimg);
-    resize_kernel<<<grid, RS_WARPS * 32, 0, s>>>(g, im, level, xofs, xw, yofs, yw);
+    resize_kernel<<<grid, RS_WARPS * 32, 0, s>>>(g, im, level, band, xofs, xw, yofs, yw);
 }
 
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
