@@ -6,12 +6,13 @@
 //
 // The kernel is instruction-issue bound, not HBM bound, so it is organised around instructions per pixel:
 // one WARP owns a 128-px wide strip (4 px per lane) and marches down a band of rows.  Per input row a lane
-// does one 32-bit load, gets its left/right neighbour words by shuffle, and computes the 4 horizontal sums
-// with 10 IDP.4A (u8x4 dot products against shifted tap vectors — no byte unpacking at all).  The vertical
-// pass keeps the last 7 horizontal rows in registers (7-phase unrolled rotation) and uses tap symmetry:
-// 3 IADD + 4 IMAD per pixel, which also balances the ALU and FMA pipes.  Results are packed with 3 PRMT and
-// stored as one 32-bit word.  Rows are prefetched BL_PF deep in registers.  Image borders (reflect-101) are
-// folded into per-lane PRMT selectors computed once per strip; interior strips skip that code entirely.
+// reads its own word and its two neighbours from a shared-memory ring the warp fills with cp.async (10 lanes
+// copy one 16-byte chunk each, BL_PF rows in flight), and computes the 4 horizontal sums with 10 IDP.4A (u8x4
+// dot products against shifted tap vectors — no byte unpacking at all).  The vertical pass keeps the last 7
+// horizontal rows in registers (7-phase unrolled rotation) and uses tap symmetry: 3 IADD + 4 IMAD per pixel,
+// which also balances the ALU and FMA pipes.  Results are packed with 3 PRMT and stored as one 32-bit word.
+// Image borders (reflect-101) are folded into per-lane PRMT selectors computed once per strip; interior strips
+// skip that code entirely.
 // One launch covers all levels of all images: blockIdx.x walks a flattened (level, band, strip) task list.
 #include "b2orb_internal.cuh"
 
@@ -25,9 +26,8 @@ constexpr int BL_ROWB = 160;                // staged bytes per row: columns [x0
 // Rows are staged with cp.async (LDGSTS): unlike plain loads, whose completion is tracked by 6 shared scoreboard
 // slots (ncu showed the 5-deep register prefetch waiting on the NEWEST load), async-copy groups complete in
 // order and wait_group N leaves exactly N rows in flight.
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+__device__ __forceinline__ void cp_async16(unsigned smem_addr, const void* gmem) {   // smem_addr: shared-window address
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -50,7 +50,7 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
     const int cb = x0 - 16 + lane * 16;                        // first column of this lane's chunk
     const bool copier = lane < BL_ROWB / 16 && cb >= 0 && cb + 16 <= spitch;
     const uint8_t* csrc = src + (copier ? cb : 0);
-    uint8_t* cdst = ring + lane * 16;
+    const unsigned cdst = (unsigned)__cvta_generic_to_shared(ring) + lane * 16;   // converted once, not per row
     const unsigned* myw = reinterpret_cast<const unsigned*>(ring + 16 + lane * 4);   // own word inside a ring row
 
     // ---- border selectors (EDGE strips only) --------------------------------------------------

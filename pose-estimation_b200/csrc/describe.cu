@@ -131,6 +131,8 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     unsigned* wa = s_wa[wid];
     unsigned* wb = s_wb[wid];
     const uint8_t* wb8 = reinterpret_cast<const uint8_t*>(wb);
+    const int ra_row = lane / 9, ra_col = lane - ra_row * 9;      // staging roles (fixed per lane)
+    const int rb_row = lane / 10, rb_col = lane - rb_row * 10;
 
     for (int it = 0; it < DS_KPW; ++it) {
         const int slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;   // output slot in this image
@@ -150,27 +152,32 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
         // ---- stage both windows (all loads first, then the stores)
         const int ax = (cx - B2_HALF_PATCH) & ~3, a = (cx - B2_HALF_PATCH) & 3;
         const int bx = (cx - 18) & ~3, ab = (cx - 18) & 3;
-        unsigned ra[9], rb[12];
+        // lane -> (row within a group of 3, word column): 27 lanes x 11 groups cover the 31 x 9 window A,
+        // 30 lanes x 13 groups the 37 x 10 window B; no per-element index arithmetic
+        unsigned ra[11], rb[13];
+        {
+            const uint8_t* pa = img + (size_t)(cy - B2_HALF_PATCH + ra_row) * pitch + ax + 4 * ra_col;
+            const bool oka = lane < 27 && (ra_col < 8 || a >= 2);
 #pragma unroll
-        for (int k = 0; k < 9; ++k) {
-            const int i = lane + 32 * k;
-            const int r = i / WA_WORDS, c = i - r * WA_WORDS;
-            ra[k] = (i < WA_ROWS * WA_WORDS && (c < 8 || a >= 2))
-                        ? *reinterpret_cast<const unsigned*>(img + (size_t)(cy - B2_HALF_PATCH + r) * pitch + ax + 4 * c) : 0u;
-        }
+            for (int k = 0; k < 11; ++k) {
+                ra[k] = (oka && 3 * k + ra_row < WA_ROWS) ? *reinterpret_cast<const unsigned*>(pa) : 0u;
+                pa += 3 * pitch;
+            }
+            const uint8_t* pb = bl + (size_t)(cy - 18 + rb_row) * bp + bx + 4 * rb_col;
+            const bool okb = lane < 30;
 #pragma unroll
-        for (int k = 0; k < 12; ++k) {
-            const int i = lane + 32 * k;
-            const int r = i / WB_WORDS, c = i - r * WB_WORDS;
-            rb[k] = i < WB_ROWS * WB_WORDS ? *reinterpret_cast<const unsigned*>(bl + (size_t)(cy - 18 + r) * bp + bx + 4 * c) : 0u;
+            for (int k = 0; k < 13; ++k) {
+                rb[k] = (okb && 3 * k + rb_row < WB_ROWS) ? *reinterpret_cast<const unsigned*>(pb) : 0u;
+                pb += 3 * bp;
+            }
         }
         __syncwarp();                                   // previous keypoint's gathers are done
 #pragma unroll
-        for (int k = 0; k < 9; ++k)
-            if (lane + 32 * k < WA_ROWS * WA_WORDS) wa[lane + 32 * k] = ra[k];
+        for (int k = 0; k < 11; ++k)
+            if (lane < 27 && 3 * k + ra_row < WA_ROWS) wa[(3 * k + ra_row) * WA_WORDS + ra_col] = ra[k];
 #pragma unroll
-        for (int k = 0; k < 12; ++k)
-            if (lane + 32 * k < WB_ROWS * WB_WORDS) wb[lane + 32 * k] = rb[k];
+        for (int k = 0; k < 13; ++k)
+            if (lane < 30 && 3 * k + rb_row < WB_ROWS) wb[(3 * k + rb_row) * WB_WORDS + rb_col] = rb[k];
         __syncwarp();
 
         // ---- IC_Angle (src/ORBextractor.cc:77-104): lane = patch row v = lane-15, IDP.4A against per-(alignment, |v|)

@@ -13,9 +13,13 @@ constexpr int RS_PF = 4;        // source rows in flight per warp
 constexpr int RS_SLOTS = 8;     // shared-memory ring (>= RS_PF + 2)
 constexpr int RS_ROWB = 512;    // staged bytes per source row: one 16-byte chunk per lane (scale <= 3 -> <= 26 chunks)
 
-__device__ __forceinline__ void rs_cp_async16(void* smem, const void* gmem) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+__device__ __forceinline__ void rs_cp_async16(unsigned smem_addr, const void* gmem) {   // shared-window address
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ unsigned rs_lds(unsigned smem_addr) {
+    unsigned v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr));
+    return v;
 }
 __device__ __forceinline__ void rs_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -54,12 +58,12 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
     const int gx1 = xofs[min(strip * 128 + 127, L.w - 1)] + 2;           // one past the last byte used
     const int cb = gx0 + lane * 16;
     const bool copier = cb < gx1 && cb + 16 <= spitch;
-    const uint8_t* csrc = src + (copier ? cb : 0);
-    uint8_t* cdst = ring + lane * 16;
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);   // all ring addressing in 32-bit shared space
+    const unsigned cdst = ring_s + lane * 16;
 
     // per-lane horizontal plan
     unsigned A[4], sel[4];
-    int o01, o23;                                                         // ring-row byte offsets of the two word pairs
+    unsigned o01, o23;                                                    // ring-row byte offsets of the two word pairs
     {
         int sx[4];
 #pragma unroll
@@ -68,67 +72,74 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
             sx[j] = xofs[dx] - gx0;
             A[j] = (unsigned)(unsigned short)xw[2 * dx] | ((unsigned)(unsigned short)xw[2 * dx + 1] << 16);
         }
-        o01 = sx[0] & ~3;
-        o23 = sx[2] & ~3;
-        // scale <= 3: sx[1] - o01 <= 6 and sx[3] - o23 <= 6, so both bytes of a pixel sit in the 8 bytes at its base
+        const int b01 = sx[0] & ~3, b23 = sx[2] & ~3;
+        // scale <= 3: sx[1] - b01 <= 6 and sx[3] - b23 <= 6, so both bytes of a pixel sit in the 8 bytes at its base
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const int o = min(sx[j] - (j < 2 ? o01 : o23), 6);
+            const int o = min(sx[j] - (j < 2 ? b01 : b23), 6);
             sel[j] = (unsigned)o | ((unsigned)(o + 1) << 4);
         }
-        o01 = min(o01, RS_ROWB - 8);
-        o23 = min(o23, RS_ROWB - 8);
+        o01 = ring_s + (unsigned)min(b01, RS_ROWB - 8);
+        o23 = ring_s + (unsigned)min(b23, RS_ROWB - 8);
     }
 
     const int s_first = yofs[dy0];
     const int s_last = min(yofs[dy1 - 1] + 1, sh - 1);
     const int nrows = s_last - s_first + 1;
+    const uint8_t* gsrc = src + (size_t)s_first * spitch + (copier ? cb : 0);   // next source row to issue
+    int issued = 0;
 #pragma unroll
     for (int i = 0; i < RS_PF; ++i) {
-        if (i < nrows && copier) rs_cp_async16(cdst + i * RS_ROWB, csrc + (size_t)(s_first + i) * spitch);
+        if (issued < nrows && copier) rs_cp_async16(cdst + i * RS_ROWB, gsrc);
         rs_commit();
+        gsrc += spitch;
+        ++issued;
     }
     unsigned H0[4] = {0, 0, 0, 0}, H1[4] = {0, 0, 0, 0};
-    int dy = dy0;
-    int sy = s_first;                                                     // yofs[dy]
-    unsigned b0 = (unsigned)yw[2 * dy] << 16, b1 = (unsigned)yw[2 * dy + 1] << 16;
-    for (int i = 0; i < nrows; ++i) {
-        const int s = s_first + i;
-        if (i + RS_PF < nrows && copier)
-            rs_cp_async16(cdst + ((i + RS_PF) & (RS_SLOTS - 1)) * RS_ROWB, csrc + (size_t)(s + RS_PF) * spitch);
+    uint8_t* dptr = dst + (size_t)dy0 * L.pitch + dx0;                    // next output row of this lane
+    const bool store = dx0 < L.w;
+    const int* yo = yofs + dy0;
+    const short* ywp = yw + 2 * dy0;
+    int left = dy1 - dy0;                                                 // output rows still to emit
+    int sy = s_first;                                                     // source row of the next output row
+    unsigned b0 = (unsigned)ywp[0] << 16, b1 = (unsigned)ywp[1] << 16;
+    unsigned slot = 0;                                                    // ring byte offset of source row s
+    for (int s = s_first; s <= s_last; ++s) {
+        if (issued < nrows && copier) rs_cp_async16(cdst + ((slot + RS_PF * RS_ROWB) & (RS_SLOTS * RS_ROWB - 1)), gsrc);
         rs_commit();
+        gsrc += spitch;
+        ++issued;
         rs_wait<RS_PF>();
         __syncwarp();
-        const uint8_t* row = ring + (i & (RS_SLOTS - 1)) * RS_ROWB;
-        const uint2 wa = make_uint2(*reinterpret_cast<const unsigned*>(row + o01), *reinterpret_cast<const unsigned*>(row + o01 + 4));
-        const uint2 wb = make_uint2(*reinterpret_cast<const unsigned*>(row + o23), *reinterpret_cast<const unsigned*>(row + o23 + 4));
+        const unsigned wa0 = rs_lds(o01 + slot), wa1 = rs_lds(o01 + slot + 4);
+        const unsigned wb0 = rs_lds(o23 + slot), wb1 = rs_lds(o23 + slot + 4);
+        slot = (slot + RS_ROWB) & (RS_SLOTS * RS_ROWB - 1);
 #pragma unroll
         for (int j = 0; j < 4; ++j) H0[j] = H1[j];
-        H1[0] = __dp2a_lo(A[0], __byte_perm(wa.x, wa.y, sel[0]), 0u) >> 4;
-        H1[1] = __dp2a_lo(A[1], __byte_perm(wa.x, wa.y, sel[1]), 0u) >> 4;
-        H1[2] = __dp2a_lo(A[2], __byte_perm(wb.x, wb.y, sel[2]), 0u) >> 4;
-        H1[3] = __dp2a_lo(A[3], __byte_perm(wb.x, wb.y, sel[3]), 0u) >> 4;
-        // emit the output rows whose pair is (s-1, s); on the last source row also those clamped to (s, s)
-#pragma unroll 1
-        for (int pass = 0; pass < 2; ++pass) {
-            const int want = pass == 0 ? s - 1 : s;
-            if (pass == 1) {
-                if (s != sh - 1) break;
+        H1[0] = __dp2a_lo(A[0], __byte_perm(wa0, wa1, sel[0]), 0u) >> 4;
+        H1[1] = __dp2a_lo(A[1], __byte_perm(wa0, wa1, sel[1]), 0u) >> 4;
+        H1[2] = __dp2a_lo(A[2], __byte_perm(wb0, wb1, sel[2]), 0u) >> 4;
+        H1[3] = __dp2a_lo(A[3], __byte_perm(wb0, wb1, sel[3]), 0u) >> 4;
+        // emit the output rows whose source pair is (s-1, s); on the last source row of the level also those clamped
+        // to (s, s) (their second weight is 0)
+        const bool last = s == sh - 1;
+        while (left > 0 && (sy == s - 1 || (last && sy == s))) {
+            unsigned u[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) H0[j] = H1[j];
+            for (int j = 0; j < 4; ++j) {
+                const unsigned h0 = sy == s ? H1[j] : H0[j];
+                u[j] = (__umulhi(b0, h0) + __umulhi(b1, H1[j]) + 2u) * 64u;                   // byte 1 = (..) >> 2
             }
-            while (dy < dy1 && sy == want) {
-                unsigned u[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) u[j] = (__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) * 64u;   // byte 1 = (..)>>2
-                const unsigned lo = __byte_perm(u[0], u[1], 0x0051), hi = __byte_perm(u[2], u[3], 0x0051);
-                if (dx0 < L.w) *reinterpret_cast<unsigned*>(dst + (size_t)dy * L.pitch + dx0) = __byte_perm(lo, hi, 0x5410);
-                ++dy;
-                if (dy < dy1) {
-                    sy = yofs[dy];
-                    b0 = (unsigned)yw[2 * dy] << 16;
-                    b1 = (unsigned)yw[2 * dy + 1] << 16;
-                }
+            const unsigned lo = __byte_perm(u[0], u[1], 0x0051), hi = __byte_perm(u[2], u[3], 0x0051);
+            if (store) *reinterpret_cast<unsigned*>(dptr) = __byte_perm(lo, hi, 0x5410);
+            dptr += L.pitch;
+            --left;
+            ++yo;
+            ywp += 2;
+            if (left > 0) {
+                sy = *yo;
+                b0 = (unsigned)ywp[0] << 16;
+                b1 = (unsigned)ywp[1] << 16;
             }
         }
     }
