@@ -121,6 +121,7 @@ def main():
     ap.add_argument("--no-temporal", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")
     args = ap.parse_args()
 
@@ -233,8 +234,8 @@ def main():
     prof_pairs = Bs
 
     # ---------------- e2e: host buffers through the C ABI, copies inside ----------------
-    nh = 2
-    Be = max(B // 2, 1)
+    nh = max(args.e2e_threads, 1)
+    Be = B                                            # pairs per C-ABI call (one value-leg step), per host thread
     handles = [fe.Handle(*cfg, w, h, max_images=2 * Be, device=local) for _ in range(nh)]
     pin_l = fe.pinned_empty(ls.shape); pin_l[...] = ls
     pin_r = fe.pinned_empty(rs.shape); pin_r[...] = rs
@@ -273,6 +274,20 @@ def main():
     e2e_value = world * nh * Be * e2e_steps / float(te.item())
     clocks = sampler.stop() if sampler else None
 
+    # context for the e2e number: what the host link delivers for a plain pinned H2D copy of one call's images
+    link_src = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
+    link_dst = torch.empty_like(link_src, device="cuda")
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    link_dst.copy_(link_src, non_blocking=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(4):
+        link_dst.copy_(link_src, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = 4 * link_src.numel() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    del link_src, link_dst
+
     # per-GPU result summaries are the only thing gathered (north star: no collective on the hot path)
     summ = torch.tensor([sum(c[0] for c in counts), sum(c[1] for c in counts), sum(c[2] for c in counts)], device="cuda")
     if world > 1:
@@ -303,7 +318,8 @@ def main():
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic", "config": config,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * img_bytes * Be, "d2h_bytes_per_step": d2h_per_pair * Be,
-                "pairs_per_call": Be, "host_threads": nh, "steps": e2e_steps * nh},
+                "pairs_per_call": Be, "host_threads": nh, "steps": e2e_steps * nh,
+                "h2d_link_gbs": round(h2d_gbs, 2), "h2d_link_bound": round(h2d_gbs * 1e9 / (2 * img_bytes), 1)},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -103,6 +103,13 @@ void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel
                         const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
 #define B2_IC_WORDS (4 * 16 * 9 * 2)   // IC_Angle weight table, describe.cu
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s);
+// Problem table of a stereo batch, written on the device so that re-binding never synchronises the host.
+struct B2BindBases {
+    uint8_t *desc, *cur_l, *cur_r;
+    int *nkp, *train, *dist, *nmatch, *tti_l, *tdi_l, *tti_r, *tdi_r;
+    int cap;
+};
+void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStream_t s);
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
                              const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,
                              int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, int npairs,

@@ -2,7 +2,10 @@
 // (src/ORBextractor.cc:410-470), per-size geometry (ComputePyramid sizes :1111-1112, FAST cell grid
 // :773-787, quadtree roots :543-545), workspace, and the launch sequence of one batch.
 // Host C++ only orchestrates; all pixel/descriptor work is in the .cu kernels next to this file.
+#include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstdio>
 #include <cstdint>
 #include <cstring>
@@ -77,6 +80,16 @@ struct b2orb_handle {
     double prof_ms[B2ORB_NUM_KERNELS] = {};
     uint64_t prof_cnt[B2ORB_NUM_KERNELS] = {};
     std::vector<void*> owned;
+    // pipelined host path (b2orb_stereo_frontend with many pairs): the batch is cut into chunks that rotate over
+    // `lanes` (child handles with their own stream + workspace) so the H2D copy of one chunk, the kernels of
+    // another and the D2H copy of a third overlap without any host thread.
+    std::vector<b2orb_handle*> lanes;
+    b2orb_handle* root = nullptr;                        // owning handle (self for a user-created handle)
+    b2orb_handle* hist_owner = nullptr;                  // root only: handle whose slot 0 holds the newest history
+    cudaEvent_t ev_hist = nullptr, ev_done = nullptr;    // history slot written / kernels of the lane's last chunk done
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;       // lane: chunk copied in / results copied out
+    cudaStream_t s_in = nullptr, s_out = nullptr;        // root: copy-in and copy-out streams of the pipelined path
+    int pipe_chunk = 32, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
 namespace {
@@ -360,20 +373,10 @@ int configure(b2orb_handle* h, int w, int hgt) {
 // hist slot p, left then right.
 int bind_problems(b2orb_handle* h, int np) {
     if (h->bound_np == np) return B2ORB_OK;
-    const size_t cap = h->geom.kp_cap;
-    std::vector<B2MatchProblem> pr((size_t)3 * np);
-    for (int p = 0; p < np; ++p) {
-        pr[p] = {h->d_desc + (size_t)p * cap * 32, h->d_desc + (size_t)(np + p) * cap * 32, h->d_nkp + p,
-                 h->d_nkp + np + p, h->d_train + (size_t)p * cap, h->d_dist + (size_t)p * cap};
-        pr[np + p] = {h->d_cur_l + (size_t)(p + 1) * cap * 32, h->d_cur_l + (size_t)p * cap * 32, h->d_nmatch + p + 1,
-                      h->d_nmatch + p, h->d_tti_l + (size_t)p * cap, h->d_tdi_l + (size_t)p * cap};
-        pr[2 * np + p] = {h->d_cur_r + (size_t)(p + 1) * cap * 32, h->d_cur_r + (size_t)p * cap * 32,
-                          h->d_nmatch + p + 1, h->d_nmatch + p, h->d_tti_r + (size_t)p * cap,
-                          h->d_tdi_r + (size_t)p * cap};
-    }
-    B2_CUDA(h, cudaMemcpyAsync(h->d_probs, pr.data(), pr.size() * sizeof(B2MatchProblem), cudaMemcpyHostToDevice,
-                               h->stream));
-    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    B2BindBases b{h->d_desc, h->d_cur_l, h->d_cur_r, h->d_nkp, h->d_train, h->d_dist, h->d_nmatch,
+                  h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->geom.kp_cap};
+    b2_launch_bind(h->d_probs, np, b, h->stream);       // stream-ordered: no host synchronisation
+    ++h->launches;
     h->bound_np = np;
     return B2ORB_OK;
 }
@@ -425,31 +428,52 @@ B2Images make_images(b2orb_handle* h, const uint8_t* a, const uint8_t* b, int sp
 // Host (or device) images -> staging area with an aligned row pitch (kernels read level 0 with 32-bit / 128-bit
 // accesses).  Host images whose rows are already aligned go straight in; tight rows of odd width (1241 ...) are
 // copied linearly (a pitched 2-D DMA of odd-width rows runs at half the PCIe rate) and re-pitched by a kernel.
-int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
-           bool on_device = false) {
+enum UploadPath { UP_DEVICE, UP_PITCHED, UP_TIGHT, UP_ROWS };
+UploadPath upload_path(const b2orb_handle* h, int w, int hgt, int step, size_t image_stride, bool on_device) {
+    if (on_device) return UP_DEVICE;
+    if (step == h->stage_pitch && image_stride == (size_t)step * hgt) return UP_PITCHED;
+    if (step == w && image_stride == (size_t)w * hgt) return UP_TIGHT;
+    return UP_ROWS;
+}
+// the host->device part, on stream `cs` (the handle's own stream, or the pipelined path's copy-in stream)
+int upload_copy(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
+                cudaStream_t cs) {
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
-    if (on_device) {
-        prof_mark(h, B2ORB_K_INGEST);
-        b2_launch_repack(src, step, image_stride, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
-        ++h->launches;
-        prof_mark(h, -1);
-        return B2ORB_OK;
-    }
-    if (step == h->stage_pitch && image_stride == (size_t)step * hgt) {
-        B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * step * hgt, cudaMemcpyHostToDevice, h->stream));
-    } else if (step == w && image_stride == (size_t)w * hgt) {
-        uint8_t* raw = h->d_raw + (size_t)slot0 * w * hgt;
-        B2_CUDA(h, cudaMemcpyAsync(raw, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, h->stream));
-        prof_mark(h, B2ORB_K_INGEST);
-        b2_launch_repack(raw, w, (size_t)w * hgt, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
-        ++h->launches;
-        prof_mark(h, -1);
-    } else {
+    switch (upload_path(h, w, hgt, step, image_stride, false)) {
+    case UP_PITCHED:
+        B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * step * hgt, cudaMemcpyHostToDevice, cs));
+        break;
+    case UP_TIGHT:
+        B2_CUDA(h, cudaMemcpyAsync(h->d_raw + (size_t)slot0 * w * hgt, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, cs));
+        break;
+    default:
         for (int i = 0; i < count; ++i)
             B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, h->stage_pitch, src + i * image_stride, step, w,
-                                         hgt, cudaMemcpyHostToDevice, h->stream));
+                                         hgt, cudaMemcpyHostToDevice, cs));
     }
     return B2ORB_OK;
+}
+// the re-pitching kernel (device sources and tight host rows), on the handle's stream
+int upload_repack(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
+                  bool on_device) {
+    const UploadPath path = upload_path(h, w, hgt, step, image_stride, on_device);
+    if (path != UP_DEVICE && path != UP_TIGHT) return B2ORB_OK;
+    uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
+    prof_mark(h, B2ORB_K_INGEST);
+    if (path == UP_DEVICE)
+        b2_launch_repack(src, step, image_stride, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
+    else
+        b2_launch_repack(h->d_raw + (size_t)slot0 * w * hgt, w, (size_t)w * hgt, dst, h->stage_pitch, h->stage_img_bytes, w,
+                         hgt, count, h->stream);
+    ++h->launches;
+    prof_mark(h, -1);
+    return B2ORB_OK;
+}
+int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
+           bool on_device = false) {
+    if (!on_device)
+        if (int rc = upload_copy(h, src, count, w, hgt, step, image_stride, slot0, h->stream)) return rc;
+    return upload_repack(h, src, count, w, hgt, step, image_stride, slot0, on_device);
 }
 
 int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
@@ -470,6 +494,14 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
     ++h->launches;
     prof_mark(h, -1);
     if (temporal) {
+        const size_t row = (size_t)g.kp_cap * 32;
+        b2orb_handle* src = h->root->hist_owner;
+        if (src && src != h) {   // the previous pair of the sequence was processed on another lane: fetch its slot 0
+            B2_CUDA(h, cudaStreamWaitEvent(s, src->ev_hist, 0));
+            B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, src->d_cur_l, row, cudaMemcpyDeviceToDevice, s));
+            B2_CUDA(h, cudaMemcpyAsync(h->d_cur_r, src->d_cur_r, row, cudaMemcpyDeviceToDevice, s));
+            B2_CUDA(h, cudaMemcpyAsync(h->d_nmatch, src->d_nmatch, sizeof(int), cudaMemcpyDeviceToDevice, s));
+        }
         prof_mark(h, B2ORB_K_MATCH_TEMPORAL);
         b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
         ++h->launches;
@@ -480,10 +512,11 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
         ++h->launches;
         prof_mark(h, -1);
         // the last pair of this call becomes the history of the next call (slot 0)
-        const size_t row = (size_t)g.kp_cap * 32;
         B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, h->d_cur_l + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
         B2_CUDA(h, cudaMemcpyAsync(h->d_cur_r, h->d_cur_r + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
         B2_CUDA(h, cudaMemcpyAsync(h->d_nmatch, h->d_nmatch + np, sizeof(int), cudaMemcpyDeviceToDevice, s));
+        B2_CUDA(h, cudaEventRecord(h->ev_hist, s));
+        h->root->hist_owner = h;
     }
     B2_CUDA(h, cudaGetLastError());
     return B2ORB_OK;
@@ -525,6 +558,13 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
     if (!cuda_ok(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) return B2ORB_ERR_CUDA;
     cudaEventCreate(&h->ev0);
     cudaEventCreate(&h->ev1);
+    cudaEventCreateWithFlags(&h->ev_hist, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming);
+    h->root = h;
+    if (const char* e = getenv("B2ORB_PIPE_CHUNK")) h->pipe_chunk = std::max(0, atoi(e));
+    if (const char* e = getenv("B2ORB_PIPE_LANES")) h->pipe_lanes = std::min(std::max(2, atoi(e)), 8);
     build_ctor_tables(h);
     return configure(h, cfg->max_width, cfg->max_height);
 }
@@ -532,8 +572,16 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
 void b2orb_destroy(b2orb_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
+    for (b2orb_handle* l : h->lanes) b2orb_destroy(l);
+    h->lanes.clear();
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_workspace(h);
+    if (h->ev_hist) cudaEventDestroy(h->ev_hist);
+    if (h->ev_done) cudaEventDestroy(h->ev_done);
+    if (h->ev_in) cudaEventDestroy(h->ev_in);
+    if (h->ev_out) cudaEventDestroy(h->ev_out);
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -543,7 +591,12 @@ void b2orb_destroy(b2orb_handle* h) {
 
 const char* b2orb_last_error(const b2orb_handle* h) { return h ? h->err.c_str() : "null handle"; }
 int b2orb_keypoint_capacity(const b2orb_handle* h) { return h ? h->geom.kp_cap : 0; }
-uint64_t b2orb_launch_count(const b2orb_handle* h) { return h ? h->launches : 0; }
+uint64_t b2orb_launch_count(const b2orb_handle* h) {
+    if (!h) return 0;
+    uint64_t n = h->launches;
+    for (const b2orb_handle* l : h->lanes) n += l->launches;
+    return n;
+}
 float b2orb_last_device_ms(const b2orb_handle* h) { return h ? h->last_ms : 0.f; }
 
 int b2orb_get_tables(const b2orb_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
@@ -579,6 +632,9 @@ void b2orb_reset_history(b2orb_handle* h) {
     if (!h || !h->d_nmatch) return;
     cudaSetDevice(h->device);
     cudaMemsetAsync(h->d_nmatch, 0, sizeof(int), h->stream);
+    for (b2orb_handle* l : h->lanes)
+        if (l->d_nmatch) cudaMemsetAsync(l->d_nmatch, 0, sizeof(int), l->stream);
+    h->hist_owner = nullptr;
 }
 
 int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int width, int height, int step,
@@ -652,16 +708,16 @@ int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, con
     return rc;
 }
 
-int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o) {
+static int enqueue_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o, cudaStream_t s) {
     if (!h || !o || npairs < 1 || 2 * npairs > h->nimg_cap) return B2ORB_ERR_INVALID;
     const int kcap = h->geom.kp_cap;
     if (o->cap < kcap) return fail(h, B2ORB_ERR_CAPACITY, "b2orb_stereo_out.cap below b2orb_keypoint_capacity()");
     B2_CUDA(h, cudaSetDevice(h->device));
-    cudaStream_t s = h->stream;
     const size_t np = npairs;
     // cap == kcap lets every slab go back in one copy; otherwise row-wise 2D copies
     auto copy2d = [&](void* dst, const void* src, size_t elem, size_t rows) -> cudaError_t {
         if (!dst) return cudaSuccess;
+        if (o->cap == kcap) return cudaMemcpyAsync(dst, src, (size_t)kcap * elem * rows, cudaMemcpyDeviceToHost, s);
         return cudaMemcpy2DAsync(dst, (size_t)o->cap * elem, src, (size_t)kcap * elem, (size_t)kcap * elem, rows,
                                  cudaMemcpyDeviceToHost, s);
     };
@@ -679,8 +735,113 @@ int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o
     if (o->n_r) B2_CUDA(h, cudaMemcpyAsync(o->n_r, h->d_nkp + np, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_match) B2_CUDA(h, cudaMemcpyAsync(o->n_match, h->d_nmatch + 1, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_circ) B2_CUDA(h, cudaMemcpyAsync(o->n_circ, h->d_ncirc, np * 4, cudaMemcpyDeviceToHost, s));
-    B2_CUDA(h, cudaStreamSynchronize(s));
     return B2ORB_OK;
+}
+
+int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o) {
+    const int rc = enqueue_download(h, npairs, o, h->stream);
+    if (rc) return rc;
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    return B2ORB_OK;
+}
+
+// b2orb_stereo_frontend for a long batch: chunks of `pipe_chunk` pairs rotate over the lanes (workspaces).  Three
+// stages run on three kinds of stream and are tied together by events only:
+//   copy-in stream  : H2D of chunk k into lane k%L's staging area, as soon as that lane's previous kernels are done
+//   lane stream     : re-pitch + the whole launch sequence, once the chunk is in and the lane's previous results are out
+//   copy-out stream : D2H of the chunk's results
+// so the H2D of chunk k+1 and the D2H of chunk k-1 overlap the kernels of chunk k with no host thread involved.
+// Results are identical to one big call: images are independent and the temporal history is handed from lane to
+// lane on the device (launch_stereo).
+static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs,
+                                     int width, int height, int step, size_t image_stride, int temporal,
+                                     const b2orb_stereo_out* out) {
+    const int chunk = h->pipe_chunk;
+    while ((int)h->lanes.size() < h->pipe_lanes) {
+        b2orb_config c = h->cfg;
+        c.max_images = 2 * chunk;
+        b2orb_handle* l = nullptr;
+        const int rc = b2orb_create(&l, h->device, &c);
+        if (rc) {
+            if (l) { h->err = l->err; b2orb_destroy(l); }
+            return rc;
+        }
+        l->root = h;
+        l->pipe_chunk = 0;
+        h->lanes.push_back(l);
+    }
+    if (!h->s_in) {
+        B2_CUDA(h, cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+        B2_CUDA(h, cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    }
+    const int nl = (int)h->lanes.size();
+    cudaEventRecord(h->ev0, h->stream);
+    B2_CUDA(h, cudaStreamWaitEvent(h->s_in, h->ev0, 0));   // ordered after earlier work on this handle
+    const size_t cap = out->cap;
+    int k = 0, rc = B2ORB_OK;
+    const bool trace = getenv("B2ORB_PIPE_TRACE") != nullptr;   // debugging aid: per-chunk timeline on stderr
+    struct Tr { cudaEvent_t e[4]; double h0, h1; };
+    std::vector<Tr> tr;
+    const auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_start = now();
+    b2orb_handle* l = nullptr;
+    for (int p0 = 0; p0 < npairs; p0 += chunk, ++k) {
+        l = h->lanes[k % nl];
+        const int n = std::min(chunk, npairs - p0);
+        if (trace) {
+            Tr t{};
+            for (auto& e : t.e) cudaEventCreate(&e);
+            t.h0 = now() - t_start;
+            tr.push_back(t);
+        }
+        if ((rc = configure(l, width, height))) break;
+        // ---- copy-in ----
+        if (k >= nl) cudaStreamWaitEvent(h->s_in, l->ev_done, 0);             // the lane's staging area is free again
+        if (trace) cudaEventRecord(tr.back().e[0], h->s_in);
+        if ((rc = upload_copy(l, images_l + (size_t)p0 * image_stride, n, width, height, step, image_stride, 0, h->s_in))) break;
+        if ((rc = upload_copy(l, images_r + (size_t)p0 * image_stride, n, width, height, step, image_stride, n, h->s_in))) break;
+        cudaEventRecord(l->ev_in, h->s_in);
+        if (trace) cudaEventRecord(tr.back().e[1], h->s_in);
+        // ---- kernels ----
+        cudaStreamWaitEvent(l->stream, l->ev_in, 0);
+        if (k >= nl) cudaStreamWaitEvent(l->stream, l->ev_out, 0);            // the lane's previous results are on the host
+        else cudaStreamWaitEvent(l->stream, h->ev0, 0);
+        if ((rc = bind_problems(l, n))) break;
+        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, 0, false))) break;
+        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, n, false))) break;
+        B2Images im = make_images(l, l->d_stage, l->d_stage + (size_t)n * l->stage_img_bytes, n, l->stage_img_bytes,
+                                  l->stage_pitch);
+        if ((rc = launch_stereo(l, im, n, temporal))) break;
+        cudaEventRecord(l->ev_done, l->stream);
+        if (trace) cudaEventRecord(tr.back().e[2], l->stream);
+        // ---- copy-out ----
+        cudaStreamWaitEvent(h->s_out, l->ev_done, 0);
+        b2orb_stereo_out o = *out;
+        const auto shift = [&](auto*& ptr, size_t per_pair) { if (ptr) ptr += (size_t)p0 * per_pair; };
+        shift(o.kp_l, cap); shift(o.kp_r, cap); shift(o.desc_l, cap * 32); shift(o.desc_r, cap * 32);
+        shift(o.train_idx, cap); shift(o.dist, cap); shift(o.match_l, cap); shift(o.match_r, cap);
+        shift(o.circ_cur, cap); shift(o.circ_hist, cap);
+        shift(o.n_l, 1); shift(o.n_r, 1); shift(o.n_match, 1); shift(o.n_circ, 1);
+        if ((rc = enqueue_download(l, n, &o, h->s_out))) break;
+        cudaEventRecord(l->ev_out, h->s_out);
+        if (trace) { cudaEventRecord(tr.back().e[3], h->s_out); tr.back().h1 = now() - t_start; }
+    }
+    if (rc && l) h->err = l->err;
+    cudaStreamSynchronize(h->s_in);
+    for (b2orb_handle* q : h->lanes) cudaStreamSynchronize(q->stream);
+    cudaEventRecord(h->ev1, h->s_out);
+    B2_CUDA(h, cudaStreamSynchronize(h->s_out));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    if (trace && !rc) {
+        fprintf(stderr, "[b2orb pipe] chunk: host enqueue [h0,h1] | device: h2d start, h2d done, kernels done, d2h done (ms); total %.3f host %.3f\n", h->last_ms, now() - t_start);
+        for (size_t i = 0; i < tr.size(); ++i) {
+            float t[4];
+            for (int j = 0; j < 4; ++j) cudaEventElapsedTime(&t[j], h->ev0, tr[i].e[j]);
+            fprintf(stderr, "[b2orb pipe] %2zu: [%.3f, %.3f] | %.3f %.3f %.3f %.3f\n", i, tr[i].h0, tr[i].h1, t[0], t[1], t[2], t[3]);
+        }
+    }
+    for (Tr& t : tr) for (auto& e : t.e) if (e) cudaEventDestroy(e);
+    return rc;
 }
 
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
@@ -690,6 +851,8 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     if (2 * npairs > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*npairs exceeds max_images");
     if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
     B2_CUDA(h, cudaSetDevice(h->device));
+    if (h->pipe_chunk > 0 && npairs > h->pipe_chunk && h->root == h)
+        return stereo_frontend_pipelined(h, images_l, images_r, npairs, width, height, step, image_stride, temporal, out);
     int rc = configure(h, width, height);
     if (rc) return rc;
     if ((rc = bind_problems(h, npairs))) return rc;

@@ -189,6 +189,21 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
 
 }  // namespace
 
+// Stereo problems [0,np): desc(left p) vs desc(right np+p).  Temporal problems [np, 3np): cur slot p+1 vs hist
+// slot p, left then right (src/feature-tracker.cpp:161-163, 258, 303).
+__global__ void bind_kernel(B2MatchProblem* pr, int np, B2BindBases b) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= np) return;
+    const size_t cap = b.cap, row = cap * 32;
+    pr[p] = {b.desc + p * row, b.desc + (np + p) * row, b.nkp + p, b.nkp + np + p, b.train + p * cap, b.dist + p * cap};
+    pr[np + p] = {b.cur_l + (p + 1) * row, b.cur_l + p * row, b.nmatch + p + 1, b.nmatch + p, b.tti_l + p * cap, b.tdi_l + p * cap};
+    pr[2 * np + p] = {b.cur_r + (p + 1) * row, b.cur_r + p * row, b.nmatch + p + 1, b.nmatch + p, b.tti_r + p * cap, b.tdi_r + p * cap};
+}
+
+void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStream_t s) {
+    bind_kernel<<<(np + 127) / 128, 128, 0, s>>>(probs, np, b);
+}
+
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s) {
     if (nprob <= 0 || max_nq <= 0) return;
     dim3 grid((max_nq + MT_THREADS - 1) / MT_THREADS, nprob);

@@ -156,6 +156,45 @@ def test_stereo_frontend_matches_oracle(shape, npairs, fe, oracle, synth):
     hd.close()
 
 
+def _stereo_equal(a, b, npairs):
+    for k in ("n_l", "n_r", "n_match", "n_circ"):
+        assert np.array_equal(a[k][:npairs], b[k][:npairs]), k
+    for p in range(npairs):
+        for key, cnt in (("kp_l", "n_l"), ("desc_l", "n_l"), ("kp_r", "n_r"), ("desc_r", "n_r"), ("train_idx", "n_l"),
+                         ("dist", "n_l"), ("match_l", "n_match"), ("match_r", "n_match"), ("circ_cur", "n_circ"),
+                         ("circ_hist", "n_circ")):
+            n = int(a[cnt][p])
+            assert np.array_equal(a[key][p, :n], b[key][p, :n]), f"pair {p}: {key}"
+
+
+@pytest.mark.parametrize("chunk,lanes", [(2, 3), (3, 2)])
+def test_pipelined_host_path_equals_single_call(chunk, lanes, fe, synth, monkeypatch):
+    """A long host batch is cut into chunks that rotate over internal lanes (streams): same results as one call,
+    including the temporal chain across chunk, lane and call boundaries."""
+    w, h, nf, ini, mn = synth.SHAPES["cfsd"]
+    ls, rs = synth.sequence("cfsd", 7, seed=33)
+    monkeypatch.setenv("B2ORB_PIPE_CHUNK", "0")
+    ref = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14)
+    monkeypatch.setenv("B2ORB_PIPE_CHUNK", str(chunk))
+    monkeypatch.setenv("B2ORB_PIPE_LANES", str(lanes))
+    pip = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14)
+    a, b = ref.stereo_frontend(ls, rs, temporal=True), pip.stereo_frontend(ls, rs, temporal=True)
+    assert a["n_circ"][1:].min() > 5
+    _stereo_equal(a, b, 7)
+    # second call: history comes from the lane that ran the last chunk; then a short (un-pipelined) call on the root
+    _stereo_equal(ref.stereo_frontend(ls[:5], rs[:5], temporal=True), pip.stereo_frontend(ls[:5], rs[:5], temporal=True), 5)
+    a1, b1 = ref.stereo_frontend(ls[6:], rs[6:], temporal=True), pip.stereo_frontend(ls[6:], rs[6:], temporal=True)
+    assert a1["n_circ"][0] > 0
+    _stereo_equal(a1, b1, 1)
+    _stereo_equal(ref.stereo_frontend(ls, rs, temporal=True), pip.stereo_frontend(ls, rs, temporal=True), 7)
+    pip.reset_history(); ref.reset_history()
+    b2 = pip.stereo_frontend(ls, rs, temporal=True)
+    assert b2["n_circ"][0] == 0
+    _stereo_equal(ref.stereo_frontend(ls, rs, temporal=True), b2, 7)
+    assert pip.launch_count > ref.launch_count
+    ref.close(); pip.close()
+
+
 def test_temporal_track_entry_point(fe, oracle):
     rng = np.random.default_rng(5)
     hist_l = rng.integers(0, 256, (300, 32), dtype=np.uint8); hist_r = rng.integers(0, 256, (300, 32), dtype=np.uint8)
