@@ -6,7 +6,7 @@
 #define B2_MAX_LEVELS 12
 #define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
 #define B2_BORDER 16        // EDGE_THRESHOLD-3 = minBorderX/Y, src/ORBextractor.cc:773-776
-#define B2_FAST_BAND 32     // corner-map rows per FAST score task (fast.cu)
+#define B2_FAST_BAND 32     // corner-map rows per FAST score task (fast.cu): variant v uses B2_FAST_BAND << v rows
 #define B2_BLUR_BAND 32     // output rows per blur task (blur.cu)
 #define B2_HALF_PATCH 15    // HALF_PATCH_SIZE, src/ORBextractor.cc:73
 
@@ -18,7 +18,7 @@ struct B2Level {
     int n_cols, n_rows;       // FAST cell grid (src/ORBextractor.cc:784-787)
     int w_cell, h_cell;
     int cell_base;            // first flattened cell index of this level
-    int fast_task_base;       // first flattened FAST score task (band, strip) of this level
+    int fast_task_base[2];    // first flattened FAST score task (band, strip) of this level, per band variant
     int fast_strips;          // 112-px strips per row band (fast.cu)
     int blur_task_base;       // first flattened blur task (band, strip) of this level
     int blur_strips;          // 128-px strips per row band
@@ -40,7 +40,7 @@ struct B2Geom {
     int ini_th, min_th;
     int total_cells;          // over all levels
     int total_blur_tasks;
-    int total_fast_tasks;
+    int total_fast_tasks[2];  // per band variant (short bands for small batches, long bands for less halo work)
     int sel_total;            // per-image selected-keypoint slots (sum of sel_cap)
     int kp_cap;               // per-image output capacity
     unsigned cand_total;      // per-image candidate slots
@@ -95,8 +95,13 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);
-void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint8_t* score, int nimg, cudaStream_t s);
-void b2_launch_fast_cells(const B2Geom& g, const uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s);
+// fast_score appends the non-zero words of the NMS'd corner map (4 px of b + position, uint2) to a raw list and raises
+// the per-cell "iniThFAST found something" flags; fast_vote applies the per-cell threshold vote and expands the words
+// into candidates x | y<<12 | (b-1)<<24
+void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
+                          cudaStream_t s);
+void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
+                         int* cand_cnt, int nimg, cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
                       B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,

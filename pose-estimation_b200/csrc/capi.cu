@@ -51,10 +51,14 @@ struct b2orb_handle {
 
     // workspace (sized for cfg.max_images images of the current size)
     int nimg_cap = 0, npair_cap = 0;
-    uint8_t *d_stage = nullptr, *d_raw = nullptr, *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
+    uint8_t *d_stage = nullptr, *d_raw = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
     size_t stage_img_bytes = 0;
     int stage_pitch = 0;                                 // level-0 rows in the staging area: 32-byte aligned pitch
-    uint32_t* d_cand = nullptr;
+    uint32_t* d_cand = nullptr;                          // voted FAST candidates
+    uint2* d_raw_cand = nullptr;                         // raw corner-map words (fast.cu)
+    int* d_raw_cnt = nullptr;                            // [nimg*nlevels] ints, then the per-cell iniThFAST flags
+    uint8_t* d_cell_ini = nullptr;
+    size_t raw_state_bytes = 0;
     unsigned short* d_pnode = nullptr;
     int *d_cand_cnt = nullptr, *d_sel_cnt = nullptr, *d_nkp = nullptr;
     uint32_t* d_sel = nullptr;
@@ -217,7 +221,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         memcpy(g.tapv, v, sizeof v);
     }
     unsigned off = 0, cand_off = 0, node_off = 0;
-    int cells = 0, tiles = 0, sel = 0, ftasks = 0;
+    int cells = 0, tiles = 0, sel = 0, ftasks[2] = {0, 0};
     for (int l = 0; l < c.nlevels; ++l) {
         B2Level& L = g.lv[l];
         // ComputePyramid :1111-1112: Size(cvRound((float)cols*scale), cvRound((float)rows*scale))
@@ -238,7 +242,8 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
         const int n_cols = width > 0 ? (int)(width / 30.f) : 0, n_rows = height > 0 ? (int)(height / 30.f) : 0;
         L.cell_base = cells;
-        L.fast_task_base = ftasks;   // levels without cells own zero tasks but must keep the list monotonic
+        L.fast_task_base[0] = ftasks[0];   // levels without cells own zero tasks but must keep the list monotonic
+        L.fast_task_base[1] = ftasks[1];
         L.n_ini = 1;
         L.h_x = 1.f;
         if (n_cols >= 1 && n_rows >= 1) {   // else: the reference divides by zero; the level yields no keypoints
@@ -250,12 +255,13 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
             if ((long long)n_cols * n_rows * L.w_cell * L.h_cell >= (1 << 24)) return "level too large for 24-bit order keys";
             cells += n_cols * n_rows;
             L.fast_strips = (L.w - 2 * B2_BORDER + 111) / 112;
-            ftasks += L.fast_strips * ((L.h - 2 * B2_EDGE + B2_FAST_BAND - 1) / B2_FAST_BAND);
+            for (int v = 0; v < 2; ++v)
+                ftasks[v] += L.fast_strips * ((L.h - 2 * B2_EDGE + (B2_FAST_BAND << v) - 1) / (B2_FAST_BAND << v));
             // DistributeOctTree :543-545
             L.n_ini = (int)std::round((float)(maxBX - minB) / (maxBY - minB));
             if (L.n_ini < 1) {   // taller than 2:1 -> the reference divides by zero; no keypoints
                 L.n_ini = 1; L.n_cols = L.n_rows = 0; cells -= n_cols * n_rows;
-                ftasks = L.fast_task_base; L.fast_strips = 0;
+                ftasks[0] = L.fast_task_base[0]; ftasks[1] = L.fast_task_base[1]; L.fast_strips = 0;
             } else if (L.n_ini > 256) return "aspect ratio above 256:1";
             L.h_x = (float)(maxBX - minB) / L.n_ini;
         }
@@ -273,7 +279,8 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     if (w > 4096 + B2_BORDER || hgt > 4096 + B2_BORDER) return "image larger than 4096 px";
     g.total_cells = cells;
     g.total_blur_tasks = tiles;
-    g.total_fast_tasks = ftasks;
+    g.total_fast_tasks[0] = ftasks[0];
+    g.total_fast_tasks[1] = ftasks[1];
     g.sel_total = sel;
     g.kp_cap = sel;
     g.cand_total = cand_off;
@@ -342,10 +349,10 @@ int configure(b2orb_handle* h, int w, int hgt) {
     bool ok = dev_alloc(h, &h->d_stage, (size_t)nimg * h->stage_img_bytes) &&
               dev_alloc(h, &h->d_raw, (size_t)nimg * w * hgt) &&
               dev_alloc(h, &h->d_pyr, (size_t)nimg * g.slab) && dev_alloc(h, &h->d_blur, (size_t)nimg * g.slab) &&
-              dev_alloc(h, &h->d_score, (size_t)nimg * g.slab) &&
+              dev_alloc(h, &h->d_raw_cand, (size_t)nimg * g.cand_total) &&
               dev_alloc(h, &h->d_cand, (size_t)nimg * g.cand_total) &&
               dev_alloc(h, &h->d_pnode, (size_t)nimg * g.cand_total) &&
-              dev_alloc(h, &h->d_cand_cnt, (size_t)nimg * nl) && dev_alloc(h, &h->d_sel_cnt, (size_t)nimg * nl) &&
+              dev_alloc(h, &h->d_sel_cnt, (size_t)nimg * nl) &&
               dev_alloc(h, &h->d_nkp, (size_t)nimg) && dev_alloc(h, &h->d_sel, (size_t)nimg * g.sel_total) &&
               dev_alloc(h, &h->d_kps, (size_t)nimg * cap) && dev_alloc(h, &h->d_desc, (size_t)nimg * cap * 32) &&
               dev_alloc(h, &h->d_train, (size_t)np * cap) && dev_alloc(h, &h->d_dist, (size_t)np * cap) &&
@@ -358,6 +365,15 @@ int configure(b2orb_handle* h, int w, int hgt) {
               dev_alloc(h, &h->d_nleft, (size_t)np) && dev_alloc(h, &h->d_nright, (size_t)np) &&
               dev_alloc(h, &h->d_probs, (size_t)3 * np + 4) && dev_alloc(h, &h->d_gcnt, (size_t)8);
     if (!ok) return B2ORB_ERR_NOMEM;
+    {   // raw candidate counters and per-cell flags share one allocation: one memset per batch clears both
+        const size_t cnt_bytes = (size_t)nimg * nl * sizeof(int);
+        h->raw_state_bytes = 2 * cnt_bytes + (size_t)nimg * std::max(g.total_cells, 1);
+        uint8_t* p = nullptr;
+        if (!dev_alloc(h, &p, h->raw_state_bytes)) return B2ORB_ERR_NOMEM;
+        h->d_raw_cnt = reinterpret_cast<int*>(p);
+        h->d_cand_cnt = reinterpret_cast<int*>(p + cnt_bytes);
+        h->d_cell_ini = p + 2 * cnt_bytes;
+    }
     if ((size_t)b2_octree_scratch_words(g) * 4 > 200 * 1024) {   // quadtree state too big for shared memory
         if (!dev_alloc(h, &h->d_ot_scratch, (size_t)nimg * g.node_total * 20)) return B2ORB_ERR_NOMEM;
     } else h->d_ot_scratch = nullptr;
@@ -391,12 +407,12 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
         ++h->launches;
     }
     prof_mark(h, -1);
-    B2_CUDA(h, cudaMemsetAsync(h->d_cand_cnt, 0, (size_t)nimg * g.nlevels * sizeof(int), s));
+    B2_CUDA(h, cudaMemsetAsync(h->d_raw_cnt, 0, h->raw_state_bytes, s));
     prof_mark(h, B2ORB_K_FAST);
     if (g.total_cells > 0) {
-        b2_launch_fast_score(g, im, h->d_score, nimg, s);
+        b2_launch_fast_score(g, im, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, nimg, s);
         prof_mark(h, B2ORB_K_FAST_CELLS);
-        b2_launch_fast_cells(g, h->d_score, h->d_cand, h->d_cand_cnt, nimg, s);
+        b2_launch_fast_vote(g, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, h->d_cand, h->d_cand_cnt, nimg, s);
         h->launches += 2;
     }
     prof_mark(h, B2ORB_K_OCTREE);

@@ -10,7 +10,7 @@
 //     b(p) > b(q) for the neighbours q inside the cell's own detect area;
 //   * detect areas of neighbouring cells tile the bordered rectangle without overlap.
 //
-// Two kernels, both organised around instructions per pixel (the stage is ALU-pipe bound, not HBM bound):
+// Organised around instructions per pixel (the stage is ALU-pipe bound, not HBM bound):
 //
 // fast_score_kernel — one WARP owns a 112-px strip (lanes 2..29 produce 4 px each, lanes 0/1/30/31 only feed
 //   the halo of the score and of the fused NMS) and marches down a band of rows.  Per image row a lane loads one 32-bit word, splits it into two
@@ -22,17 +22,23 @@
 //   min(min8[k+1..k+8], max(r[k], r[k+9])) — 36 min/max per side per pixel pair.  The 3x3 non-max suppression
 //   with the cell-boundary rule is fused in (3-row window of packed scores, column masks per lane, row masks
 //   per step) and the kernel writes a sparse corner map M: M = b where the pixel survives NMS inside its
-//   cell and b > minThFAST, else 0.
-// fast_cells_kernel — one warp per cell scans its part of M, votes on the threshold (any survivor with
-//   b > ini ? ini : min — src/ORBextractor.cc:809-816) and appends the survivors to the level's candidate
-//   list.  Candidate order is irrelevant downstream: the quadtree breaks response ties with a key that
-//   reproduces the reference's cell-row-major order.
+//   cell and b > minThFAST, else 0.  M itself is never stored: its non-zero words (few: NMS keeps <= 3 px of 4)
+//   are compacted by ballot into a per-warp shared-memory queue and copied to the level's RAW list (uint2 = the
+//   4 scores + position) every FS_FLUSH rows with one global atomic; "b > iniThFAST seen" is OR-ed into two
+//   registers per lane and written to the per-cell flag array whenever the band crosses a cell-row boundary.
+// fast_vote_kernel — the threshold vote of src/ORBextractor.cc:809-816 (a cell falls back to minThFAST only when
+//   iniThFAST found nothing in it) needs every strip of a cell, i.e. a kernel boundary: one thread per raw word
+//   keeps a corner iff b > ini or its cell's flag is clear and appends x | y<<12 | (b-1)<<24 to the candidate list
+//   (warp-aggregated atomics).  Candidate order is irrelevant downstream: the quadtree breaks response ties with
+//   a key that reproduces the reference's cell-row-major order.
 #include "b2orb_internal.cuh"
 
 namespace {
 
 constexpr int FS_WARPS = 4;
-constexpr int FS_PF = 4;        // rows in flight per warp
+constexpr int FS_PF = 5;        // rows in flight per warp (ring of 7 slots, slot = row % 7 = unroll phase)
+constexpr int FS_FLUSH = 7;     // output rows between queue flushes (one pass of the 7-phase unrolled loop)
+constexpr int FS_QUEUE = 28 * FS_FLUSH;   // at most one non-zero word per storing lane and row
 
 __device__ __forceinline__ unsigned vmin2(unsigned a, unsigned b) { return __vminu2(a, b); }
 __device__ __forceinline__ unsigned vmax2(unsigned a, unsigned b) { return __vmaxu2(a, b); }
@@ -66,6 +72,17 @@ __device__ __forceinline__ unsigned fast_b_pair(const unsigned (&v)[16], unsigne
     return vmax2(rmax, c) - vmin2(rmin, c);   // per-lane non-negative: no borrow between the halves
 }
 
+// one 4-byte async copy + its own commit group
+__device__ __forceinline__ void fs_cp_async4(unsigned smem_addr, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n\tcp.async.commit_group;" ::"r"(smem_addr), "l"(gmem) : "memory");
+}
+// wait until at most FS_PF groups are pending (the oldest needed row has landed), then read this lane's word
+__device__ __forceinline__ unsigned fs_wait_lds(unsigned smem_addr) {
+    unsigned v;
+    asm volatile("cp.async.wait_group %1;\n\tld.shared.u32 %0, [%2];" : "=r"(v) : "n"(FS_PF), "r"(smem_addr) : "memory");
+    return v;
+}
+
 // out = (b > nb) ? b : 0 per u16 lane, all values < 256
 __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
     const unsigned d = b + 0x00FF00FFu - nb;                 // bit 8 of each lane: b > nb
@@ -73,24 +90,32 @@ __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
     return b & (one * 255u);
 }
 
-__global__ void __launch_bounds__(FS_WARPS * 32)
-fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* __restrict__ score) {
+__global__ void __launch_bounds__(FS_WARPS * 32, 4)
+fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __restrict__ raw_list,
+                  int* __restrict__ raw_cnt, uint8_t* __restrict__ cell_ini, int variant) {
+    __shared__ uint2 s_queue[FS_WARPS][FS_QUEUE];
+    __shared__ unsigned s_ring[FS_WARPS][7][32];
     const int lane = threadIdx.x & 31;
     const int task = blockIdx.x * FS_WARPS + (threadIdx.x >> 5);
-    if (task >= g.total_fast_tasks) return;
+    if (task >= g.total_fast_tasks[variant]) return;
+    const int band_rows = B2_FAST_BAND << variant;
     const int b = blockIdx.y;
     int level = 0;
-    while (level + 1 < g.nlevels && task >= g.lv[level + 1].fast_task_base) ++level;
+    while (level + 1 < g.nlevels && task >= g.lv[level + 1].fast_task_base[variant]) ++level;
     const B2Level& L = g.lv[level];
-    const int t = task - L.fast_task_base;
+    const int t = task - L.fast_task_base[variant];
     const int band = t / L.fast_strips, strip = t - band * L.fast_strips;
     int pitch;
     const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
-    uint8_t* M = score + (size_t)b * g.slab + L.off;
+    uint2* queue = s_queue[threadIdx.x >> 5];
+    int qn = 0;                                                // queue fill, warp-uniform
+    uint2* out = raw_list + (size_t)b * g.cand_total + L.cand_off;
+    int* out_cnt = raw_cnt + b * g.nlevels + level;
+    uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
     const int w = L.w, h = L.h;
     const int x = B2_BORDER - 8 + strip * 112 + lane * 4;      // lanes 2..29 own columns x .. x+3
-    const int ya = B2_EDGE + band * B2_FAST_BAND;              // M rows [ya, yb)
-    const int yb = min(ya + B2_FAST_BAND, h - B2_EDGE);
+    const int ya = B2_EDGE + band * band_rows;                 // M rows [ya, yb)
+    const int yb = min(ya + band_rows, h - B2_EDGE);
     const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
     const int xo = min(x, pitch - 4);
     const uint8_t* col = img + xo;
@@ -108,26 +133,37 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
         if (j & 1) { if (in) inO |= lanebits; if (left) mlO |= lanebits; if (right) mrO |= lanebits; }
         else       { if (in) inE |= lanebits; if (left) mlE |= lanebits; if (right) mrE |= lanebits; }
     }
+    // cell column of pixel 0 and which of the 4 pixels share it (a lane spans at most two cells: w_cell >= 30)
+    const int cjA = max(x - B2_EDGE, 0) / L.w_cell;
+    unsigned sameA = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        if (max(x + j - B2_EDGE, 0) / L.w_cell == cjA) sameA |= 1u << j;
+    const unsigned kini = 0x00FF00FFu - (unsigned)g.ini_th * 0x00010001u;   // (o + kini) bit 8 per lane: o > ini
+    const unsigned lt_mask = (1u << lane) - 1;
+    unsigned accE = 0, accO = 0;
     const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
     const bool store_lane = lane >= 2 && lane <= 29 && x < w - B2_BORDER;   // b valid on lanes 1..30, NMS on 2..29
 
-    unsigned raw[7];
     unsigned P[7][8];            // pairs (p[a], p[a+2]) for a = x-3 .. x+4, last 7 rows
     // Rows are addressed by a 32-bit offset that is clamped to the last row of the band, so the prefetch needs no
-    // branch; pixel row r of the band sits at col0 + r * pitch.
+    // branch; pixel row r of the band sits at col0 + r * pitch.  Each lane stages its own word of the next FS_PF
+    // rows with 4-byte cp.async into a private shared-memory slot: async-copy groups complete in order, so waiting
+    // for row r never waits for the rows issued after it (plain loads share scoreboards and did, see blur.cu).
     const uint8_t* col0 = col + (size_t)(ya - 4) * pitch;
     const unsigned offmax = (unsigned)(nsteps - 1) * (unsigned)pitch;
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(&s_ring[threadIdx.x >> 5][0][lane]);
     unsigned off = 0;
 #pragma unroll
     for (int i = 0; i < FS_PF; ++i) {
-        raw[i] = *reinterpret_cast<const unsigned*>(col0 + min(off, offmax));
+        fs_cp_async4(ring_s + i * 128, col0 + min(off, offmax));
         off += pitch;
     }
 #define B2_FAST_PAIRS(p)                                                                                        \
     {                                                                                                           \
-        const unsigned R1 = raw[p];                                                                             \
-        raw[((p) + FS_PF) % 7] = *reinterpret_cast<const unsigned*>(col0 + min(off, offmax));                   \
+        fs_cp_async4(ring_s + (((p) + FS_PF) % 7) * 128, col0 + min(off, offmax));                              \
         off += pitch;                                                                                           \
+        const unsigned R1 = fs_wait_lds(ring_s + (p) * 128);                                                    \
         const unsigned E1 = __byte_perm(R1, 0u, 0x4240), O1 = __byte_perm(R1, 0u, 0x4341);                      \
         const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);    \
         const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                      \
@@ -142,11 +178,35 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
 
     // NMS state: rows s-2 (rm only), s-1 (pending centre), s (newest)
     unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
-    uint8_t* mrow = M + (size_t)ya * L.pitch + x;             // output row of step r = 8
     int y = ya;
-    int cy = (band * B2_FAST_BAND) % L.h_cell;                 // row of y inside its cell
+    int ci = (band * band_rows) / L.h_cell;                    // cell row of y, and row of y inside its cell
+    int cy = band * band_rows - ci * L.h_cell;
+    // queue entry position word: x - 16 | (y - 16) << 12 | cell row << 24, advanced incrementally
+    unsigned meta = (unsigned)(x - B2_BORDER) | ((unsigned)(ya - B2_BORDER) << 12) | ((unsigned)ci << 24);
     const int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
 
+    // "b > ini seen" bits of this lane's 4 pixels -> the (at most two) cells they belong to
+#define B2_FAST_FLAGS()                                                                                        \
+    {                                                                                                           \
+        const unsigned hit = ((accE >> 8) & 1u) | ((accO >> 7) & 2u) | ((accE >> 22) & 4u) | ((accO >> 21) & 8u); \
+        if (store_lane && (hit & sameA)) flags[ci * L.n_cols + cjA] = 1;                                       \
+        if (store_lane && (hit & ~sameA)) flags[ci * L.n_cols + cjA + 1] = 1;                                  \
+        accE = accO = 0;                                                                                        \
+    }
+    /* queue -> raw list: one global atomic per flush, coalesced 8-byte copies */
+#define B2_FAST_FLUSH()                                                                                        \
+    {                                                                                                           \
+        __syncwarp();                                                                                           \
+        if (qn) {                                                                                               \
+            int base = 0;                                                                                       \
+            if (lane == 0) base = atomicAdd(out_cnt, qn);                                                       \
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);                                                           \
+            for (int i = lane; i < qn; i += 32)                                                                 \
+                if (base + i < L.cand_cap) out[base + i] = queue[i];                                            \
+            __syncwarp();                                                                                       \
+            qn = 0;                                                                                             \
+        }                                                                                                       \
+    }
 #define B2_FAST_STEP(p, OUT)                                                                                   \
     {                                                                                                           \
         B2_FAST_PAIRS(p)                                                                                     \
@@ -175,10 +235,15 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
             const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));                            \
             const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));                            \
             const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;     \
-            if (store_lane) *reinterpret_cast<unsigned*>(mrow) = __byte_perm(oE, oO, 0x6240);                \
-            mrow += L.pitch;                                                                                 \
+            const unsigned m4 = __byte_perm(oE, oO, 0x6240);                                                 \
+            accE |= oE + kini; accO |= oO + kini;                                                            \
+            const bool has = store_lane && m4 != 0;                                                          \
+            const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);                                            \
+            if (has) queue[qn + __popc(bal & lt_mask)] = make_uint2(m4, meta);                               \
+            qn += __popc(bal);                                                                               \
             ++y;                                                                                             \
-            cy = cy == hcell1 ? 0 : cy + 1;                                                                  \
+            meta += 0x1000u;                                                                                 \
+            if (cy == hcell1) { B2_FAST_FLAGS() cy = 0; ++ci; meta += 0x1000000u; } else ++cy;               \
         }                                                                                                    \
         rmE_a = rmE_b; rmO_a = rmO_b;                                                                        \
         rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;                                                      \
@@ -192,119 +257,80 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint8_t* 
         for (int q = 0; q < 7; ++q) {
             if (base + q < nsteps) B2_FAST_STEP((1 + q) % 7, true)
         }
+        B2_FAST_FLUSH()
     }
+    B2_FAST_FLAGS()
 #undef B2_FAST_STEP
 #undef B2_FAST_PAIRS
+#undef B2_FAST_FLAGS
+#undef B2_FAST_FLUSH
 }
 
 // ---------------------------------------------------------------------------------------------------
-constexpr int FC_WARPS = 4;
-constexpr int FC_CHUNK = 8;
-constexpr int FC_BUF = 1024;     // >= ceil(64/2) * ceil(64/2) survivors of one cell (NMS keeps <= 1 of 4)
+constexpr int FV_THREADS = 256;
+constexpr int FV_CHUNKS = 4;       // CTAs per (image, level)
 
-__global__ void __launch_bounds__(FC_WARPS * 32)
-fast_cells_kernel(const __grid_constant__ B2Geom g, const uint8_t* __restrict__ score, uint32_t* __restrict__ cand,
-                  int* __restrict__ cand_cnt) {
-    __shared__ uint32_t s_buf[FC_WARPS][FC_BUF];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int cellid = blockIdx.x * FC_WARPS + wid;
-    if (cellid >= g.total_cells) return;
-    const int b = blockIdx.y;
-    int level = 0;
-    while (level + 1 < g.nlevels && cellid >= g.lv[level + 1].cell_base) ++level;
+__global__ void __launch_bounds__(FV_THREADS)
+fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw_list, const int* __restrict__ raw_cnt,
+                 const uint8_t* __restrict__ cell_ini, uint32_t* __restrict__ cand, int* __restrict__ cand_cnt) {
+    const int level = blockIdx.x / FV_CHUNKS, chunk = blockIdx.x - level * FV_CHUNKS, b = blockIdx.y;
     const B2Level& L = g.lv[level];
-    const int cell = cellid - L.cell_base;
-    const int ci = cell / L.n_cols, cj = cell - ci * L.n_cols;
-    // detect area of this cell in level coordinates (ROI inset by 3, clipped to maxBorder-3 = dim-19)
-    const int x0 = B2_EDGE + cj * L.w_cell, y0 = B2_EDGE + ci * L.h_cell;
-    const int x1 = min(x0 + L.w_cell, L.w - B2_EDGE), y1 = min(y0 + L.h_cell, L.h - B2_EDGE);
-    if (x1 <= x0 || y1 <= y0) return;
-    const uint8_t* M = score + (size_t)b * g.slab + L.off;
-    uint32_t* buf = s_buf[wid];
-    const int ini = g.ini_th;
-    __shared__ int s_cnt[FC_WARPS];
-    if (lane == 0) s_cnt[wid] = 0;
-    __syncwarp();
-    // Word-wise scan: a lane owns one aligned 32-bit column of the cell (4 px) and, when the cell is at most 16
-    // words wide, every other row.  M is sparse (NMS keeps <= 1 px of 4), so the append path is rarely taken;
-    // buffer order is irrelevant (the quadtree re-derives the reference order from coordinates).
-    const int xa = x0 & ~3;
-    const int wpr = (((x1 + 3) & ~3) - xa) >> 2;               // words per cell row, <= 17
-    const int rpi = wpr <= 16 ? 2 : 1;                          // rows per iteration
-    const int wc = rpi == 2 ? (lane & 15) : lane;
-    const int rsub = rpi == 2 ? (lane >> 4) : 0;
-    unsigned bytemask = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int X = xa + 4 * wc + j;
-        if (wc < wpr && X >= x0 && X < x1) bytemask |= 0xFFu << (8 * j);
-    }
-    bool mine_ini = false;
-    const uint8_t* colp = M + xa + 4 * wc;
-    // loads are issued FC_CHUNK rows at a time so their latencies overlap; the (rare) append path runs afterwards
-    for (int yc = y0 + rsub; yc < y1; yc += rpi * FC_CHUNK) {
-        unsigned vv[FC_CHUNK];
-#pragma unroll
-        for (int k = 0; k < FC_CHUNK; ++k) {
-            const int y = yc + k * rpi;
-            vv[k] = (bytemask && y < y1) ? (*reinterpret_cast<const unsigned*>(colp + (size_t)y * L.pitch) & bytemask) : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < FC_CHUNK; ++k) {
-            unsigned v = vv[k];
-            const int y = yc + k * rpi;
-            while (v) {
-                const int j = (__ffs(v) - 1) >> 3;
-                const unsigned bv = (v >> (8 * j)) & 0xFFu;
-                v &= ~(0xFFu << (8 * j));
-                mine_ini |= (int)bv > ini;
-                const int pos = atomicAdd(&s_cnt[wid], 1);
-                if (pos < FC_BUF)
-                    buf[pos] = (unsigned)(xa + 4 * wc + j - B2_BORDER) | ((unsigned)(y - B2_BORDER) << 12) | ((bv - 1u) << 24);
-            }
-        }
-    }
-    const bool any_ini = __any_sync(0xFFFFFFFFu, mine_ini);
-    __syncwarp();
-    int n = s_cnt[wid];
-    __syncwarp();
-    n = min(n, FC_BUF);
-    // src/ORBextractor.cc:809-816: the min threshold applies only if the ini threshold found nothing in this cell
-    const unsigned thr = any_ini ? (unsigned)ini : 0u;     // entries hold b-1; keep b > thr  <=>  b-1 >= thr
-    int kept = 0;
-    for (int i0 = 0; i0 < n; i0 += 32) {
-        const int i = i0 + lane;
-        const bool k = i < n && (buf[i] >> 24) >= thr;
-        kept += __popc(__ballot_sync(0xFFFFFFFFu, k));
-    }
-    if (kept == 0) return;
-    int basepos = 0;
-    if (lane == 0) basepos = atomicAdd(&cand_cnt[b * g.nlevels + level], kept);
-    basepos = __shfl_sync(0xFFFFFFFFu, basepos, 0);
+    const int n = min(raw_cnt[b * g.nlevels + level], L.cand_cap);
+    const int per = ((n + FV_CHUNKS * FV_THREADS - 1) / (FV_CHUNKS * FV_THREADS)) * FV_THREADS;
+    const int lo = chunk * per, hi = min(lo + per, n);
+    if (lo >= hi) return;
+    const uint2* raw = raw_list + (size_t)b * g.cand_total + L.cand_off;
+    const uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
     uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
-    for (int i0 = 0; i0 < n; i0 += 32) {
-        const int i = i0 + lane;
-        const uint32_t e = i < n ? buf[i] : 0u;
-        const bool k = i < n && (e >> 24) >= thr;
-        const unsigned bal = __ballot_sync(0xFFFFFFFFu, k);
-        if (k) {
-            const int pos = basepos + __popc(bal & ((1u << lane) - 1));
-            if (pos < L.cand_cap) out[pos] = e;
+    int* out_cnt = cand_cnt + b * g.nlevels + level;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1;
+    const unsigned ini = (unsigned)g.ini_th;
+    // cell column by multiplication: exact for n < 2^20 / w_cell (n < 4096, w_cell < 60)
+    const unsigned magic = ((1u << 20) + (unsigned)L.w_cell - 1u) / (unsigned)L.w_cell;
+    for (int i0 = lo; i0 < lo + per; i0 += FV_THREADS) {       // whole warps iterate together (ballots below)
+        const int i = i0 + (int)threadIdx.x;
+        uint2 e = make_uint2(0u, 0u);
+        if (i < hi) e = raw[i];
+        // NMS leaves at most three corners in a word of 4 horizontally adjacent pixels (neighbours in different
+        // cells do not suppress each other, so two may be adjacent across a cell boundary)
+        uint32_t keep[3];
+        int nk = 0;
+        unsigned m4 = e.x;
+        const unsigned rowbase = (e.y >> 24) * (unsigned)L.n_cols;
+        while (m4) {
+            const int j = (__ffs(m4) - 1) >> 3;
+            const unsigned bv = (m4 >> (8 * j)) & 0xFFu;
+            m4 &= ~(0xFFu << (8 * j));
+            const unsigned X = (e.y & 0xFFFu) + j;              // relative to the 16-px border
+            const bool k = bv > ini || flags[rowbase + (((X - (B2_EDGE - B2_BORDER)) * magic) >> 20)] == 0;
+            if (k && nk < 3) keep[nk++] = X | (e.y & 0x00FFF000u) | ((bv - 1u) << 24);
         }
-        basepos += __popc(bal);
+        const unsigned b0 = __ballot_sync(0xFFFFFFFFu, nk & 1), b1 = __ballot_sync(0xFFFFFFFFu, nk & 2);
+        const int total = __popc(b0) + 2 * __popc(b1);
+        if (total == 0) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(out_cnt, total);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        int pos = base + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask);
+        for (int k = 0; k < nk; ++k, ++pos)
+            if (pos < L.cand_cap) out[pos] = keep[k];
     }
 }
 
 }  // namespace
 
-void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint8_t* score, int nimg, cudaStream_t s) {
-    if (g.total_fast_tasks <= 0) return;
-    dim3 grid((g.total_fast_tasks + FS_WARPS - 1) / FS_WARPS, nimg);
-    fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, score);
+void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
+                          cudaStream_t s) {
+    if (g.total_fast_tasks[0] <= 0) return;
+    // long bands (less halo work per output row) once the batch alone fills the machine several times over
+    const int variant = (long long)g.total_fast_tasks[1] * nimg >= 148LL * 16 * 4 ? 1 : 0;
+    dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);
+    fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, raw, raw_cnt, cell_ini, variant);
 }
 
-void b2_launch_fast_cells(const B2Geom& g, const uint8_t* score, uint32_t* cand, int* cand_cnt, int nimg, cudaStream_t s) {
-    if (g.total_cells <= 0) return;
-    dim3 grid((g.total_cells + FC_WARPS - 1) / FC_WARPS, nimg);
-    fast_cells_kernel<<<grid, FC_WARPS * 32, 0, s>>>(g, score, cand, cand_cnt);
+void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
+                         int* cand_cnt, int nimg, cudaStream_t s) {
+    dim3 grid(g.nlevels * FV_CHUNKS, nimg);
+    fast_vote_kernel<<<grid, FV_THREADS, 0, s>>>(g, raw, raw_cnt, cell_ini, cand, cand_cnt);
 }
