@@ -907,7 +907,7 @@ int b2orb_match(b2orb_handle* h, const uint8_t* query, int nq, const uint8_t* tr
     if (!h || nq < 0 || nt < 0) return B2ORB_ERR_INVALID;
     if (nq == 0) return B2ORB_OK;
     if (!query || !train_idx || !dist || (nt > 0 && !train)) return fail(h, B2ORB_ERR_INVALID, "bad match arguments");
-    if (nt >= (1 << 23)) return fail(h, B2ORB_ERR_INVALID, "train set larger than 2^23 rows");
+    if (nt >= (1 << 22)) return fail(h, B2ORB_ERR_INVALID, "train set larger than 2^22 rows");
     if (nt == 0) {   // BFMatcher on an empty train set returns no matches
         for (int i = 0; i < nq; ++i) { train_idx[i] = -1; dist[i] = 0x7fffffff; }
         return B2ORB_OK;
@@ -944,7 +944,7 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
     if (n_right) *n_right = 0;
     if (ncur == 0 || nhist == 0) return B2ORB_OK;   // externalTrack early-out, src/feature-tracker.cpp:237-240
     if (!cur_l || !cur_r || !hist_l || !hist_r || !circ_cur || !circ_hist) return fail(h, B2ORB_ERR_INVALID, "bad temporal arguments");
-    if (nhist >= (1 << 23)) return fail(h, B2ORB_ERR_INVALID, "history larger than 2^23 rows");
+    if (nhist >= (1 << 22)) return fail(h, B2ORB_ERR_INVALID, "history larger than 2^22 rows");
     B2_CUDA(h, cudaSetDevice(h->device));
     int rc = ensure_generic(h, ncur, nhist);
     if (rc) return rc;
