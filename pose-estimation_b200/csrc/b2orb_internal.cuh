@@ -122,4 +122,5 @@ void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
                         const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
                         int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s);
+#define B2_OT_WORDS 24   // quadtree workspace words per node slot (octree.cu)
 int b2_octree_scratch_words(const B2Geom& g);

@@ -375,7 +375,7 @@ int configure(b2orb_handle* h, int w, int hgt) {
         h->d_cell_ini = p + 2 * cnt_bytes;
     }
     if ((size_t)b2_octree_scratch_words(g) * 4 > 200 * 1024) {   // quadtree state too big for shared memory
-        if (!dev_alloc(h, &h->d_ot_scratch, (size_t)nimg * g.node_total * 20)) return B2ORB_ERR_NOMEM;
+        if (!dev_alloc(h, &h->d_ot_scratch, (size_t)nimg * g.node_total * B2_OT_WORDS)) return B2ORB_ERR_NOMEM;
     } else h->d_ot_scratch = nullptr;
     // match problem table: [0,np) stereo pair p (left slot p vs right slot n+p is bound per call because the
     // right slot depends on the batch size) — filled by bind_problems().

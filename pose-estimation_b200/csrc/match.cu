@@ -12,7 +12,7 @@
 
 namespace {
 
-constexpr int MT_WARPS = 8;
+constexpr int MT_WARPS = 4;
 constexpr int MT_THREADS = MT_WARPS * 32;
 constexpr int MT_QPW = 32;                    // query rows per warp: two m16 tiles
 constexpr int MT_QPC = MT_WARPS * MT_QPW;     // query rows per CTA
@@ -38,7 +38,7 @@ __device__ __forceinline__ unsigned expand_q(unsigned w, int j) {
     return j <= 3 ? x << (7 - 2 * j) : x >> (2 * j - 7);
 }
 
-__global__ void __launch_bounds__(MT_THREADS, 2)
+__global__ void __launch_bounds__(MT_THREADS, 4)
 match_kernel(const B2MatchProblem* __restrict__ probs) {
     __shared__ __align__(16) unsigned s_bits[MT_TILE * 8];   // train descriptors of the current pass
     __shared__ __align__(8) int s_cn[MT_TILE];                // (|t| << 22) + global train index, INT_MAX beyond nt

@@ -89,36 +89,16 @@ __device__ __forceinline__ B2Node child_rect(const B2Node& nd, int q, unsigned c
 }
 
 // One expansion round.  partial == false: outer pass; true: sorted partial pass with early stop at N.
+// cc holds the child point counts of every multi-point node of `cur` (filled by the previous round's point pass, or
+// by the root pass); ccn receives the same for the new list while the points are moved: ONE pass over the points
+// per round.
 __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, unsigned short* __restrict__ pnode,
-                         int M, B2Node* cur, B2Node* nxt, unsigned* cc, int* cpos, int* newpos, unsigned* rank,
-                         unsigned* order, unsigned* epre, unsigned* flag, int node_cap, OtShared& sh) {
+                         int M, B2Node* cur, B2Node* nxt, const unsigned* cc, unsigned* ccn, int* cpos, int* newpos,
+                         unsigned* rank, unsigned* order, unsigned* epre, unsigned* flag, int node_cap, OtShared& sh) {
     const int tid = threadIdx.x;
     const int lsz = sh.lsz;
-    // 1. candidates = multi-point nodes; zero child counters
-    for (int i = tid; i < lsz; i += OT_THREADS) {
-        flag[i] = cur[i].cnt > 1 ? 1u : 0u;
-        cc[4 * i] = cc[4 * i + 1] = cc[4 * i + 2] = cc[4 * i + 3] = 0;
-    }
-    __syncthreads();
-    // 2. child point counts of every candidate
-    // (point loops are batched OT_ILP deep: the passes are chains of dependent L2 loads, so the loads of several
-    //  points are issued before any of them is used)
-    for (int p0 = tid; p0 < M; p0 += OT_ILP * OT_THREADS) {
-        int nn[OT_ILP];
-        uint32_t vv[OT_ILP];
-#pragma unroll
-        for (int k = 0; k < OT_ILP; ++k) {
-            const int p = p0 + k * OT_THREADS;
-            nn[k] = p < M ? (int)pnode[p] : -1;
-            vv[k] = p < M ? pts[p] : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < OT_ILP; ++k) {
-            if (nn[k] < 0) continue;
-            const B2Node nd = cur[nn[k]];
-            if (nd.cnt > 1) atomicAdd(&cc[4 * nn[k] + quadrant(nd, vv[k] & 0xFFF, (vv[k] >> 12) & 0xFFF)], 1u);
-        }
-    }
+    // 1. candidates = multi-point nodes
+    for (int i = tid; i < lsz; i += OT_THREADS) flag[i] = cur[i].cnt > 1 ? 1u : 0u;
     __syncthreads();
     // 3. expansion order: rank r of candidate i, order[r] = i
     //    flag -> compact candidate index (list order)
@@ -200,6 +180,7 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
             for (int q = 3; q >= 0; --q) {
                 if (cs[q]) {
                     nxt[pos] = child_rect(nd, q, cs[q]);
+                    ccn[4 * pos] = ccn[4 * pos + 1] = ccn[4 * pos + 2] = ccn[4 * pos + 3] = 0;
                     cpos[4 * i + q] = pos;
                     multi += cs[q] > 1;
                     ++pos;
@@ -209,13 +190,16 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
         } else {
             const int pos = t_children + (int)flag[i];
             nxt[pos] = nd;
+            ccn[4 * pos] = ccn[4 * pos + 1] = ccn[4 * pos + 2] = ccn[4 * pos + 3] = 0;
             newpos[i] = pos;
             multi += nd.cnt > 1;
         }
     }
     if (multi) atomicAdd(&sh.n_multi, multi);
     __syncthreads();
-    // 7. move the points
+    // 7. move the points and count them into the children of their new node (next round's cc)
+    // (point loops are batched OT_ILP deep: the pass is a chain of dependent L2 loads, so the loads of several
+    //  points are issued before any of them is used)
     for (int p0 = tid; p0 < M; p0 += OT_ILP * OT_THREADS) {
         int nn[OT_ILP];
         uint32_t vv[OT_ILP];
@@ -229,9 +213,14 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
         for (int k = 0; k < OT_ILP; ++k) {
             if (nn[k] < 0) continue;
             const int n = nn[k];
-            const int np = newpos[n];
-            pnode[p0 + k * OT_THREADS] =
-                (unsigned short)(np >= 0 ? np : cpos[4 * n + quadrant(cur[n], vv[k] & 0xFFF, (vv[k] >> 12) & 0xFFF)]);
+            const int x = vv[k] & 0xFFF, y = (vv[k] >> 12) & 0xFFF;
+            int np = newpos[n];
+            if (np < 0) {
+                np = cpos[4 * n + quadrant(cur[n], x, y)];
+                pnode[p0 + k * OT_THREADS] = (unsigned short)np;
+            } else if (np != n) pnode[p0 + k * OT_THREADS] = (unsigned short)np;
+            const B2Node nd = nxt[np];
+            if (nd.cnt > 1) atomicAdd(&ccn[4 * np + quadrant(nd, x, y)], 1u);
         }
     }
     __syncthreads();
@@ -259,18 +248,19 @@ octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ can
         if (tid == 0) sel_cnt[b * g.nlevels + level] = 0;
         return;
     }
-    // workspace carve-up (20*Q words): two node arrays (3 words each), then 14*Q words of scratch
-    unsigned* ws = use_global ? gscratch + ((size_t)b * g.node_total + L.node_off) * 20 : dyn;
+    // workspace carve-up (B2_OT_WORDS*Q words): two node arrays (3 words each), two child-count arrays, scratch
+    unsigned* ws = use_global ? gscratch + ((size_t)b * g.node_total + L.node_off) * B2_OT_WORDS : dyn;
     B2Node* cur = reinterpret_cast<B2Node*>(ws);
     B2Node* nxt = reinterpret_cast<B2Node*>(ws + 3 * Q);
     unsigned* cc = ws + 6 * Q;
-    int* cpos = reinterpret_cast<int*>(ws + 10 * Q);
-    int* newpos = reinterpret_cast<int*>(ws + 14 * Q);
-    unsigned* rank = ws + 15 * Q;
-    unsigned* order = ws + 16 * Q;
-    unsigned* epre = ws + 17 * Q;
-    unsigned* flag = ws + 18 * Q;
-    unsigned* best = ws + 19 * Q;
+    unsigned* ccn = ws + 10 * Q;
+    int* cpos = reinterpret_cast<int*>(ws + 14 * Q);
+    int* newpos = reinterpret_cast<int*>(ws + 18 * Q);
+    unsigned* rank = ws + 19 * Q;
+    unsigned* order = ws + 20 * Q;
+    unsigned* epre = ws + 21 * Q;
+    unsigned* flag = ws + 22 * Q;
+    unsigned* best = ws + 23 * Q;
 
     // roots (:543-590): nIni = round(W'/H'), hX = W'/nIni; point -> root (int)(x / hX); empty roots dropped
     const int n_ini = L.n_ini;
@@ -301,10 +291,16 @@ octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ can
         sh.lsz = k;
     }
     __syncthreads();
+    for (int i = tid; i < 4 * sh.lsz; i += OT_THREADS) cc[i] = 0;
+    __syncthreads();
     for (int p = tid; p < M; p += OT_THREADS) {
-        int r = (int)((float)(pts[p] & 0xFFF) / h_x);
+        const uint32_t v = pts[p];
+        int r = (int)((float)(v & 0xFFF) / h_x);
         r = min(r, n_ini - 1);
-        pnode[p] = (unsigned short)sh.root_map[r];
+        const int n = sh.root_map[r];
+        pnode[p] = (unsigned short)n;
+        const B2Node nd = cur[n];
+        if (nd.cnt > 1) atomicAdd(&cc[4 * n + quadrant(nd, v & 0xFFF, (v >> 12) & 0xFFF)], 1u);
     }
     __syncthreads();
 
@@ -312,16 +308,16 @@ octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ can
     bool finish = false;
     while (!finish) {
         int prev = sh.lsz;
-        ot_round(false, N, pts, pnode, M, cur, nxt, cc, cpos, newpos, rank, order, epre, flag, Q, sh);
-        { B2Node* t = cur; cur = nxt; nxt = t; }
+        ot_round(false, N, pts, pnode, M, cur, nxt, cc, ccn, cpos, newpos, rank, order, epre, flag, Q, sh);
+        { B2Node* t = cur; cur = nxt; nxt = t; unsigned* u = cc; cc = ccn; ccn = u; }
         int lsz = sh.lsz;
         if (lsz < 0) break;
         if (lsz >= N || lsz == prev) finish = true;
         else if (lsz + 3 * sh.n_multi > N) {
             while (!finish) {
                 prev = sh.lsz;
-                ot_round(true, N, pts, pnode, M, cur, nxt, cc, cpos, newpos, rank, order, epre, flag, Q, sh);
-                { B2Node* t = cur; cur = nxt; nxt = t; }
+                ot_round(true, N, pts, pnode, M, cur, nxt, cc, ccn, cpos, newpos, rank, order, epre, flag, Q, sh);
+                { B2Node* t = cur; cur = nxt; nxt = t; unsigned* u = cc; cc = ccn; ccn = u; }
                 lsz = sh.lsz;
                 if (lsz < 0 || lsz >= N || lsz == prev) finish = true;
             }
@@ -375,7 +371,7 @@ octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ can
 int b2_octree_scratch_words(const B2Geom& g) {
     int q = 0;
     for (int l = 0; l < g.nlevels; ++l) q = q > g.lv[l].node_cap ? q : g.lv[l].node_cap;
-    return 20 * q;
+    return B2_OT_WORDS * q;
 }
 
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,

@@ -115,6 +115,22 @@ def test_bf_match_matches_oracle(nq, nt, fe, oracle):
     hd.close()
 
 
+@pytest.mark.parametrize("nq,nt", [(5, 7), (300, 9), (257, 1025), (33, 3000)])
+def test_bf_match_extreme_rows(nq, nt, fe, oracle):
+    """Saturated descriptors (all zeros / all ones: distances 0 and 256), random rows, ragged tile sizes."""
+    rng = np.random.default_rng(nq + 31 * nt)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8); t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    q[0] = 0; q[nq // 2] = 0xFF; q[-1] = 0xFF
+    t[nt // 3] = 0; t[-1] = 0xFF; t[0] = 0xFF
+    hd = fe.Handle(500, 1.2, 8, 20, 7, 128, 128, max_images=2)
+    for qq, tt in ((q, t), (q, t[-1:]), (q[:1], t[:1]), (np.zeros((3, 32), np.uint8), np.full((2, 32), 0xFF, np.uint8))):
+        ti, di = hd.match(qq, tt)
+        oi, od = oracle.bf_match(qq, tt)
+        assert np.array_equal(ti, oi) and np.array_equal(di, od)
+    assert hd.match(np.zeros((3, 32), np.uint8), np.full((2, 32), 0xFF, np.uint8))[1].tolist() == [256, 256, 256]
+    hd.close()
+
+
 @pytest.mark.parametrize("shape,npairs", [("euroc", 3), ("kitti", 2), ("cfsd", 4)])
 def test_stereo_frontend_matches_oracle(shape, npairs, fe, oracle, synth):
     """internalMatch (extract L/R + BF match + min-dist/row filter) and the temporal circular matching."""
