@@ -313,6 +313,15 @@ def main():
     # per_kernel is bytes per PAIR (both eyes); one profiled step covers prof_pairs pairs in `launches_per_step` launches
     dom_bytes = per_kernel.get(dom, 0) * prof_pairs / max(launches_per_step, 1)
     achieved = dom_bytes / (dom_ms_per_launch * 1e-3) / 1e9 if dom_ms_per_launch > 0 else 0.0
+    # DRAM traffic of that kernel from the committed ncu --set full capture (tools/ncu_traffic.py), scaled from the
+    # captured launch to this launch by image count; only valid for the workload it was captured on
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r1", "traffic.json")
+    if args.workload == "kitti" and os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if dom in tj["kernels"]:
+            traffic = tj["kernels"][dom]["dram_bytes_per_image"] * 2 * prof_pairs / max(launches_per_step, 1)
+            traffic_src = f"profiles/r1/traffic.json ({tj['source']}, {tj['images_per_launch']} images/launch, scaled by image count)"
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -323,7 +332,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms_per_launch,
                      "kernel_time_shares": shares,
                      "kernel_us_per_pair": {k: round(v[0] * 1e3 / (psteps * prof_pairs), 3) for k, v in prof.items() if v[1]}},

@@ -2,8 +2,10 @@
 # One gpurun call: GPU parity tests, smoke, a bench line, the ncu launch list and one --set full capture
 # of the kernels named in $1 (regex, default: the FAST kernel).  Outputs land in gpurun_out/.
 set -u
-K=${1:-fast_cells_kernel}
+K=${1:-fast_score_kernel}
 TAG=${2:-r1}
+SKIP=${3:-6}
+CNT=${4:-8}
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"
 tail -3 gpurun_out/${TAG}_pytest.log
@@ -15,5 +17,5 @@ $P > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${TAG}_launches.csv $P > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu list rc=$?"
 $P > gpurun_out/${TAG}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"$K" -s 6 -c 8 -f -o gpurun_out/${TAG}_prof $P > gpurun_out/${TAG}_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"$K" -s $SKIP -c $CNT -f -o gpurun_out/${TAG}_prof $P > gpurun_out/${TAG}_ncu2.log 2>&1
 echo "ncu full rc=$?"
