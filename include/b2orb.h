@@ -95,7 +95,7 @@ int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int w
 
 /* cv::BFMatcher(cv::NORM_HAMMING).match(query, train, matches): one result per query row in query
  * order; train_idx = nearest train row (lowest index on ties), dist = Hamming distance.
- * nt == 0 -> train_idx = -1, dist = INT32_MAX.  Host pointers, 32-byte descriptor rows. */
+ * nt == 0 -> train_idx = -1, dist = INT32_MAX.  Host pointers, 32-byte descriptor rows, nt < 2^22. */
 int b2orb_match(b2orb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, int32_t* train_idx,
                 int32_t* dist);
 
@@ -126,7 +126,11 @@ typedef struct b2orb_stereo_out {
  * dist < max(match_ratio*minDist, min_match_dist) and |yL - yR| < max_vertical_pixel_dist.
  * With temporal != 0 it also runs the matching parts of externalTrack (:258-259,293-296,303-321) between
  * consecutive pairs: cur = kept descriptors of pair p, hist = those of pair p-1 (the last pair of the
- * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers. */
+ * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers (pinned memory, see
+ * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 32 pairs are processed as a pipeline
+ * of chunks on internal streams so that the H2D copy, the kernels and the D2H copy of different chunks overlap;
+ * results do not depend on the chunking.  Environment: B2ORB_PIPE_CHUNK (pairs per chunk, 0 = off, read at
+ * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3). */
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
                           int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
 
