@@ -127,7 +127,7 @@ typedef struct b2orb_stereo_out {
  * With temporal != 0 it also runs the matching parts of externalTrack (:258-259,293-296,303-321) between
  * consecutive pairs: cur = kept descriptors of pair p, hist = those of pair p-1 (the last pair of the
  * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers (pinned memory, see
- * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 32 pairs are processed as a pipeline
+ * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 64 pairs are processed as a pipeline
  * of chunks on internal streams so that the H2D copy, the kernels and the D2H copy of different chunks overlap;
  * results do not depend on the chunking.  Environment: B2ORB_PIPE_CHUNK (pairs per chunk, 0 = off, read at
  * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3). */

@@ -93,7 +93,7 @@ struct b2orb_handle {
     cudaEvent_t ev_hist = nullptr, ev_done = nullptr;    // history slot written / kernels of the lane's last chunk done
     cudaEvent_t ev_in = nullptr, ev_out = nullptr;       // lane: chunk copied in / results copied out
     cudaStream_t s_in = nullptr, s_out = nullptr;        // root: copy-in and copy-out streams of the pipelined path
-    int pipe_chunk = 32, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
+    int pipe_chunk = 64, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
 namespace {

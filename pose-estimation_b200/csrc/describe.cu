@@ -95,14 +95,14 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned
 }
 
 
-constexpr int DS_KPW = 4;            // keypoints per warp (amortises the weight-table copy)
+constexpr int DS_KPW = 8;            // keypoints per warp (amortises the weight-table copy)
 constexpr int WA_ROWS = 31, WA_WORDS = 9;    // un-blurred window: rows cy-15..cy+15, 36 bytes from (cx-15) & ~3
 constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..cy+18, 40 bytes from (cx-18) & ~3
 
 // The descriptor's 512 single-byte gathers and the orientation's 31 short rows are L1-wavefront bound when done
 // straight from global memory (ncu: lg/mio throttle), so each warp first copies the two windows of its keypoint into
 // shared memory with coalesced 32-bit loads and gathers from there.
-__global__ void __launch_bounds__(DS_WARPS * 32, 3)
+__global__ void __launch_bounds__(DS_WARPS * 32, 2)
 describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
                 const int* __restrict__ sel_cnt, const unsigned* __restrict__ ic_table, KeyPointOut* __restrict__ kps,
                 uint8_t* __restrict__ desc, int* __restrict__ n_out) {
@@ -134,43 +134,57 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     const int ra_row = lane / 9, ra_col = lane - ra_row * 9;      // staging roles (fixed per lane)
     const int rb_row = lane / 10, rb_col = lane - rb_row * 10;
 
-    for (int it = 0; it < DS_KPW; ++it) {
-        const int slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;   // output slot in this image
-        if (slot >= total || slot >= g.kp_cap) break;
+    // Software pipeline over the warp's keypoints: the window loads of keypoint k+1 are issued right after the
+    // windows of keypoint k went to shared memory, so their latency hides behind k's orientation + descriptor math.
+    struct Kp { int slot, level, cx, cy; float response; bool valid; };
+    unsigned ra[11], rb[13];
+    const auto fetch = [&](int it) {
+        Kp k;
+        k.slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;      // output slot in this image
+        k.valid = it < DS_KPW && k.slot < total && k.slot < g.kp_cap;
+        k.level = 0; k.cx = k.cy = 0; k.response = 0.f;
+        if (!k.valid) return k;
         // level = number of levels whose inclusive prefix is <= slot
-        const int level = __popc(__ballot_sync(0xFFFFFFFFu, lane < g.nlevels && pre <= slot));
-        const int base = level ? __shfl_sync(0xFFFFFFFFu, pre, level - 1) : 0;
-        const B2Level& L = g.lv[level];
-        const uint32_t v = sel[(size_t)b * g.sel_total + L.sel_base + (slot - base)];
-        const int cx = (int)(v & 0xFFF) + B2_BORDER, cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
-        const float response = (float)(v >> 24);
+        k.level = __popc(__ballot_sync(0xFFFFFFFFu, lane < g.nlevels && pre <= k.slot));
+        const int base = k.level ? __shfl_sync(0xFFFFFFFFu, pre, k.level - 1) : 0;
+        const B2Level& L = g.lv[k.level];
+        const uint32_t v = sel[(size_t)b * g.sel_total + L.sel_base + (k.slot - base)];
+        k.cx = (int)(v & 0xFFF) + B2_BORDER;
+        k.cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
+        k.response = (float)(v >> 24);
         int pitch;
-        const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
+        const uint8_t* img = b2_level_ptr(g, im, b, k.level, pitch);
         const uint8_t* bl = im.blur + (size_t)b * g.slab + L.off;
         const int bp = L.pitch;
-
-        // ---- stage both windows (all loads first, then the stores)
-        const int ax = (cx - B2_HALF_PATCH) & ~3, a = (cx - B2_HALF_PATCH) & 3;
-        const int bx = (cx - 18) & ~3, ab = (cx - 18) & 3;
         // lane -> (row within a group of 3, word column): 27 lanes x 11 groups cover the 31 x 9 window A,
         // 30 lanes x 13 groups the 37 x 10 window B; no per-element index arithmetic
-        unsigned ra[11], rb[13];
-        {
-            const uint8_t* pa = img + (size_t)(cy - B2_HALF_PATCH + ra_row) * pitch + ax + 4 * ra_col;
-            const bool oka = lane < 27 && (ra_col < 8 || a >= 2);
+        const int ax = (k.cx - B2_HALF_PATCH) & ~3, a = (k.cx - B2_HALF_PATCH) & 3;
+        const int bx = (k.cx - 18) & ~3;
+        const uint8_t* pa = img + (size_t)(k.cy - B2_HALF_PATCH + ra_row) * pitch + ax + 4 * ra_col;
+        const bool oka = lane < 27 && (ra_col < 8 || a >= 2);
 #pragma unroll
-            for (int k = 0; k < 11; ++k) {
-                ra[k] = (oka && 3 * k + ra_row < WA_ROWS) ? *reinterpret_cast<const unsigned*>(pa) : 0u;
-                pa += 3 * pitch;
-            }
-            const uint8_t* pb = bl + (size_t)(cy - 18 + rb_row) * bp + bx + 4 * rb_col;
-            const bool okb = lane < 30;
-#pragma unroll
-            for (int k = 0; k < 13; ++k) {
-                rb[k] = (okb && 3 * k + rb_row < WB_ROWS) ? *reinterpret_cast<const unsigned*>(pb) : 0u;
-                pb += 3 * bp;
-            }
+        for (int i = 0; i < 11; ++i) {
+            ra[i] = (oka && 3 * i + ra_row < WA_ROWS) ? *reinterpret_cast<const unsigned*>(pa) : 0u;
+            pa += 3 * pitch;
         }
+        const uint8_t* pb = bl + (size_t)(k.cy - 18 + rb_row) * bp + bx + 4 * rb_col;
+        const bool okb = lane < 30;
+#pragma unroll
+        for (int i = 0; i < 13; ++i) {
+            rb[i] = (okb && 3 * i + rb_row < WB_ROWS) ? *reinterpret_cast<const unsigned*>(pb) : 0u;
+            pb += 3 * bp;
+        }
+        return k;
+    };
+
+    Kp nxt = fetch(0);
+    for (int it = 0; it < DS_KPW; ++it) {
+        const Kp cur = nxt;
+        if (!cur.valid) break;
+        const int slot = cur.slot, level = cur.level, cx = cur.cx, cy = cur.cy;
+        const float response = cur.response;
+        const B2Level& L = g.lv[level];
+        const int a = (cx - B2_HALF_PATCH) & 3, ab = (cx - 18) & 3;
         __syncwarp();                                   // previous keypoint's gathers are done
 #pragma unroll
         for (int k = 0; k < 11; ++k)
@@ -179,6 +193,7 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
         for (int k = 0; k < 13; ++k)
             if (lane < 30 && 3 * k + rb_row < WB_ROWS) wb[(3 * k + rb_row) * WB_WORDS + rb_col] = rb[k];
         __syncwarp();
+        nxt = fetch(it + 1);                            // loads in flight during the math below
 
         // ---- IC_Angle (src/ORBextractor.cc:77-104): lane = patch row v = lane-15, IDP.4A against per-(alignment, |v|)
         // weights: wu = u inside the disc |u| <= umax[|v|] (-> m10), wm = 1 inside the disc (-> row sum -> m01)

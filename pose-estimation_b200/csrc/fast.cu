@@ -268,15 +268,16 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
 
 // ---------------------------------------------------------------------------------------------------
 constexpr int FV_THREADS = 256;
-constexpr int FV_CHUNKS = 4;       // CTAs per (image, level)
+constexpr int FV_MAX_CHUNKS = 32;  // CTAs per (image, level): 4 for large batches, more when few images are in flight
 
 __global__ void __launch_bounds__(FV_THREADS)
 fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw_list, const int* __restrict__ raw_cnt,
-                 const uint8_t* __restrict__ cell_ini, uint32_t* __restrict__ cand, int* __restrict__ cand_cnt) {
-    const int level = blockIdx.x / FV_CHUNKS, chunk = blockIdx.x - level * FV_CHUNKS, b = blockIdx.y;
+                 const uint8_t* __restrict__ cell_ini, uint32_t* __restrict__ cand, int* __restrict__ cand_cnt,
+                 int chunks) {
+    const int level = blockIdx.x / chunks, chunk = blockIdx.x - level * chunks, b = blockIdx.y;
     const B2Level& L = g.lv[level];
     const int n = min(raw_cnt[b * g.nlevels + level], L.cand_cap);
-    const int per = ((n + FV_CHUNKS * FV_THREADS - 1) / (FV_CHUNKS * FV_THREADS)) * FV_THREADS;
+    const int per = ((n + chunks * FV_THREADS - 1) / (chunks * FV_THREADS)) * FV_THREADS;
     const int lo = chunk * per, hi = min(lo + per, n);
     if (lo >= hi) return;
     const uint2* raw = raw_list + (size_t)b * g.cand_total + L.cand_off;
@@ -331,6 +332,8 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* 
 
 void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
                          int* cand_cnt, int nimg, cudaStream_t s) {
-    dim3 grid(g.nlevels * FV_CHUNKS, nimg);
-    fast_vote_kernel<<<grid, FV_THREADS, 0, s>>>(g, raw, raw_cnt, cell_ini, cand, cand_cnt);
+    int chunks = 4;
+    while (chunks < FV_MAX_CHUNKS && g.nlevels * chunks * nimg < 148 * 8) chunks *= 2;
+    dim3 grid(g.nlevels * chunks, nimg);
+    fast_vote_kernel<<<grid, FV_THREADS, 0, s>>>(g, raw, raw_cnt, cell_ini, cand, cand_cnt, chunks);
 }
