@@ -8,6 +8,8 @@
 //     compaction in query order, gather of the kept descriptor rows (_curDescriptorsL/R).
 //   * circular_kernel — externalTrack, :258-259, 293-296, 303-321 (useRANSAC=false): distance filter on both
 //     sides and the circular test mapCurHist[queryIdx] == trainIdx.
+#include <cstdlib>
+
 #include "b2orb_internal.cuh"
 
 namespace {
@@ -260,6 +262,176 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
 
 }  // namespace
 
+// =================================================================================================
+// tcgen05 matcher: the same contraction on the 5th-generation tensor cores.
+//   popcount(q xor t) = (256 - q'.t') / 2   with q' = 1 - 2q, t' = 1 - 2t in {+1,-1}^256 (signed 8-bit),
+// so the accumulator alone orders the candidates (no |q|, |t| terms) and the epilogue is a running max.
+// One CTA = 128 query rows (TMEM lane = query row = thread).  Bits are expanded to +-1 bytes in registers
+// (shift, PRMT sign-replicate, OR 1) and stored to shared memory in the canonical K-major no-swizzle UMMA layout:
+//   byte (row r, k) of a 128 x 256 operand tile at  (k / 16) * 2048 + r * 16 + k % 16
+// (8-row x 16-byte core matrices; LBO = 2048 B between 16-byte K chunks, SBO = 128 B between 8-row groups).
+// Per train tile of 128 rows one elected thread issues 8 x tcgen05.mma.kind::i8 (M128 N128 K32) into one of two
+// 128-column TMEM accumulator stages and commits to an mbarrier; the expansion of the next tile and the epilogue of
+// the previous one overlap the tensor pipe.  k order inside a row is free (both operands use the same one):
+// byte 32 s + 4 j + i is bit 8 i + j of 32-bit word s.
+constexpr int TC_ROWS = 128;                       // M and N of one MMA
+constexpr int TC_TILE = TC_ROWS * 256;             // bytes of one expanded operand tile
+constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((TC_ROWS >> 3) << 17) | ((TC_ROWS >> 4) << 24);
+//                             D = s32     A = s8      B = s8       N >> 3                  M >> 4        (K-major A, B)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(2048 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
+}
+
+// msb of every byte replicated over the byte (prmt with the sign-replicate bit of each selector nibble set;
+// __byte_perm only honours the low three selector bits, hence the PTX)
+__device__ __forceinline__ unsigned tc_sign_bytes(unsigned x) {
+    unsigned d;
+    asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(d) : "r"(x));
+    return d;
+}
+
+// one descriptor row (8 words) -> 256 bytes of +-1 at row r of the tile at generic address `tile`
+__device__ __forceinline__ void tc_expand_row(uint8_t* tile, int r, const uint4& lo, const uint4& hi, bool valid) {
+    const unsigned w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        unsigned e[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)   // bit 8i + j -> msb of byte i -> 0x00 / 0xFF -> +1 / -1
+            e[j] = valid ? (tc_sign_bytes(w[s] << (7 - j)) | 0x01010101u) : 0u;
+        *reinterpret_cast<uint4*>(tile + (2 * s) * 2048 + r * 16) = make_uint4(e[0], e[1], e[2], e[3]);
+        *reinterpret_cast<uint4*>(tile + (2 * s + 1) * 2048 + r * 16) = make_uint4(e[4], e[5], e[6], e[7]);
+    }
+}
+
+__device__ __forceinline__ void tc_mbar_wait(uint32_t mbar, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+                 "@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}" ::"r"(mbar), "r"(parity) : "memory");
+}
+
+// 8 MMAs (K = 256) of one 128 x 128 tile into TMEM columns [tmem_d, tmem_d + 128), then commit -> mbarrier
+__device__ __forceinline__ void tc_issue_tile(uint32_t tmem_d, uint32_t sa, uint32_t sb, uint32_t mbar) {
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const uint64_t da = tc_smem_desc(sa + s * 4096), db = tc_smem_desc(sb + s * 4096);
+        const uint32_t acc = s > 0, zero = 0;
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+                     ::"r"(tmem_d), "l"(da), "l"(db), "r"(TC_IDESC), "r"(acc), "r"(zero) : "memory");
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar) : "memory");
+}
+
+__global__ void __launch_bounds__(TC_ROWS, 2)
+match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
+    extern __shared__ __align__(1024) uint8_t tc_smem[];       // A tile, then two B tiles
+    __shared__ __align__(8) uint64_t s_mbar[2];
+    __shared__ uint32_t s_tmem;
+    const B2MatchProblem P = probs[blockIdx.y];
+    const int nq = *P.nq, nt = *P.nt;
+    const int q0 = blockIdx.x * TC_ROWS;
+    if (q0 >= nq) return;
+    const int tid = threadIdx.x, wid = tid >> 5;
+    const int row = q0 + tid;
+    if (nt <= 0) {
+        if (row < nq) { P.train_idx[row] = -1; P.dist[row] = 0x7fffffff; }
+        return;
+    }
+    uint8_t* sA = tc_smem;
+    uint8_t* sB = tc_smem + TC_TILE;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar[1])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (wid == 0) {   // two accumulator stages of 128 columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(256) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // query tile
+        uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+        if (row < nq) {
+            const uint4* qp = reinterpret_cast<const uint4*>(P.q + (size_t)row * 32);
+            lo = qp[0]; hi = qp[1];
+        }
+        tc_expand_row(sA, tid, lo, hi, row < nq);
+    }
+    const uint4* tp = reinterpret_cast<const uint4*>(P.t);
+    const auto expand_b = [&](int tile) {
+        const int tr = tile * TC_ROWS + tid;
+        uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+        if (tr < nt) { lo = tp[2 * (size_t)tr]; hi = tp[2 * (size_t)tr + 1]; }
+        tc_expand_row(sB + (tile & 1) * TC_TILE, tid, lo, hi, tr < nt);
+    };
+    const int ntiles = (nt + TC_ROWS - 1) / TC_ROWS;
+    expand_b(0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = s_tmem;
+    const uint32_t sa = smem_u32(sA), sb = smem_u32(sB);
+    const uint32_t mb0 = smem_u32(&s_mbar[0]);
+    if (tid == 0) tc_issue_tile(tmem, sa, sb, mb0);
+
+    int best_acc = -100000, best_idx = 0;
+    for (int i = 0; i < ntiles; ++i) {
+        if (i + 1 < ntiles) expand_b(i + 1);                    // its buffer was last read by MMA i-1 (completed)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();                                        // also: epilogue i-1 drained accumulator stage (i+1)&1
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (i + 1 < ntiles && tid == 0)
+            tc_issue_tile(tmem + ((i + 1) & 1) * TC_ROWS, sa, sb + ((i + 1) & 1) * TC_TILE, mb0 + ((i + 1) & 1) * 8);
+        tc_mbar_wait(mb0 + (i & 1) * 8, (i >> 1) & 1);          // MMA i done
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // ---- epilogue: this thread's row, 128 columns in chunks of 32 ----
+        const int t0 = i * TC_ROWS;
+        const int nvalid = nt - t0;                             // >= 1
+        const uint32_t taddr = tmem + (i & 1) * TC_ROWS + ((uint32_t)(wid * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            int v[32];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                         "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                           "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                           "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                         : "r"(taddr + c * 32));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (nvalid < TC_ROWS) {                              // last, partial tile: padded train rows never win
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                    if (c * 32 + k >= nvalid) v[k] = -100000;
+            }
+            int cm = v[0];
+#pragma unroll
+            for (int k = 1; k < 31; k += 2) cm = __vimax3_s32(cm, v[k], v[k + 1]);
+            cm = max(cm, v[31]);
+            if (cm > best_acc) {                                 // strict: earlier (lower index) columns keep ties
+                int first = 31;
+#pragma unroll
+                for (int k = 30; k >= 0; --k)
+                    if (v[k] == cm) first = k;
+                best_acc = cm;
+                best_idx = t0 + c * 32 + first;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
+    if (row < nq) {
+        P.train_idx[row] = best_idx;
+        P.dist[row] = (256 - best_acc) >> 1;
+    }
+}
+
 // Stereo problems [0,np): desc(left p) vs desc(right np+p).  Temporal problems [np, 3np): cur slot p+1 vs hist
 // slot p, left then right (src/feature-tracker.cpp:161-163, 258, 303).
 __global__ void bind_kernel(B2MatchProblem* pr, int np, B2BindBases b) {
@@ -277,8 +449,16 @@ void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStr
 
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s) {
     if (nprob <= 0 || max_nq <= 0) return;
-    dim3 grid((max_nq + MT_QPC - 1) / MT_QPC, nprob);
-    match_kernel<<<grid, MT_THREADS, 0, s>>>(probs);
+    static const bool use_imma = [] { const char* e = getenv("B2ORB_MATCH"); return e && e[0] == 'i'; }();
+    if (use_imma) {   // warp-level IMMA version, kept for A/B measurements (B2ORB_MATCH=imma)
+        dim3 grid((max_nq + MT_QPC - 1) / MT_QPC, nprob);
+        match_kernel<<<grid, MT_THREADS, 0, s>>>(probs);
+        return;
+    }
+    const int smem = 3 * TC_TILE;
+    cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device; cheap
+    dim3 grid((max_nq + TC_ROWS - 1) / TC_ROWS, nprob);
+    match_tc_kernel<<<grid, TC_ROWS, smem, s>>>(probs);
 }
 
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
