@@ -264,10 +264,11 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
 
 // =================================================================================================
 // tcgen05 matcher: the same contraction on the 5th-generation tensor cores.
-//   popcount(q xor t) = (256 - q'.t') / 2   with q' = 1 - 2q, t' = 1 - 2t in {+1,-1}^256 (signed 8-bit),
-// so the accumulator alone orders the candidates (no |q|, |t| terms) and the epilogue is a running max.
-// One CTA = 128 query rows (TMEM lane = query row = thread).  Bits are expanded to +-1 bytes in registers
-// (shift, PRMT sign-replicate, OR 1) and stored to shared memory in the canonical K-major no-swizzle UMMA layout:
+//   popcount(q xor t) = |q| + sum_k (2 q_k - 1)(-t_k)      (signed 8-bit operands: q' in {+1,-1}, t' in {0,-1}),
+// so the accumulator alone orders the candidates of a query row (|q| is added once at the end) and the epilogue is
+// a running min of (accumulator, column) keys.
+// One CTA = 128 query rows (TMEM lane = query row = thread).  Bits are expanded to bytes in registers (shift, PRMT
+// sign-replicate: 0x00 / 0xFF = 0 / -1 for the train side, one more LOP3 makes +-1 on the query side) and stored to shared memory in the canonical K-major no-swizzle UMMA layout:
 //   byte (row r, k) of a 128 x 256 operand tile at  (k / 16) * 2048 + r * 16 + k % 16
 // (8-row x 16-byte core matrices; LBO = 2048 B between 16-byte K chunks, SBO = 128 B between 8-row groups).
 // Per train tile of 128 rows one elected thread issues 8 x tcgen05.mma.kind::i8 (M128 N128 K32) into one of two
@@ -294,14 +295,18 @@ __device__ __forceinline__ unsigned tc_sign_bytes(unsigned x) {
 }
 
 // one descriptor row (8 words) -> 256 bytes of +-1 at row r of the tile at generic address `tile`
-__device__ __forceinline__ void tc_expand_row(uint8_t* tile, int r, const uint4& lo, const uint4& hi, bool valid) {
+// QUERY: bit 1 -> +1, bit 0 -> -1;  train: bit 1 -> -1, bit 0 -> 0.  Rows beyond the set are all-zero words.
+template <bool QUERY>
+__device__ __forceinline__ void tc_expand_row(uint8_t* tile, int r, const uint4& lo, const uint4& hi) {
     const unsigned w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
         unsigned e[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)   // bit 8i + j -> msb of byte i -> 0x00 / 0xFF -> +1 / -1
-            e[j] = valid ? (tc_sign_bytes(w[s] << (7 - j)) | 0x01010101u) : 0u;
+        for (int j = 0; j < 8; ++j) {   // bit 8i + j -> msb of byte i -> 0x00 / 0xFF
+            const unsigned m = tc_sign_bytes(w[s] << (7 - j));
+            e[j] = QUERY ? (~m | 0x01010101u) : m;       // query: 0xFF -> 0x01, 0x00 -> 0xFF
+        }
         *reinterpret_cast<uint4*>(tile + (2 * s) * 2048 + r * 16) = make_uint4(e[0], e[1], e[2], e[3]);
         *reinterpret_cast<uint4*>(tile + (2 * s + 1) * 2048 + r * 16) = make_uint4(e[4], e[5], e[6], e[7]);
     }
@@ -351,22 +356,31 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(256) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    int qpop = 0;
     {   // query tile
         uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
         if (row < nq) {
             const uint4* qp = reinterpret_cast<const uint4*>(P.q + (size_t)row * 32);
             lo = qp[0]; hi = qp[1];
         }
-        tc_expand_row(sA, tid, lo, hi, row < nq);
+        tc_expand_row<true>(sA, tid, lo, hi);
+        qpop = __popc(lo.x) + __popc(lo.y) + __popc(lo.z) + __popc(lo.w) + __popc(hi.x) + __popc(hi.y) + __popc(hi.z) + __popc(hi.w);
     }
     const uint4* tp = reinterpret_cast<const uint4*>(P.t);
-    const auto expand_b = [&](int tile) {
+    // this thread's train row of the NEXT tile to expand is always in registers one iteration ahead (L2 latency)
+    uint4 nlo = make_uint4(0, 0, 0, 0), nhi = nlo;
+    const auto fetch_b = [&](int tile) {
         const int tr = tile * TC_ROWS + tid;
-        uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
-        if (tr < nt) { lo = tp[2 * (size_t)tr]; hi = tp[2 * (size_t)tr + 1]; }
-        tc_expand_row(sB + (tile & 1) * TC_TILE, tid, lo, hi, tr < nt);
+        nlo = nhi = make_uint4(0, 0, 0, 0);
+        if (tr < nt) { nlo = tp[2 * (size_t)tr]; nhi = tp[2 * (size_t)tr + 1]; }
+    };
+    const auto expand_b = [&](int tile) {
+        const uint4 lo = nlo, hi = nhi;
+        fetch_b(tile + 1);
+        tc_expand_row<false>(sB + (tile & 1) * TC_TILE, tid, lo, hi);
     };
     const int ntiles = (nt + TC_ROWS - 1) / TC_ROWS;
+    fetch_b(0);
     expand_b(0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -377,7 +391,8 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
     const uint32_t mb0 = smem_u32(&s_mbar[0]);
     if (tid == 0) tc_issue_tile(tmem, sa, sb, mb0);
 
-    int best_acc = -100000, best_idx = 0;
+    // running min over (accumulator << 12 | column): strict-'<' ascending scan of BFMatcher == lexicographic min
+    int best_key = 0x7FFFFFFF, best_t0 = 0;
     for (int i = 0; i < ntiles; ++i) {
         if (i + 1 < ntiles) expand_b(i + 1);                    // its buffer was last read by MMA i-1 (completed)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -404,31 +419,29 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
                            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                          : "r"(taddr + c * 32));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (nvalid < TC_ROWS) {                              // last, partial tile: padded train rows never win
+            // key = acc * 4096 + column-in-tile (acc in [-256, 256]); padded train rows (last tile) never win
+            int key[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) key[k] = v[k] * 4096 + (c * 32 + k);
+            if (nvalid < TC_ROWS) {
 #pragma unroll
                 for (int k = 0; k < 32; ++k)
-                    if (c * 32 + k >= nvalid) v[k] = -100000;
+                    if (c * 32 + k >= nvalid) key[k] = 0x7FFFFFFF;
             }
-            int cm = v[0];
+            int cm = key[0];
 #pragma unroll
-            for (int k = 1; k < 31; k += 2) cm = __vimax3_s32(cm, v[k], v[k + 1]);
-            cm = max(cm, v[31]);
-            if (cm > best_acc) {                                 // strict: earlier (lower index) columns keep ties
-                int first = 31;
-#pragma unroll
-                for (int k = 30; k >= 0; --k)
-                    if (v[k] == cm) first = k;
-                best_acc = cm;
-                best_idx = t0 + c * 32 + first;
-            }
+            for (int k = 1; k < 31; k += 2) cm = __vimin3_s32(cm, key[k], key[k + 1]);
+            cm = min(cm, key[31]);
+            // compare accumulators across tiles (a later tile wins only with a strictly smaller distance)
+            if ((cm >> 12) < (best_key >> 12)) { best_key = cm; best_t0 = t0; }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
     if (row < nq) {
-        P.train_idx[row] = best_idx;
-        P.dist[row] = (256 - best_acc) >> 1;
+        P.train_idx[row] = best_t0 + (best_key & 0xFFF);
+        P.dist[row] = (best_key >> 12) + qpop;
     }
 }
 
