@@ -296,19 +296,21 @@ __device__ __forceinline__ unsigned tc_sign_bytes(unsigned x) {
 
 // one descriptor row (8 words) -> 256 bytes of +-1 at row r of the tile at generic address `tile`
 // QUERY: bit 1 -> +1, bit 0 -> -1;  train: bit 1 -> -1, bit 0 -> 0.  Rows beyond the set are all-zero words.
+// One thread expands HALF a row: words 4*half .. 4*half+3 of row r.
 template <bool QUERY>
-__device__ __forceinline__ void tc_expand_row(uint8_t* tile, int r, const uint4& lo, const uint4& hi) {
-    const unsigned w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+__device__ __forceinline__ void tc_expand_half(uint8_t* tile, int r, int half, const uint4& q) {
+    const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
+    for (int s = 0; s < 4; ++s) {
         unsigned e[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {   // bit 8i + j -> msb of byte i -> 0x00 / 0xFF
             const unsigned m = tc_sign_bytes(w[s] << (7 - j));
             e[j] = QUERY ? (~m | 0x01010101u) : m;       // query: 0xFF -> 0x01, 0x00 -> 0xFF
         }
-        *reinterpret_cast<uint4*>(tile + (2 * s) * 2048 + r * 16) = make_uint4(e[0], e[1], e[2], e[3]);
-        *reinterpret_cast<uint4*>(tile + (2 * s + 1) * 2048 + r * 16) = make_uint4(e[4], e[5], e[6], e[7]);
+        uint8_t* dst = tile + (size_t)(2 * (4 * half + s)) * 2048 + r * 16;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(e[0], e[1], e[2], e[3]);
+        *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(e[4], e[5], e[6], e[7]);
     }
 }
 
@@ -330,19 +332,23 @@ __device__ __forceinline__ void tc_issue_tile(uint32_t tmem_d, uint32_t sa, uint
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar) : "memory");
 }
 
-__global__ void __launch_bounds__(TC_ROWS, 2)
+constexpr int TC_THREADS = 2 * TC_ROWS;   // two thread groups: each expands half of every row and scans half of the columns
+
+__global__ void __launch_bounds__(TC_THREADS, 2)
 match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
     extern __shared__ __align__(1024) uint8_t tc_smem[];       // A tile, then two B tiles
     __shared__ __align__(8) uint64_t s_mbar[2];
     __shared__ uint32_t s_tmem;
+    __shared__ int s_pop[TC_ROWS], s_key[TC_ROWS], s_t0[TC_ROWS];
     const B2MatchProblem P = probs[blockIdx.y];
     const int nq = *P.nq, nt = *P.nt;
     const int q0 = blockIdx.x * TC_ROWS;
     if (q0 >= nq) return;
     const int tid = threadIdx.x, wid = tid >> 5;
-    const int row = q0 + tid;
+    const int r = tid & (TC_ROWS - 1), grp = tid >> 7;          // row inside the tile, thread group
+    const int row = q0 + r;
     if (nt <= 0) {
-        if (row < nq) { P.train_idx[row] = -1; P.dist[row] = 0x7fffffff; }
+        if (grp == 0 && row < nq) { P.train_idx[row] = -1; P.dist[row] = 0x7fffffff; }
         return;
     }
     uint8_t* sA = tc_smem;
@@ -356,32 +362,23 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(256) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    int qpop = 0;
     {   // query tile
-        uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
-        if (row < nq) {
-            const uint4* qp = reinterpret_cast<const uint4*>(P.q + (size_t)row * 32);
-            lo = qp[0]; hi = qp[1];
-        }
-        tc_expand_row<true>(sA, tid, lo, hi);
-        qpop = __popc(lo.x) + __popc(lo.y) + __popc(lo.z) + __popc(lo.w) + __popc(hi.x) + __popc(hi.y) + __popc(hi.z) + __popc(hi.w);
+        uint4 q = make_uint4(0, 0, 0, 0);
+        if (row < nq) q = reinterpret_cast<const uint4*>(P.q + (size_t)row * 32)[grp];
+        tc_expand_half<true>(sA, r, grp, q);
+        if (grp == 1) s_pop[r] = __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);
+        else s_key[r] = __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);   // read back by the same thread below
     }
     const uint4* tp = reinterpret_cast<const uint4*>(P.t);
-    // this thread's train row of the NEXT tile to expand is always in registers one iteration ahead (L2 latency)
-    uint4 nlo = make_uint4(0, 0, 0, 0), nhi = nlo;
-    const auto fetch_b = [&](int tile) {
-        const int tr = tile * TC_ROWS + tid;
-        nlo = nhi = make_uint4(0, 0, 0, 0);
-        if (tr < nt) { nlo = tp[2 * (size_t)tr]; nhi = tp[2 * (size_t)tr + 1]; }
-    };
-    const auto expand_b = [&](int tile) {
-        const uint4 lo = nlo, hi = nhi;
-        fetch_b(tile + 1);
-        tc_expand_row<false>(sB + (tile & 1) * TC_TILE, tid, lo, hi);
-    };
     const int ntiles = (nt + TC_ROWS - 1) / TC_ROWS;
-    fetch_b(0);
-    expand_b(0);
+    // This thread's half row of the next two train tiles lives in registers (two sets, the loop below is unrolled by
+    // two so that no register copy — which would wait for the load — sits between a load and its use a tile later).
+    const auto fetch_b = [&](int tile) {
+        const int tr = tile * TC_ROWS + r;
+        return tr < nt ? tp[2 * (size_t)tr + grp] : make_uint4(0, 0, 0, 0);
+    };
+    uint4 rb0 = fetch_b(0), rb1 = fetch_b(1);
+    tc_expand_half<false>(sB, r, grp, rb0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -390,11 +387,14 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
     const uint32_t sa = smem_u32(sA), sb = smem_u32(sB);
     const uint32_t mb0 = smem_u32(&s_mbar[0]);
     if (tid == 0) tc_issue_tile(tmem, sa, sb, mb0);
+    const int qpop_half = s_key[r];                              // (group 0: own value; group 1: unused)
 
     // running min over (accumulator << 12 | column): strict-'<' ascending scan of BFMatcher == lexicographic min
     int best_key = 0x7FFFFFFF, best_t0 = 0;
-    for (int i = 0; i < ntiles; ++i) {
-        if (i + 1 < ntiles) expand_b(i + 1);                    // its buffer was last read by MMA i-1 (completed)
+    // one tile step: cur = registers holding tile i+1's half row, nxt = registers to refill with tile i+2's
+    const auto step = [&](int i, const uint4& cur, uint4& nxt) {
+        if (i + 1 < ntiles) tc_expand_half<false>(sB + ((i + 1) & 1) * TC_TILE, r, grp, cur);   // buffer last read by MMA i-1 (completed)
+        nxt = fetch_b(i + 2);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();                                        // also: epilogue i-1 drained accumulator stage (i+1)&1
@@ -403,12 +403,13 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
             tc_issue_tile(tmem + ((i + 1) & 1) * TC_ROWS, sa, sb + ((i + 1) & 1) * TC_TILE, mb0 + ((i + 1) & 1) * 8);
         tc_mbar_wait(mb0 + (i & 1) * 8, (i >> 1) & 1);          // MMA i done
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // ---- epilogue: this thread's row, 128 columns in chunks of 32 ----
+        // ---- epilogue: this thread's row (TMEM lane), its group's 64 columns in two chunks of 32 ----
         const int t0 = i * TC_ROWS;
         const int nvalid = nt - t0;                             // >= 1
-        const uint32_t taddr = tmem + (i & 1) * TC_ROWS + ((uint32_t)(wid * 32) << 16);
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        const uint32_t taddr = tmem + (i & 1) * TC_ROWS + ((uint32_t)((wid & 3) * 32) << 16) + grp * 64;
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int col0 = grp * 64 + cc * 32;
             int v[32];
             asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -417,31 +418,41 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
                            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
                            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
                            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                         : "r"(taddr + c * 32));
+                         : "r"(taddr + cc * 32));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             // key = acc * 4096 + column-in-tile (acc in [-256, 256]); padded train rows (last tile) never win
             int key[32];
 #pragma unroll
-            for (int k = 0; k < 32; ++k) key[k] = v[k] * 4096 + (c * 32 + k);
+            for (int k = 0; k < 32; ++k) key[k] = v[k] * 4096 + (col0 + k);
             if (nvalid < TC_ROWS) {
 #pragma unroll
                 for (int k = 0; k < 32; ++k)
-                    if (c * 32 + k >= nvalid) key[k] = 0x7FFFFFFF;
+                    if (col0 + k >= nvalid) key[k] = 0x7FFFFFFF;
             }
             int cm = key[0];
 #pragma unroll
             for (int k = 1; k < 31; k += 2) cm = __vimin3_s32(cm, key[k], key[k + 1]);
             cm = min(cm, key[31]);
-            // compare accumulators across tiles (a later tile wins only with a strictly smaller distance)
+            // compare accumulators across chunks and tiles (a later one wins only with a strictly smaller distance)
             if ((cm >> 12) < (best_key >> 12)) { best_key = cm; best_t0 = t0; }
         }
+    };
+    for (int i = 0; i < ntiles; i += 2) {
+        step(i, rb1, rb0);
+        if (i + 1 < ntiles) step(i + 1, rb0, rb1);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    if (grp == 1) { s_key[r] = best_key; s_t0[r] = best_t0; }
     __syncthreads();
     if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
-    if (row < nq) {
-        P.train_idx[row] = best_t0 + (best_key & 0xFFF);
-        P.dist[row] = (best_key >> 12) + qpop;
+    if (grp == 0 && row < nq) {
+        // merge with the other group's columns: smaller distance, then smaller train index
+        const int ok = s_key[r], ot = s_t0[r];
+        const int da = best_key >> 12, db = ok >> 12;
+        const int ia = best_t0 + (best_key & 0xFFF), ib = ot + (ok & 0xFFF);
+        const bool other = db < da || (db == da && ib < ia);
+        P.train_idx[row] = other ? ib : ia;
+        P.dist[row] = (other ? db : da) + qpop_half + s_pop[r];
     }
 }
 
@@ -471,7 +482,7 @@ void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStr
     const int smem = 3 * TC_TILE;
     cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device; cheap
     dim3 grid((max_nq + TC_ROWS - 1) / TC_ROWS, nprob);
-    match_tc_kernel<<<grid, TC_ROWS, smem, s>>>(probs);
+    match_tc_kernel<<<grid, TC_THREADS, smem, s>>>(probs);
 }
 
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
