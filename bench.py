@@ -45,6 +45,7 @@ def algorithmic_bytes(geom_levels, nfeat, temporal):
         "blur": 2 * 2 * sum(p),                            # read + write every level
         "describe": 2 * nfeat * (961 + 1369 + 32 + 28),
         "match_stereo": b_match,
+        "ingest": 2 * p[0] * (1 + 6 + 1),                  # remap: 4-tap gather ~ one read of the frame + 6 map bytes + 1 write per pixel
     }
     return 2 * b_img + b_match * (3 if temporal else 1), per_kernel
 
@@ -121,6 +122,8 @@ def main():
     ap.add_argument("--no-temporal", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--rectify", action="store_true",
+                    help="next row f1: inputs are raw camera frames, cv::remap runs on the device in front of the pyramid")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")
     args = ap.parse_args()
@@ -188,6 +191,12 @@ def main():
     hds = [fe.Handle(*cfg, w, h, max_images=2 * Bs, device=local) for _ in range(nstr)]
     streams = [torch.cuda.ExternalStream(hh.stream, device=torch.device("cuda", local)) for hh in hds]
     hd = hds[0]
+    rect_maps = None
+    if args.rectify:   # + 2 x cv::remap per pair (src/feature-tracker.cpp:75-76), fused into the ingest
+        rect_maps = [synth.rectification_maps(w, h, e) for e in (0, 1)]
+        for x in hds:
+            x.set_rectification(rect_maps[0][0], rect_maps[0][1], rect_maps[1][0], rect_maps[1][1])
+        config["rectify"] = "cv::remap INTER_LINEAR, CV_16SC2 maps, fused into the level-0 staging pass"
     img_bytes = w * h
 
     def step_device(k, only=None):
@@ -237,6 +246,9 @@ def main():
     nh = max(args.e2e_threads, 1)
     Be = B                                            # pairs per C-ABI call (one value-leg step), per host thread
     handles = [fe.Handle(*cfg, w, h, max_images=2 * Be, device=local) for _ in range(nh)]
+    if rect_maps is not None:
+        for x in handles:
+            x.set_rectification(rect_maps[0][0], rect_maps[0][1], rect_maps[1][0], rect_maps[1][1])
     pin_l = fe.pinned_empty(ls.shape); pin_l[...] = ls
     pin_r = fe.pinned_empty(rs.shape); pin_r[...] = rs
     outs = [hh.alloc_stereo_out(Be, pinned=True) for hh in handles]

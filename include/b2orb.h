@@ -93,6 +93,20 @@ int b2orb_extract(b2orb_handle* h, const uint8_t* image, int width, int height, 
 int b2orb_extract_batch(b2orb_handle* h, const uint8_t* images, int count, int width, int height, int step,
                         size_t image_stride, b2orb_keypoint* kps, uint8_t* desc, int cap, int32_t* n);
 
+/* Rectification in front of the pyramid: cv::remap(gray, img, rmap[eye][0], rmap[eye][1], cv::INTER_LINEAR),
+ * src/feature-tracker.cpp:75-76, 416-417, with the fixed-point maps initUndistortRectifyMap(..., CV_16SC2, ...)
+ * produces (include/cfsd/camera-model.hpp:76-77): map1 = width*height (x, y) int16 pairs, map2 = width*height
+ * uint16 (fx | fy << 5, 1/32 px); BORDER_CONSTANT 0.  After this call b2orb_stereo_frontend and
+ * b2orb_stereo_frontend_device treat width x height images as UN-rectified camera frames and rectify them on the
+ * device while staging them (no extra pass over the image); all four maps NULL switches it off again.  Host
+ * pointers, copied. */
+int b2orb_set_rectification(b2orb_handle* h, int width, int height, const int16_t* map1_l, const uint16_t* map2_l,
+                            const int16_t* map1_r, const uint16_t* map2_r);
+
+/* One cv::remap call with the maps above (eye 0 = left, 1 = right): host image in, host image out. */
+int b2orb_remap(b2orb_handle* h, int eye, const uint8_t* image, int width, int height, int step, uint8_t* out,
+                int out_step);
+
 /* cv::BFMatcher(cv::NORM_HAMMING).match(query, train, matches): one result per query row in query
  * order; train_idx = nearest train row (lowest index on ties), dist = Hamming distance.
  * nt == 0 -> train_idx = -1, dist = INT32_MAX.  Host pointers, 32-byte descriptor rows, nt < 2^22. */

@@ -51,6 +51,7 @@ def lib():
         L.orc_get_raw.argtypes = [vp, C.c_int, vp, C.c_int]
         L.orc_resize.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]
         L.orc_blur.argtypes = [vp, C.c_int, C.c_int, vp, i32p]
+        L.orc_remap.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int]
         L.orc_fast.restype = C.c_int
         L.orc_fast.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
         L.orc_fast_atan2.restype = C.c_float
@@ -139,6 +140,16 @@ def resize(src, dw, dh):
     src = _img(src)
     dst = np.zeros((dh, dw), np.uint8)
     lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
+    return dst
+
+
+def remap(src, map1, map2):
+    """cv::remap(src, map1 (H x W x 2 int16), map2 (H x W uint16), INTER_LINEAR), src/feature-tracker.cpp:75-76."""
+    src = _img(src)
+    map1 = np.ascontiguousarray(map1, np.int16); map2 = np.ascontiguousarray(map2, np.uint16)
+    dh, dw = map2.shape
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_remap(_p(src), src.shape[1], src.shape[0], src.shape[1], map1.ctypes.data, map2.ctypes.data, dw, dh, _p(dst), dw)
     return dst
 
 

@@ -92,6 +92,9 @@ struct B2MatchProblem {
 // ---- kernel launchers (each file documents the reference lines it restates) --------------------
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s);
+// cv::remap with fixed-point maps (map1: short2 per pixel, map2: u16 per pixel), source and output of size w x h
+void b2_launch_remap(const uint8_t* src, int step, size_t stride, const void* map1, const void* map2, uint8_t* dst,
+                     int dpitch, size_t dstride, int w, int h, int count, cudaStream_t s);
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);

@@ -93,6 +93,10 @@ struct b2orb_handle {
     cudaEvent_t ev_hist = nullptr, ev_done = nullptr;    // history slot written / kernels of the lane's last chunk done
     cudaEvent_t ev_in = nullptr, ev_out = nullptr;       // lane: chunk copied in / results copied out
     cudaStream_t s_in = nullptr, s_out = nullptr;        // root: copy-in and copy-out streams of the pipelined path
+    // rectification maps of b2orb_set_rectification (root handle; lanes read the root's): [eye] map1 = short2, map2 = u16
+    void* d_map1[2] = {nullptr, nullptr};
+    void* d_map2[2] = {nullptr, nullptr};
+    int rect_w = 0, rect_h = 0;                          // 0 = rectification off
     int pipe_chunk = 64, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
@@ -451,45 +455,58 @@ UploadPath upload_path(const b2orb_handle* h, int w, int hgt, int step, size_t i
     if (step == w && image_stride == (size_t)w * hgt) return UP_TIGHT;
     return UP_ROWS;
 }
+// Rectification (b2orb_set_rectification) turns the ingest step into cv::remap: raw images are staged as tight rows
+// in d_raw and remap_kernel writes the rectified image straight into the pitched staging area.  eye: -1 = images are
+// already rectified, 0 / 1 = left / right maps.
+bool rectifying(const b2orb_handle* h, int w, int hgt, int eye) {
+    return eye >= 0 && h->root->rect_w == w && h->root->rect_h == hgt;
+}
 // the host->device part, on stream `cs` (the handle's own stream, or the pipelined path's copy-in stream)
 int upload_copy(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
-                cudaStream_t cs) {
+                cudaStream_t cs, int eye = -1) {
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
-    switch (upload_path(h, w, hgt, step, image_stride, false)) {
-    case UP_PITCHED:
+    uint8_t* raw = h->d_raw + (size_t)slot0 * w * hgt;
+    const UploadPath path = upload_path(h, w, hgt, step, image_stride, false);
+    if (path == UP_TIGHT) {
+        B2_CUDA(h, cudaMemcpyAsync(raw, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, cs));
+    } else if (rectifying(h, w, hgt, eye)) {
+        for (int i = 0; i < count; ++i)
+            B2_CUDA(h, cudaMemcpy2DAsync(raw + (size_t)i * w * hgt, w, src + i * image_stride, step, w, hgt,
+                                         cudaMemcpyHostToDevice, cs));
+    } else if (path == UP_PITCHED) {
         B2_CUDA(h, cudaMemcpyAsync(dst, src, (size_t)count * step * hgt, cudaMemcpyHostToDevice, cs));
-        break;
-    case UP_TIGHT:
-        B2_CUDA(h, cudaMemcpyAsync(h->d_raw + (size_t)slot0 * w * hgt, src, (size_t)count * w * hgt, cudaMemcpyHostToDevice, cs));
-        break;
-    default:
+    } else {
         for (int i = 0; i < count; ++i)
             B2_CUDA(h, cudaMemcpy2DAsync(dst + (size_t)i * h->stage_img_bytes, h->stage_pitch, src + i * image_stride, step, w,
                                          hgt, cudaMemcpyHostToDevice, cs));
     }
     return B2ORB_OK;
 }
-// the re-pitching kernel (device sources and tight host rows), on the handle's stream
+// the kernel part of the ingest (re-pitching, or rectification), on the handle's stream
 int upload_repack(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
-                  bool on_device) {
+                  bool on_device, int eye = -1) {
     const UploadPath path = upload_path(h, w, hgt, step, image_stride, on_device);
-    if (path != UP_DEVICE && path != UP_TIGHT) return B2ORB_OK;
+    const bool rect = rectifying(h, w, hgt, eye);
+    if (!rect && path != UP_DEVICE && path != UP_TIGHT) return B2ORB_OK;
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
+    const uint8_t* from = path == UP_DEVICE ? src : h->d_raw + (size_t)slot0 * w * hgt;
+    const int fstep = path == UP_DEVICE ? step : w;
+    const size_t fstride = path == UP_DEVICE ? image_stride : (size_t)w * hgt;
     prof_mark(h, B2ORB_K_INGEST);
-    if (path == UP_DEVICE)
-        b2_launch_repack(src, step, image_stride, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
+    if (rect)
+        b2_launch_remap(from, fstep, fstride, h->root->d_map1[eye], h->root->d_map2[eye], dst, h->stage_pitch,
+                        h->stage_img_bytes, w, hgt, count, h->stream);
     else
-        b2_launch_repack(h->d_raw + (size_t)slot0 * w * hgt, w, (size_t)w * hgt, dst, h->stage_pitch, h->stage_img_bytes, w,
-                         hgt, count, h->stream);
+        b2_launch_repack(from, fstep, fstride, dst, h->stage_pitch, h->stage_img_bytes, w, hgt, count, h->stream);
     ++h->launches;
     prof_mark(h, -1);
     return B2ORB_OK;
 }
 int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
-           bool on_device = false) {
+           bool on_device = false, int eye = -1) {
     if (!on_device)
-        if (int rc = upload_copy(h, src, count, w, hgt, step, image_stride, slot0, h->stream)) return rc;
-    return upload_repack(h, src, count, w, hgt, step, image_stride, slot0, on_device);
+        if (int rc = upload_copy(h, src, count, w, hgt, step, image_stride, slot0, h->stream, eye)) return rc;
+    return upload_repack(h, src, count, w, hgt, step, image_stride, slot0, on_device, eye);
 }
 
 int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
@@ -592,6 +609,10 @@ void b2orb_destroy(b2orb_handle* h) {
     h->lanes.clear();
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_workspace(h);
+    for (int e = 0; e < 2; ++e) {
+        if (h->d_map1[e]) cudaFree(h->d_map1[e]);
+        if (h->d_map2[e]) cudaFree(h->d_map2[e]);
+    }
     if (h->ev_hist) cudaEventDestroy(h->ev_hist);
     if (h->ev_done) cudaEventDestroy(h->ev_done);
     if (h->ev_in) cudaEventDestroy(h->ev_in);
@@ -711,11 +732,12 @@ int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, con
     cudaEventRecord(h->ev0, h->stream);
     B2Images im;
     const auto aligned = [](const void* p, size_t a, size_t b) { return ((uintptr_t)p | a | b) % 16 == 0; };
-    if (aligned(d_images_l, (size_t)step, image_stride) && aligned(d_images_r, (size_t)step, image_stride)) {
+    if (!rectifying(h, width, height, 0) && aligned(d_images_l, (size_t)step, image_stride) &&
+        aligned(d_images_r, (size_t)step, image_stride)) {
         im = make_images(h, d_images_l, d_images_r, npairs, image_stride, step);   // read in place
     } else {   // kernels need 16-byte aligned rows: repack into the staging area (device-to-device)
-        if ((rc = upload(h, d_images_l, npairs, width, height, step, image_stride, 0, true))) return rc;
-        if ((rc = upload(h, d_images_r, npairs, width, height, step, image_stride, npairs, true))) return rc;
+        if ((rc = upload(h, d_images_l, npairs, width, height, step, image_stride, 0, true, 0))) return rc;
+        if ((rc = upload(h, d_images_r, npairs, width, height, step, image_stride, npairs, true, 1))) return rc;
         im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs, h->stage_img_bytes,
                          h->stage_pitch);
     }
@@ -814,8 +836,8 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
         // ---- copy-in ----
         if (k >= nl) cudaStreamWaitEvent(h->s_in, l->ev_done, 0);             // the lane's staging area is free again
         if (trace) cudaEventRecord(tr.back().e[0], h->s_in);
-        if ((rc = upload_copy(l, images_l + (size_t)p0 * image_stride, n, width, height, step, image_stride, 0, h->s_in))) break;
-        if ((rc = upload_copy(l, images_r + (size_t)p0 * image_stride, n, width, height, step, image_stride, n, h->s_in))) break;
+        if ((rc = upload_copy(l, images_l + (size_t)p0 * image_stride, n, width, height, step, image_stride, 0, h->s_in, 0))) break;
+        if ((rc = upload_copy(l, images_r + (size_t)p0 * image_stride, n, width, height, step, image_stride, n, h->s_in, 1))) break;
         cudaEventRecord(l->ev_in, h->s_in);
         if (trace) cudaEventRecord(tr.back().e[1], h->s_in);
         // ---- kernels ----
@@ -823,8 +845,8 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
         if (k >= nl) cudaStreamWaitEvent(l->stream, l->ev_out, 0);            // the lane's previous results are on the host
         else cudaStreamWaitEvent(l->stream, h->ev0, 0);
         if ((rc = bind_problems(l, n))) break;
-        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, 0, false))) break;
-        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, n, false))) break;
+        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, 0, false, 0))) break;
+        if ((rc = upload_repack(l, nullptr, n, width, height, step, image_stride, n, false, 1))) break;
         B2Images im = make_images(l, l->d_stage, l->d_stage + (size_t)n * l->stage_img_bytes, n, l->stage_img_bytes,
                                   l->stage_pitch);
         if ((rc = launch_stereo(l, im, n, temporal))) break;
@@ -873,8 +895,8 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     if (rc) return rc;
     if ((rc = bind_problems(h, npairs))) return rc;
     cudaEventRecord(h->ev0, h->stream);
-    if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0))) return rc;
-    if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs))) return rc;
+    if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0, false, 0))) return rc;
+    if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs, false, 1))) return rc;
     B2Images im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs,
                               h->stage_img_bytes, h->stage_pitch);
     if ((rc = launch_stereo(h, im, npairs, temporal))) return rc;
@@ -882,6 +904,57 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     rc = b2orb_stereo_download(h, npairs, out);
     cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
     return rc;
+}
+
+// ---- rectification (next row f1: cv::remap in front of the pyramid) --------------------------------
+int b2orb_set_rectification(b2orb_handle* h, int width, int height, const int16_t* map1_l, const uint16_t* map2_l,
+                            const int16_t* map1_r, const uint16_t* map2_r) {
+    if (!h || h->root != h) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    const bool off = !map1_l && !map2_l && !map1_r && !map2_r;
+    if (!off && (!map1_l || !map2_l || !map1_r || !map2_r || width < 1 || height < 1 || width > h->cfg.max_width ||
+                 height > h->cfg.max_height))
+        return fail(h, B2ORB_ERR_INVALID, "bad rectification maps");
+    // no launch may still be reading the old maps
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (b2orb_handle* l : h->lanes) B2_CUDA(h, cudaStreamSynchronize(l->stream));
+    for (int e = 0; e < 2; ++e) {
+        if (h->d_map1[e]) cudaFree(h->d_map1[e]);
+        if (h->d_map2[e]) cudaFree(h->d_map2[e]);
+        h->d_map1[e] = h->d_map2[e] = nullptr;
+    }
+    h->rect_w = h->rect_h = 0;
+    if (off) return B2ORB_OK;
+    const size_t n = (size_t)width * height;
+    const int16_t* m1[2] = {map1_l, map1_r};
+    const uint16_t* m2[2] = {map2_l, map2_r};
+    for (int e = 0; e < 2; ++e) {
+        B2_CUDA(h, cudaMalloc(&h->d_map1[e], n * 4));
+        B2_CUDA(h, cudaMalloc(&h->d_map2[e], n * 2));
+        B2_CUDA(h, cudaMemcpy(h->d_map1[e], m1[e], n * 4, cudaMemcpyHostToDevice));
+        B2_CUDA(h, cudaMemcpy(h->d_map2[e], m2[e], n * 2, cudaMemcpyHostToDevice));
+    }
+    h->rect_w = width;
+    h->rect_h = height;
+    return B2ORB_OK;
+}
+
+int b2orb_remap(b2orb_handle* h, int eye, const uint8_t* image, int width, int height, int step, uint8_t* out,
+                int out_step) {
+    if (!h || !image || !out || eye < 0 || eye > 1 || step < width || out_step < width)
+        return fail(h, B2ORB_ERR_INVALID, "bad remap arguments");
+    if (h->rect_w != width || h->rect_h != height || width < 1)
+        return fail(h, B2ORB_ERR_INVALID, "no rectification maps for this image size");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = configure(h, width, height);
+    if (rc) return rc;
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = upload(h, image, 1, width, height, step, (size_t)step * height, 0, false, eye))) return rc;
+    cudaEventRecord(h->ev1, h->stream);
+    B2_CUDA(h, cudaMemcpy2DAsync(out, out_step, h->d_stage, h->stage_pitch, width, height, cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return B2ORB_OK;
 }
 
 // ---- generic matcher entry points (host descriptor sets) ------------------------------------------

@@ -76,6 +76,10 @@ def lib():
         L.b2orb_extract_batch.argtypes = [vp, vp, i32, i32, i32, i32, sz, vp, vp, i32, vp]
         L.b2orb_match.restype = i32
         L.b2orb_match.argtypes = [vp, vp, i32, vp, i32, vp, vp]
+        L.b2orb_set_rectification.restype = i32
+        L.b2orb_set_rectification.argtypes = [vp, i32, i32, vp, vp, vp, vp]
+        L.b2orb_remap.restype = i32
+        L.b2orb_remap.argtypes = [vp, i32, vp, i32, i32, i32, vp, i32]
         L.b2orb_stereo_frontend.restype = i32
         L.b2orb_stereo_frontend.argtypes = [vp, vp, vp, i32, i32, i32, i32, sz, i32, C.POINTER(B2StereoOut)]
         L.b2orb_stereo_frontend_device.restype = i32
@@ -277,6 +281,29 @@ class Handle:
         self.check(self.L.b2orb_stereo_download(self.h, npairs, C.byref(out[1])))
         return out[0]
 
+    def set_rectification(self, map1_l=None, map2_l=None, map1_r=None, map2_r=None):
+        """Maps of cv::initUndistortRectifyMap(..., CV_16SC2) per eye (include/cfsd/camera-model.hpp:76-77): map1 H x W x 2
+        int16, map2 H x W uint16.  Afterwards stereo_frontend rectifies raw camera frames on the device
+        (cv::remap, src/feature-tracker.cpp:75-76).  No arguments: off."""
+        if map1_l is None:
+            self.check(self.L.b2orb_set_rectification(self.h, 0, 0, None, None, None, None))
+            self._maps = None
+            return
+        maps = [np.ascontiguousarray(map1_l, np.int16), np.ascontiguousarray(map2_l, np.uint16),
+                np.ascontiguousarray(map1_r, np.int16), np.ascontiguousarray(map2_r, np.uint16)]
+        hgt, w = maps[1].shape
+        assert maps[0].shape == (hgt, w, 2) and maps[2].shape == (hgt, w, 2) and maps[3].shape == (hgt, w)
+        self.check(self.L.b2orb_set_rectification(self.h, w, hgt, *[m.ctypes.data for m in maps]))
+        self._maps = maps
+
+    def remap(self, image, eye):
+        """cv::remap of one image with the maps of set_rectification (eye 0 = left, 1 = right)."""
+        image = np.ascontiguousarray(image, np.uint8)
+        hgt, w = image.shape
+        out = np.zeros((hgt, w), np.uint8)
+        self.check(self.L.b2orb_remap(self.h, eye, _p(image), w, hgt, w, _p(out), w))
+        return out
+
     def sync(self):
         self.check(self.L.b2orb_sync(self.h))
 
@@ -359,6 +386,14 @@ class FeatureTracker:
 
     def extractORB(self, flag, img):
         return self.h.extract(img)
+
+    def setRectification(self, rmap):
+        """rmap[eye] = (map1, map2) as CameraModel::_rmap (include/cfsd/camera-model.hpp:76-77, 128)."""
+        self.h.set_rectification(rmap[0][0], rmap[0][1], rmap[1][0], rmap[1][1])
+
+    def processImage(self, grayLeft, grayRight):
+        """remap both eyes + internalMatch in one device pass (src/feature-tracker.cpp:69-76 then :140-229)."""
+        return self.internalMatch(grayLeft, grayRight)
 
     def internalMatch(self, imgLeft, imgRight):
         o = self.h.stereo_frontend(imgLeft, imgRight)

@@ -70,3 +70,24 @@ def sequence(shape, nframes, seed=0, passes=3):
     for t in range(nframes):
         ls[t], rs[t] = stereo_pair(cv, w, h, t, seed)
     return ls, rs
+
+
+def rectification_maps(w, h, eye):
+    """Deterministic fixed-point rectification maps in the format cv::initUndistortRectifyMap(..., CV_16SC2, ...) produces
+    (include/cfsd/camera-model.hpp:76-77): map1 (h, w, 2) int16 = integer source (x, y), map2 (h, w) uint16 =
+    fx | fy << 5 in 1/32 px.  A radial distortion plus a small per-eye rotation and shift; pure float64 + rint, so the
+    same bits everywhere without OpenCV.  Corner pixels sample outside the image (BORDER_CONSTANT taps)."""
+    ys, xs = np.mgrid[0:h, 0:w].astype(np.float64)
+    cx, cy, f = 0.5 * w + 3.25, 0.5 * h - 2.5, 0.55 * w
+    th = (0.004, -0.003)[eye]
+    xn, yn = (xs - cx) / f, (ys - cy) / f
+    xr, yr = xn * np.cos(th) - yn * np.sin(th), xn * np.sin(th) + yn * np.cos(th)
+    r2 = xr * xr + yr * yr
+    d = 1.0 + (-0.17, -0.16)[eye] * r2 + 0.025 * r2 * r2
+    X = cx + f * xr * d * 1.06 + (1.3, -0.7)[eye]
+    Y = cy + f * yr * d * 1.06 + (-0.4, 0.6)[eye]
+    ix, iy = np.rint(X * 32).astype(np.int64), np.rint(Y * 32).astype(np.int64)
+    map1 = np.stack([ix >> 5, iy >> 5], -1).astype(np.int16)
+    map2 = ((ix & 31) | ((iy & 31) << 5)).astype(np.uint16)
+    return map1, map2
+
