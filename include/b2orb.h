@@ -107,6 +107,16 @@ int b2orb_set_rectification(b2orb_handle* h, int width, int height, const int16_
 int b2orb_remap(b2orb_handle* h, int eye, const uint8_t* image, int width, int height, int step, uint8_t* out,
                 int out_step);
 
+/* cfsd live ingest, src/cfsd-state-estimation.cpp:117-127: `frame` is the camera's CV_8UC4 image with both eyes side by
+ * side (src_w x src_h, src_step bytes per row, multiple of 4); it is cv::resize'd (INTER_LINEAR) to 2*width x height,
+ * converted with cvtColor(BGR2GRAY) (4th channel ignored) and split into the left and right grey eye (width x height
+ * each) — one fused kernel.  b2orb_cfsd_ingest returns the two grey images (host in, host out; rectified as well when
+ * rectification maps for width x height are set, as VisualInertialSLAM::process -> processImage would);
+ * b2orb_stereo_frontend_packed continues on the device with the stereo front end of b2orb_stereo_frontend for
+ * `nframes` frames (frame i at frames + i*frame_stride, 2*nframes <= max_images). */
+int b2orb_cfsd_ingest(b2orb_handle* h, const uint8_t* frame, int src_w, int src_h, int src_step, int width, int height,
+                      uint8_t* gray_l, uint8_t* gray_r, int out_step);
+
 /* cv::BFMatcher(cv::NORM_HAMMING).match(query, train, matches): one result per query row in query
  * order; train_idx = nearest train row (lowest index on ties), dist = Hamming distance.
  * nt == 0 -> train_idx = -1, dist = INT32_MAX.  Host pointers, 32-byte descriptor rows, nt < 2^22. */
@@ -147,6 +157,10 @@ typedef struct b2orb_stereo_out {
  * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3). */
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
                           int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
+
+/* b2orb_cfsd_ingest followed by b2orb_stereo_frontend without leaving the device (see b2orb_cfsd_ingest). */
+int b2orb_stereo_frontend_packed(b2orb_handle* h, const uint8_t* frames, int nframes, int src_w, int src_h, int src_step,
+                                 size_t frame_stride, int width, int height, int temporal, const b2orb_stereo_out* out);
 
 /* Same work with inputs ALREADY RESIDENT in device memory and results LEFT on the device (read them with
  * b2orb_stereo_download).  Asynchronous on the handle's stream; b2orb_sync() waits. */

@@ -51,6 +51,7 @@ def lib():
         L.orc_get_raw.argtypes = [vp, C.c_int, vp, C.c_int]
         L.orc_resize.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]
         L.orc_blur.argtypes = [vp, C.c_int, C.c_int, vp, i32p]
+        L.orc_cfsd_ingest.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
         L.orc_remap.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, C.c_int]
         L.orc_fast.restype = C.c_int
         L.orc_fast.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
@@ -141,6 +142,16 @@ def resize(src, dw, dh):
     dst = np.zeros((dh, dw), np.uint8)
     lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
     return dst
+
+
+def cfsd_ingest(frame, dw, dh):
+    """src/cfsd-state-estimation.cpp:117-127: (H, W, 4) u8 side-by-side frame -> resize to dw x dh, BGR2GRAY, split.
+    Returns (grayL, grayR), each dh x dw/2."""
+    frame = np.ascontiguousarray(frame, np.uint8)
+    sh, sw, _ = frame.shape
+    gl = np.zeros((dh, dw // 2), np.uint8); gr = np.zeros((dh, dw // 2), np.uint8)
+    lib().orc_cfsd_ingest(frame.ctypes.data, sw, sh, sw * 4, dw, dh, _p(gl), _p(gr), dw // 2)
+    return gl, gr
 
 
 def remap(src, map1, map2):

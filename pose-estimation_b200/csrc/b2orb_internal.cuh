@@ -95,6 +95,10 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
 // cv::remap with fixed-point maps (map1: short2 per pixel, map2: u16 per pixel), source and output of size w x h
 void b2_launch_remap(const uint8_t* src, int step, size_t stride, const void* map1, const void* map2, uint8_t* dst,
                      int dpitch, size_t dstride, int w, int h, int count, cudaStream_t s);
+// side-by-side 4-channel frame -> resize -> grey -> left / right eye (src/cfsd-state-estimation.cpp:117-127)
+void b2_launch_ingest_bgra(const uint8_t* frames, int sstep, size_t sstride, int sw, int sh, const int* xofs, const short* xw,
+                           const int* yofs, const short* yw, uint8_t* dst_l, uint8_t* dst_r, int dpitch, size_t dstride,
+                           int half_w, int dh, int count, cudaStream_t s);
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);

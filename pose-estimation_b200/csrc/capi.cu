@@ -97,6 +97,12 @@ struct b2orb_handle {
     void* d_map1[2] = {nullptr, nullptr};
     void* d_map2[2] = {nullptr, nullptr};
     int rect_w = 0, rect_h = 0;                          // 0 = rectification off
+    // packed colour frames of the cfsd ingest (b2orb_cfsd_ingest / b2orb_stereo_frontend_packed)
+    uint8_t* d_packed = nullptr;
+    size_t packed_bytes = 0;
+    int ing_key[4] = {0, 0, 0, 0};                       // (src_w, src_h, dst_w, dst_h) the resize tables were built for
+    int *d_ing_xofs = nullptr, *d_ing_yofs = nullptr;
+    short *d_ing_xw = nullptr, *d_ing_yw = nullptr;
     int pipe_chunk = 64, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
@@ -613,6 +619,9 @@ void b2orb_destroy(b2orb_handle* h) {
         if (h->d_map1[e]) cudaFree(h->d_map1[e]);
         if (h->d_map2[e]) cudaFree(h->d_map2[e]);
     }
+    if (h->d_packed) cudaFree(h->d_packed);
+    for (void* p : {(void*)h->d_ing_xofs, (void*)h->d_ing_yofs, (void*)h->d_ing_xw, (void*)h->d_ing_yw})
+        if (p) cudaFree(p);
     if (h->ev_hist) cudaEventDestroy(h->ev_hist);
     if (h->ev_done) cudaEventDestroy(h->ev_done);
     if (h->ev_in) cudaEventDestroy(h->ev_in);
@@ -955,6 +964,112 @@ int b2orb_remap(b2orb_handle* h, int eye, const uint8_t* image, int width, int h
     B2_CUDA(h, cudaStreamSynchronize(h->stream));
     cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
     return B2ORB_OK;
+}
+
+// ---- cfsd live ingest (next row f2: colour frame -> resize -> grey -> split) -----------------------
+// Uploads `count` packed frames and leaves the grey eyes of frame i in staging slots i (left) and count + i (right);
+// with rectification on, the grey eyes go through remap_kernel on the way (process() -> processImage()).
+static int ingest_packed(b2orb_handle* h, const uint8_t* frames, int count, int src_w, int src_h, int src_step,
+                         size_t frame_stride, int width, int height) {
+    const int key[4] = {src_w, src_h, 2 * width, height};
+    if (std::memcmp(key, h->ing_key, sizeof key) != 0) {   // cv::resize tables for this geometry
+        std::vector<int> xo, yo;
+        std::vector<short> xw, yw;
+        resize_axis_table(src_w, 2 * width, xo, xw);
+        resize_axis_table(src_h, height, yo, yw);
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+        for (void* p : {(void*)h->d_ing_xofs, (void*)h->d_ing_yofs, (void*)h->d_ing_xw, (void*)h->d_ing_yw})
+            if (p) cudaFree(p);
+        B2_CUDA(h, cudaMalloc(&h->d_ing_xofs, xo.size() * 4));
+        B2_CUDA(h, cudaMalloc(&h->d_ing_yofs, yo.size() * 4));
+        B2_CUDA(h, cudaMalloc(&h->d_ing_xw, xw.size() * 2));
+        B2_CUDA(h, cudaMalloc(&h->d_ing_yw, yw.size() * 2));
+        B2_CUDA(h, cudaMemcpy(h->d_ing_xofs, xo.data(), xo.size() * 4, cudaMemcpyHostToDevice));
+        B2_CUDA(h, cudaMemcpy(h->d_ing_yofs, yo.data(), yo.size() * 4, cudaMemcpyHostToDevice));
+        B2_CUDA(h, cudaMemcpy(h->d_ing_xw, xw.data(), xw.size() * 2, cudaMemcpyHostToDevice));
+        B2_CUDA(h, cudaMemcpy(h->d_ing_yw, yw.data(), yw.size() * 2, cudaMemcpyHostToDevice));
+        std::memcpy(h->ing_key, key, sizeof key);
+    }
+    const size_t fbytes = (size_t)src_step * src_h;
+    if (h->packed_bytes < fbytes * count) {
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (h->d_packed) cudaFree(h->d_packed);
+        h->d_packed = nullptr;
+        h->packed_bytes = 0;
+        B2_CUDA(h, cudaMalloc(&h->d_packed, fbytes * count));
+        h->packed_bytes = fbytes * count;
+    }
+    if (frame_stride == fbytes) {
+        B2_CUDA(h, cudaMemcpyAsync(h->d_packed, frames, fbytes * count, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int i = 0; i < count; ++i)
+            B2_CUDA(h, cudaMemcpyAsync(h->d_packed + i * fbytes, frames + i * frame_stride, fbytes, cudaMemcpyHostToDevice, h->stream));
+    }
+    const bool rect = rectifying(h, width, height, 0);
+    // with rectification the grey eyes are an intermediate: park them in the (not yet used) blur slab, pitched
+    uint8_t* gl = rect ? h->d_blur : h->d_stage;
+    const size_t gstride = rect ? (size_t)h->geom.slab : h->stage_img_bytes;
+    uint8_t* gr = gl + (size_t)count * gstride;
+    prof_mark(h, B2ORB_K_INGEST);
+    b2_launch_ingest_bgra(h->d_packed, src_step, fbytes, src_w, src_h, h->d_ing_xofs, h->d_ing_xw, h->d_ing_yofs, h->d_ing_yw,
+                          gl, gr, h->stage_pitch, gstride, width, height, count, h->stream);
+    ++h->launches;
+    if (rect) {
+        for (int e = 0; e < 2; ++e) {
+            b2_launch_remap(e ? gr : gl, h->stage_pitch, gstride, h->root->d_map1[e], h->root->d_map2[e],
+                            h->d_stage + (size_t)e * count * h->stage_img_bytes, h->stage_pitch, h->stage_img_bytes, width, height,
+                            count, h->stream);
+            ++h->launches;
+        }
+    }
+    prof_mark(h, -1);
+    return B2ORB_OK;
+}
+
+static int check_packed_args(b2orb_handle* h, const void* frames, int count, int src_w, int src_h, int src_step, int width,
+                             int height) {
+    if (!h || !frames || count < 1 || src_w < 2 || src_h < 1 || src_step < 4 * src_w || (src_step & 3) || width < 1 || height < 1)
+        return fail(h, B2ORB_ERR_INVALID, "bad packed-frame arguments");
+    if (2 * count > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*frames exceeds max_images");
+    if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    return B2ORB_OK;
+}
+
+int b2orb_cfsd_ingest(b2orb_handle* h, const uint8_t* frame, int src_w, int src_h, int src_step, int width, int height,
+                      uint8_t* gray_l, uint8_t* gray_r, int out_step) {
+    int rc = check_packed_args(h, frame, 1, src_w, src_h, src_step, width, height);
+    if (rc) return rc;
+    if (!gray_l || !gray_r || out_step < width) return fail(h, B2ORB_ERR_INVALID, "bad packed-frame arguments");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    if ((rc = configure(h, width, height))) return rc;
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = ingest_packed(h, frame, 1, src_w, src_h, src_step, (size_t)src_step * src_h, width, height))) return rc;
+    cudaEventRecord(h->ev1, h->stream);
+    B2_CUDA(h, cudaMemcpy2DAsync(gray_l, out_step, h->d_stage, h->stage_pitch, width, height, cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaMemcpy2DAsync(gray_r, out_step, h->d_stage + h->stage_img_bytes, h->stage_pitch, width, height,
+                                 cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return B2ORB_OK;
+}
+
+int b2orb_stereo_frontend_packed(b2orb_handle* h, const uint8_t* frames, int nframes, int src_w, int src_h, int src_step,
+                                 size_t frame_stride, int width, int height, int temporal, const b2orb_stereo_out* out) {
+    int rc = check_packed_args(h, frames, nframes, src_w, src_h, src_step, width, height);
+    if (rc) return rc;
+    if (!out) return fail(h, B2ORB_ERR_INVALID, "bad packed-frame arguments");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    if ((rc = configure(h, width, height))) return rc;
+    if ((rc = bind_problems(h, nframes))) return rc;
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = ingest_packed(h, frames, nframes, src_w, src_h, src_step, frame_stride, width, height))) return rc;
+    B2Images im = make_images(h, h->d_stage, h->d_stage + (size_t)nframes * h->stage_img_bytes, nframes,
+                              h->stage_img_bytes, h->stage_pitch);
+    if ((rc = launch_stereo(h, im, nframes, temporal))) return rc;
+    cudaEventRecord(h->ev1, h->stream);
+    rc = b2orb_stereo_download(h, nframes, out);
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return rc;
 }
 
 // ---- generic matcher entry points (host descriptor sets) ------------------------------------------

@@ -196,7 +196,61 @@ remap_kernel(const uint8_t* __restrict__ src, int step, size_t stride, const sho
     *reinterpret_cast<uint32_t*>(dst + blockIdx.y * dstride + (size_t)y * dpitch + xw) = v;
 }
 
+// cfsd live ingest (next row f2), src/cfsd-state-estimation.cpp:117-127: CV_8UC4 frame with both eyes side by side ->
+// cv::resize(INTER_LINEAR) to 2*half_w x dh -> cvtColor(BGR2GRAY) -> left / right halves, fused: one thread per output
+// word of one eye; four 32-bit pixel loads per output pixel, the Q11 resize arithmetic of resize_kernel per channel
+// (H = S0*wx0 + S1*wx1;  v = ((wy0*(H0>>4))>>16) + ((wy1*(H1>>4))>>16) + 2) >> 2), then OpenCV 4.x's 15-bit grey
+// weights (B*3735 + G*19235 + R*9798 + 16384) >> 15.  The 7.4 MB colour frame is read once; nothing but the two grey
+// eyes is written.
+__global__ void __launch_bounds__(256)
+ingest_bgra_kernel(const uint8_t* __restrict__ frames, int sstep, size_t sstride, int sw, int sh,
+                   const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
+                   const short* __restrict__ yw, uint8_t* __restrict__ dst_l, uint8_t* __restrict__ dst_r, int dpitch,
+                   size_t dstride, int half_w, int dh) {
+    const int words = dpitch >> 2;
+    int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= 2 * words * dh) return;
+    const int eye = i >= words * dh;
+    i -= eye * words * dh;
+    const int y = i / words, x4 = (i - y * words) * 4;
+    const uint8_t* fr = frames + blockIdx.y * sstride;
+    const int sy0 = yofs[y], sy1 = min(sy0 + 1, sh - 1);
+    const int wy0 = yw[2 * y], wy1 = yw[2 * y + 1];
+    const uint8_t* r0 = fr + (size_t)sy0 * sstep;
+    const uint8_t* r1 = fr + (size_t)sy1 * sstep;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x4 + k;
+        if (x >= half_w) break;
+        const int X = x + eye * half_w;
+        const int sx0 = xofs[X], sx1 = min(sx0 + 1, sw - 1);
+        const int wx0 = xw[2 * X], wx1 = xw[2 * X + 1];
+        const uint32_t p00 = *reinterpret_cast<const uint32_t*>(r0 + 4 * sx0), p01 = *reinterpret_cast<const uint32_t*>(r0 + 4 * sx1);
+        const uint32_t p10 = *reinterpret_cast<const uint32_t*>(r1 + 4 * sx0), p11 = *reinterpret_cast<const uint32_t*>(r1 + 4 * sx1);
+        int ch[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int h0 = (int)((p00 >> (8 * c)) & 255u) * wx0 + (int)((p01 >> (8 * c)) & 255u) * wx1;
+            const int h1 = (int)((p10 >> (8 * c)) & 255u) * wx0 + (int)((p11 >> (8 * c)) & 255u) * wx1;
+            const int v = (((wy0 * (h0 >> 4)) >> 16) + ((wy1 * (h1 >> 4)) >> 16) + 2) >> 2;
+            ch[c] = min(max(v, 0), 255);
+        }
+        out |= (uint32_t)((ch[0] * 3735 + ch[1] * 19235 + ch[2] * 9798 + 16384) >> 15) << (8 * k);
+    }
+    uint8_t* d = (eye ? dst_r : dst_l) + blockIdx.y * dstride + (size_t)y * dpitch + x4;
+    *reinterpret_cast<uint32_t*>(d) = out;
+}
+
 }  // namespace
+
+void b2_launch_ingest_bgra(const uint8_t* frames, int sstep, size_t sstride, int sw, int sh, const int* xofs, const short* xw,
+                           const int* yofs, const short* yw, uint8_t* dst_l, uint8_t* dst_r, int dpitch, size_t dstride,
+                           int half_w, int dh, int count, cudaStream_t s) {
+    dim3 grid((2 * (dpitch >> 2) * dh + 255) / 256, count);
+    ingest_bgra_kernel<<<grid, 256, 0, s>>>(frames, sstep, sstride, sw, sh, xofs, xw, yofs, yw, dst_l, dst_r, dpitch, dstride,
+                                            half_w, dh);
+}
 
 void b2_launch_remap(const uint8_t* src, int step, size_t stride, const void* map1, const void* map2, uint8_t* dst,
                      int dpitch, size_t dstride, int w, int h, int count, cudaStream_t s) {

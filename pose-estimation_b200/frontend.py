@@ -78,6 +78,10 @@ def lib():
         L.b2orb_match.argtypes = [vp, vp, i32, vp, i32, vp, vp]
         L.b2orb_set_rectification.restype = i32
         L.b2orb_set_rectification.argtypes = [vp, i32, i32, vp, vp, vp, vp]
+        L.b2orb_cfsd_ingest.restype = i32
+        L.b2orb_cfsd_ingest.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, i32]
+        L.b2orb_stereo_frontend_packed.restype = i32
+        L.b2orb_stereo_frontend_packed.argtypes = [vp, vp, i32, i32, i32, i32, sz, i32, i32, i32, C.POINTER(B2StereoOut)]
         L.b2orb_remap.restype = i32
         L.b2orb_remap.argtypes = [vp, i32, vp, i32, i32, i32, vp, i32]
         L.b2orb_stereo_frontend.restype = i32
@@ -303,6 +307,25 @@ class Handle:
         out = np.zeros((hgt, w), np.uint8)
         self.check(self.L.b2orb_remap(self.h, eye, _p(image), w, hgt, w, _p(out), w))
         return out
+
+    def cfsd_ingest(self, frame, width, height):
+        """src/cfsd-state-estimation.cpp:117-127: (H, W, 4) u8 side-by-side frame -> (grayL, grayR), height x width each."""
+        frame = np.ascontiguousarray(frame, np.uint8)
+        sh, sw, _ = frame.shape
+        gl = np.zeros((height, width), np.uint8); gr = np.zeros((height, width), np.uint8)
+        self.check(self.L.b2orb_cfsd_ingest(self.h, frame.ctypes.data, sw, sh, sw * 4, width, height, _p(gl), _p(gr), width))
+        return gl, gr
+
+    def stereo_frontend_packed(self, frames, width, height, temporal=False, out=None):
+        """frames: (N, H, W, 4) u8 side-by-side colour frames; the ingest and the stereo front end run on the device."""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        if frames.ndim == 3:
+            frames = frames[None]
+        n, sh, sw, _ = frames.shape
+        arrays, s = out if out is not None else self.alloc_stereo_out(n)
+        self.check(self.L.b2orb_stereo_frontend_packed(self.h, frames.ctypes.data, n, sw, sh, sw * 4, sw * sh * 4, width,
+                                                       height, 1 if temporal else 0, C.byref(s)))
+        return arrays
 
     def sync(self):
         self.check(self.L.b2orb_sync(self.h))

@@ -91,3 +91,21 @@ def rectification_maps(w, h, eye):
     map2 = ((ix & 31) | ((iy & 31) << 5)).astype(np.uint16)
     return map1, map2
 
+
+def packed_frame(left, right, src_w, src_h, seed=0):
+    """A camera-style CV_8UC4 frame (both eyes side by side, src_w x src_h) whose grey content follows the given left /
+    right images: nearest-neighbour upsample (pure integer index maps) with per-channel integer offsets so that the
+    three colour channels differ, 4th channel = deterministic junk (cvtColor ignores it).  Library-independent."""
+    h, w = left.shape
+    both = np.concatenate([left, right], 1)
+    yi = (np.arange(src_h) * h) // src_h
+    xi = (np.arange(src_w) * (2 * w)) // src_w
+    g = both[yi][:, xi].astype(np.int32)
+    rng = np.random.Generator(np.random.PCG64(seed + 77))
+    fr = np.empty((src_h, src_w, 4), np.uint8)
+    fr[..., 0] = np.clip(g - 9, 0, 255)
+    fr[..., 1] = np.clip(g + 4, 0, 255)
+    fr[..., 2] = np.clip(g + (g >> 3) - 11, 0, 255)
+    fr[..., 3] = rng.integers(0, 256, (src_h, src_w), dtype=np.uint8)
+    return fr
+

@@ -81,6 +81,49 @@ def main():
             line["bit_exact_vs_oracle_pair0"] = bool(ok)
         print(json.dumps(line), flush=True)
         hd.close()
+    if "cfsd" in args.shapes.split(","):
+        cfsd_live(args, synth, fe)
+
+
+def cfsd_live(args, synth, fe):
+    """Config 3 as the reference runs it (src/cfsd-state-estimation.cpp:117-127 + process()): one 2560x720 CV_8UC4
+    frame per call -> fused resize + grey + split (f2) -> rectification (f1) -> stereo front end; host frame in, host
+    results out.  p50 / p95 latency against the 5 ms period of the 200 Hz stream, CPU port of the ingest beside it."""
+    w, h, nf, ini, mn = synth.SHAPES["cfsd"]
+    sw, sh = 2560, 720
+    ls, rs = synth.sequence("cfsd", 8, seed=11)
+    frames = fe.pinned_empty((8, sh, sw, 4))
+    for i in range(8):
+        frames[i] = synth.packed_frame(ls[i], rs[i], sw, sh, seed=i)
+    hd = fe.Handle(nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn, w, h, max_images=2)
+    maps = [synth.rectification_maps(w, h, e) for e in (0, 1)]
+    hd.set_rectification(maps[0][0], maps[0][1], maps[1][0], maps[1][1])
+    out1 = hd.alloc_stereo_out(1, pinned=True)
+    lat = []
+    for k in range(args.calls + 10):
+        i = k % 8
+        t0 = time.perf_counter()
+        hd.check(hd.L.b2orb_stereo_frontend_packed(hd.h, frames[i:].ctypes.data, 1, sw, sh, sw * 4, sw * sh * 4, w, h, 0, out1[1]))
+        lat.append((time.perf_counter() - t0) * 1e3)
+    lat = np.sort(np.array(lat[10:]))
+    line = {"shape": "cfsd_live", "frame": [sw, sh, 4], "eye": [w, h], "nfeatures": nf, "rectify": True,
+            "latency_ms": {"p50": round(float(lat[len(lat) // 2]), 4), "p95": round(float(lat[int(len(lat) * 0.95)]), 4),
+                           "max": round(float(lat[-1]), 4), "calls": int(len(lat)), "device_ms_last_call": round(hd.last_device_ms, 4)},
+            "h2d_bytes_per_frame": sw * sh * 4, "deadline_5ms_met": bool(lat[int(len(lat) * 0.95)] < 5.0),
+            "keypoints_left": int(out1[0]["n_l"][0])}
+    if not args.no_parity:
+        from oracle import oracle as orc
+        t0 = time.perf_counter()
+        gl, gr = orc.cfsd_ingest(frames[0], 2 * w, h)
+        rl, rr = orc.remap(gl, *maps[0]), orc.remap(gr, *maps[1])
+        line["cpu_port_ingest_rectify_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
+        ex = orc.OracleExtractor(nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn)
+        kl, dl = ex(rl)
+        hd.check(hd.L.b2orb_stereo_frontend_packed(hd.h, frames.ctypes.data, 1, sw, sh, sw * 4, sw * sh * 4, w, h, 0, out1[1]))
+        n = int(out1[0]["n_l"][0])
+        line["bit_exact_vs_oracle"] = bool(n == len(kl) and np.array_equal(out1[0]["desc_l"][0, :n], dl))
+    print(json.dumps(line), flush=True)
+    hd.close()
 
 
 if __name__ == "__main__":
