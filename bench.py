@@ -358,6 +358,14 @@ def main():
         v, n, dt = cpu_baseline(synth, orc, args.workload, cfg, temporal, workers, args.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": workers, "kind": "port",
                                 "sample": f"{n} pairs of the same workload in {dt:.1f} s, pairs sharded over {workers} host threads"}
+        # the reference's own structure (src/feature-tracker.cpp:153-156): pairs one after the other, left and right
+        # extraction on two threads — what one instance of the reference does on this host
+        fl, fr = synth.sequence(args.workload, 6, seed=1)
+        t0 = time.perf_counter()
+        orc.run_pairs(cfg, fl, fr, synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST, 1, 2, temporal)
+        fdt = time.perf_counter() - t0
+        line["cpu_baseline"]["faithful"] = {"value": 6 / fdt, "unit": UNIT, "cores": 2,
+                                            "sample": f"6 pairs sequentially, L/R extraction on 2 threads, {fdt:.2f} s"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
