@@ -124,6 +124,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--rectify", action="store_true",
                     help="next row f1: inputs are raw camera frames, cv::remap runs on the device in front of the pyramid")
+    ap.add_argument("--triangulate", action="store_true",
+                    help="next row f4: cv::triangulatePoints + depth gate of the kept matches in the same device pass")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")
     args = ap.parse_args()
@@ -197,6 +199,15 @@ def main():
         for x in hds:
             x.set_rectification(rect_maps[0][0], rect_maps[0][1], rect_maps[1][0], rect_maps[1][1])
         config["rectify"] = "cv::remap INTER_LINEAR, CV_16SC2 maps, fused into the level-0 staging pass"
+    proj = None
+    if args.triangulate:   # triangulatePoints of the kept matches (src/feature-tracker.cpp:365-379)
+        fx = 0.58 * w
+        P1 = [[fx, 0, 0.49 * w, 0], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]
+        P2 = [[fx, 0, 0.49 * w, 0.537 * fx], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]   # synthetic right eye lies towards +x
+        proj = (P1, P2, 20.0)
+        for x in hds:
+            x.set_projection(*proj)
+        config["triangulate"] = "cv::triangulatePoints (4x4 Jacobi SVD per kept match, fp64) + depth gates, fused behind the stereo filter"
     img_bytes = w * h
 
     def step_device(k, only=None):
@@ -249,11 +260,14 @@ def main():
     if rect_maps is not None:
         for x in handles:
             x.set_rectification(rect_maps[0][0], rect_maps[0][1], rect_maps[1][0], rect_maps[1][1])
+    if proj is not None:
+        for x in handles:
+            x.set_projection(*proj)
     pin_l = fe.pinned_empty(ls.shape); pin_l[...] = ls
     pin_r = fe.pinned_empty(rs.shape); pin_r[...] = rs
     outs = [hh.alloc_stereo_out(Be, pinned=True) for hh in handles]
     cap = handles[0].keypoint_capacity
-    d2h_per_pair = 2 * cap * (28 + 32) + 6 * cap * 4 + 4 * 4
+    d2h_per_pair = 2 * cap * (28 + 32) + 6 * cap * 4 + 4 * 4 + (cap * (32 + 24 + 1) if proj is not None else 0)
     e2e_steps = max(args.steps // 2, 4)
     counts = []
 

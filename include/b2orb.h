@@ -143,6 +143,11 @@ typedef struct b2orb_stereo_out {
     int32_t* circ_cur;        /* [npairs*cap] */
     int32_t* circ_hist;       /* [npairs*cap] */
     int32_t* n_circ;          /* [npairs] (0 for the first pair after b2orb_reset_history) */
+    /* triangulation of the kept matches, filled when b2orb_set_projection() is active (NULL = not copied back):
+     * pair p, kept match i (same order as match_l / match_r). */
+    double* points4d;         /* [npairs][4][cap]: pair p is a 4 x cap row-major matrix = cv::Mat(4, n, CV_64F, ptr, cap*8) */
+    double* point_cam;        /* [npairs*cap][3]: (X/W, Y/W, Z/W), the reference's point_wrt_cam */
+    uint8_t* depth_flags;     /* [npairs*cap]: bit 0 = !(depth > max_depth), bit 1 = !(depth < 0.1 || depth > max_depth) */
 } b2orb_stereo_out;
 
 /* FeatureTracker::internalMatch (useRANSAC=false, src/feature-tracker.cpp:140-164,208-218) for `npairs`
@@ -170,6 +175,20 @@ int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o
 int b2orb_sync(b2orb_handle* h);
 void b2orb_reset_history(b2orb_handle* h);
 
+/* cv::triangulatePoints(P1, P2, pixelsL, pixelsR, points4D) as the reference calls it (src/feature-tracker.cpp:367, :489):
+ * P1, P2 = 3x4 row-major double projection matrices (CameraModel::_P1/_P2), pix_l / pix_r = n cv::Point2d (x, y
+ * doubles), points4d = 4 x n row-major doubles (the CV_64F matrix the reference indexes as points4D.at<double>(r, i)).
+ * Same arithmetic as OpenCV (4x4 one-sided Jacobi SVD per point, last row of Vt), one thread per point.  n == 0 is a
+ * no-op.  Host pointers. */
+int b2orb_triangulate(b2orb_handle* h, const double* P1, const double* P2, const double* pix_l, const double* pix_r,
+                      int n, double* points4d);
+
+/* Fused form: after this call b2orb_stereo_frontend* also triangulates the kept stereo matches of every pair on the
+ * device (pixels = the float keypoint coordinates widened to double, as _curPixelsL/R are built at
+ * src/feature-tracker.cpp:214-215) and fills b2orb_stereo_out.points4d / point_cam / depth_flags with the quantities
+ * featurePoolUpdate (:371-378) and structFromMotion (:501-506) derive from points4D.  Both NULL switches it off. */
+int b2orb_set_projection(b2orb_handle* h, const double* P1, const double* P2, double max_depth);
+
 /* externalTrack matching parts as one call on host descriptor sets (src/feature-tracker.cpp:258-259,
  * 293-296, 303-321, useRANSAC=false): match(cur_l, hist_l) and match(cur_r, hist_r), each filtered by
  * dist < max(ratio*minDist, min_match_dist), then the circular test mapCurHist[q] == trainIdx.
@@ -195,7 +214,8 @@ void* b2orb_stream(const b2orb_handle* h);
  * accumulated milliseconds and launch counts per kernel id since b2orb_profile_enable(h, 1). */
 enum {
     B2ORB_K_RESIZE = 0, B2ORB_K_FAST, B2ORB_K_OCTREE, B2ORB_K_BLUR, B2ORB_K_DESCRIBE, B2ORB_K_MATCH_STEREO,
-    B2ORB_K_STEREO_FILTER, B2ORB_K_MATCH_TEMPORAL, B2ORB_K_CIRCULAR, B2ORB_K_FAST_CELLS, B2ORB_K_INGEST, B2ORB_NUM_KERNELS
+    B2ORB_K_STEREO_FILTER, B2ORB_K_MATCH_TEMPORAL, B2ORB_K_CIRCULAR, B2ORB_K_FAST_CELLS, B2ORB_K_INGEST, B2ORB_K_TRIANGULATE,
+    B2ORB_NUM_KERNELS
 };
 void b2orb_profile_enable(b2orb_handle* h, int on);
 int b2orb_profile_read(b2orb_handle* h, double* ms /*[B2ORB_NUM_KERNELS]*/, uint64_t* launches /*[B2ORB_NUM_KERNELS]*/);

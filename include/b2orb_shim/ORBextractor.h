@@ -143,6 +143,23 @@ private:
     std::vector<int32_t> idx_, dist_;
 };
 
+/* Replacement for `cv::triangulatePoints(_pCameraModel->_P1, _pCameraModel->_P2, pixelsL, pixelsR, points4D)`
+ * (src/feature-tracker.cpp:367, :489; next row f4): P1, P2 = 3x4 CV_64F, pixels = std::vector<cv::Point2d>, points4D
+ * becomes a 4 x N CV_64F matrix with the same values OpenCV's own routine produces (read by the reference as
+ * points4D.at<double>(r, i)). */
+inline void triangulatePoints(b2orb_handle* h, const cv::Mat& P1, const cv::Mat& P2, const std::vector<cv::Point2d>& pixelsL,
+                              const std::vector<cv::Point2d>& pixelsR, cv::Mat& points4D) {
+    CV_Assert(P1.type() == CV_64F && P2.type() == CV_64F && P1.rows == 3 && P1.cols == 4 && P2.rows == 3 && P2.cols == 4);
+    CV_Assert(pixelsL.size() == pixelsR.size());
+    static_assert(sizeof(cv::Point2d) == 2 * sizeof(double), "cv::Point2d is two packed doubles");
+    cv::Mat p1 = P1.isContinuous() ? P1 : P1.clone(), p2 = P2.isContinuous() ? P2 : P2.clone();
+    const int n = (int)pixelsL.size();
+    points4D.create(4, n, CV_64F);
+    if (b2orb_triangulate(h, (const double*)p1.data, (const double*)p2.data, n ? &pixelsL[0].x : nullptr,
+                          n ? &pixelsR[0].x : nullptr, n, (double*)points4D.data) != B2ORB_OK)
+        throw std::runtime_error(std::string("b2orb: ") + b2orb_last_error(h));
+}
+
 }  // namespace b2orb
 
 #endif /* ORBEXTRACTOR_H */

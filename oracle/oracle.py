@@ -70,6 +70,8 @@ def lib():
         L.orc_stereo_filter.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, C.c_float, C.c_float, C.c_float, vp, vp]
         L.orc_threshold_filter.restype = C.c_int
         L.orc_threshold_filter.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]
+        L.orc_triangulate.argtypes = [vp, vp, vp, vp, C.c_int, vp]
+        L.orc_depth_gate.argtypes = [vp, C.c_int, C.c_double, vp, vp]
         L.orc_stereo_pair.restype = C.c_int
         L.orc_stereo_pair.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_int, vp, vp, vp, vp, C.c_int, i32p, i32p, vp, vp, vp, vp]
@@ -219,6 +221,32 @@ def threshold_filter(train_idx, dist, nt, ratio, min_match_dist):
     ti = np.ascontiguousarray(train_idx, np.int32); di = np.ascontiguousarray(dist, np.int32)
     m = lib().orc_threshold_filter(_p(ti), _p(di), nq, nt, ratio, min_match_dist, _p(o_q), _p(o_t))
     return o_q[:m].copy(), o_t[:m].copy()
+
+
+def triangulate(P1, P2, pix_l, pix_r):
+    """cv::triangulatePoints(P1, P2, pixelsL, pixelsR, points4D) with vector<Point2d> inputs
+    (src/feature-tracker.cpp:367, :489): pix_* are (n, 2) float64; returns points4D as a (4, n) float64 array."""
+    P1 = np.ascontiguousarray(P1, np.float64).reshape(3, 4)
+    P2 = np.ascontiguousarray(P2, np.float64).reshape(3, 4)
+    pl = np.ascontiguousarray(pix_l, np.float64).reshape(-1, 2)
+    pr = np.ascontiguousarray(pix_r, np.float64).reshape(-1, 2)
+    assert len(pl) == len(pr)
+    out = np.zeros((4, len(pl)), np.float64)
+    if len(pl):
+        lib().orc_triangulate(_p(P1), _p(P2), _p(pl), _p(pr), len(pl), _p(out))
+    return out
+
+
+def depth_gate(points4d, max_depth):
+    """point_wrt_cam = (X/W, Y/W, Z/W) and the two depth gates (src/feature-tracker.cpp:371-378, :501-506):
+    flags bit 0 = !(depth > maxDepth), bit 1 = !(depth < 0.1 || depth > maxDepth)."""
+    p4 = np.ascontiguousarray(points4d, np.float64)
+    n = p4.shape[1]
+    pc = np.zeros((n, 3), np.float64)
+    fl = np.zeros(n, np.uint8)
+    if n:
+        lib().orc_depth_gate(_p(p4), n, float(max_depth), _p(pc), _p(fl))
+    return pc, fl
 
 
 def run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads, temporal=False):

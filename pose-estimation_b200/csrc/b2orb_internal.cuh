@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "../../include/b2orb.h"
 
 #define B2_MAX_LEVELS 12
 #define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
@@ -129,5 +130,15 @@ void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
                         const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
                         int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s);
+// cv::triangulatePoints operands (triangulate.cu): 3x4 row-major projection matrices, passed by value
+struct B2Projection {
+    double P1[12], P2[12];
+    double max_depth;
+};
+void b2_launch_triangulate(const B2Projection& pr, const double* pix_l, const double* pix_r, int n, double* points4d,
+                           cudaStream_t s);
+void b2_launch_triangulate_matches(const B2Projection& pr, const void* kps, const int* match_l, const int* match_r,
+                                   const int* n_match, int cap, int npairs, double* points4d, double* point_cam,
+                                   uint8_t* flags, cudaStream_t s);
 #define B2_OT_WORDS 24   // quadtree workspace words per node slot (octree.cu)
 int b2_octree_scratch_words(const B2Geom& g);

@@ -103,6 +103,13 @@ struct b2orb_handle {
     int ing_key[4] = {0, 0, 0, 0};                       // (src_w, src_h, dst_w, dst_h) the resize tables were built for
     int *d_ing_xofs = nullptr, *d_ing_yofs = nullptr;
     short *d_ing_xw = nullptr, *d_ing_yw = nullptr;
+    // next row f4: cv::triangulatePoints of the kept stereo matches (b2orb_set_projection; root handle, lanes read it)
+    B2Projection proj{};
+    bool proj_on = false;
+    double *d_pts4 = nullptr, *d_ptcam = nullptr;        // [npair_cap][4][cap] homogeneous points, [npair_cap][cap][3]
+    uint8_t* d_dflag = nullptr;                          // [npair_cap][cap] depth-gate flags
+    double *d_tri_in = nullptr, *d_tri_out = nullptr;    // b2orb_triangulate scratch (grow-only)
+    int tri_cap = 0;
     int pipe_chunk = 64, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
@@ -373,7 +380,9 @@ int configure(b2orb_handle* h, int w, int hgt) {
               dev_alloc(h, &h->d_tdi_r, (size_t)np * cap) && dev_alloc(h, &h->d_circ_cur, (size_t)np * cap) &&
               dev_alloc(h, &h->d_circ_hist, (size_t)np * cap) && dev_alloc(h, &h->d_ncirc, (size_t)np) &&
               dev_alloc(h, &h->d_nleft, (size_t)np) && dev_alloc(h, &h->d_nright, (size_t)np) &&
-              dev_alloc(h, &h->d_probs, (size_t)3 * np + 4) && dev_alloc(h, &h->d_gcnt, (size_t)8);
+              dev_alloc(h, &h->d_probs, (size_t)3 * np + 4) && dev_alloc(h, &h->d_gcnt, (size_t)8) &&
+              dev_alloc(h, &h->d_pts4, (size_t)np * cap * 4) && dev_alloc(h, &h->d_ptcam, (size_t)np * cap * 3) &&
+              dev_alloc(h, &h->d_dflag, (size_t)np * cap);
     if (!ok) return B2ORB_ERR_NOMEM;
     {   // raw candidate counters and per-cell flags share one allocation: one memset per batch clears both
         const size_t cnt_bytes = (size_t)nimg * nl * sizeof(int);
@@ -531,6 +540,12 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
                             h->d_nmatch + 1, h->d_cur_l + (size_t)g.kp_cap * 32, h->d_cur_r + (size_t)g.kp_cap * 32, np,
                             s);
     ++h->launches;
+    if (h->root->proj_on) {   // f4: triangulate the kept matches where they lie (src/feature-tracker.cpp:365-379)
+        prof_mark(h, B2ORB_K_TRIANGULATE);
+        b2_launch_triangulate_matches(h->root->proj, h->d_kps, h->d_match_l, h->d_match_r, h->d_nmatch + 1, g.kp_cap, np,
+                                      h->d_pts4, h->d_ptcam, h->d_dflag, s);
+        ++h->launches;
+    }
     prof_mark(h, -1);
     if (temporal) {
         const size_t row = (size_t)g.kp_cap * 32;
@@ -620,6 +635,8 @@ void b2orb_destroy(b2orb_handle* h) {
         if (h->d_map2[e]) cudaFree(h->d_map2[e]);
     }
     if (h->d_packed) cudaFree(h->d_packed);
+    if (h->d_tri_in) cudaFree(h->d_tri_in);
+    if (h->d_tri_out) cudaFree(h->d_tri_out);
     for (void* p : {(void*)h->d_ing_xofs, (void*)h->d_ing_yofs, (void*)h->d_ing_xw, (void*)h->d_ing_yw})
         if (p) cudaFree(p);
     if (h->ev_hist) cudaEventDestroy(h->ev_hist);
@@ -778,6 +795,11 @@ static int enqueue_download(b2orb_handle* h, int npairs, const b2orb_stereo_out*
     B2_CUDA(h, copy2d(o->match_r, h->d_match_r, 4, np));
     B2_CUDA(h, copy2d(o->circ_cur, h->d_circ_cur, 4, np));
     B2_CUDA(h, copy2d(o->circ_hist, h->d_circ_hist, 4, np));
+    if (h->root->proj_on) {
+        B2_CUDA(h, copy2d(o->points4d, h->d_pts4, 8, 4 * np));
+        B2_CUDA(h, copy2d(o->point_cam, h->d_ptcam, 24, np));
+        B2_CUDA(h, copy2d(o->depth_flags, h->d_dflag, 1, np));
+    }
     if (o->n_l) B2_CUDA(h, cudaMemcpyAsync(o->n_l, h->d_nkp, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_r) B2_CUDA(h, cudaMemcpyAsync(o->n_r, h->d_nkp + np, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_match) B2_CUDA(h, cudaMemcpyAsync(o->n_match, h->d_nmatch + 1, np * 4, cudaMemcpyDeviceToHost, s));
@@ -868,6 +890,7 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
         shift(o.kp_l, cap); shift(o.kp_r, cap); shift(o.desc_l, cap * 32); shift(o.desc_r, cap * 32);
         shift(o.train_idx, cap); shift(o.dist, cap); shift(o.match_l, cap); shift(o.match_r, cap);
         shift(o.circ_cur, cap); shift(o.circ_hist, cap);
+        shift(o.points4d, cap * 4); shift(o.point_cam, cap * 3); shift(o.depth_flags, cap);
         shift(o.n_l, 1); shift(o.n_r, 1); shift(o.n_match, 1); shift(o.n_circ, 1);
         if ((rc = enqueue_download(l, n, &o, h->s_out))) break;
         cudaEventRecord(l->ev_out, h->s_out);
@@ -913,6 +936,56 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     rc = b2orb_stereo_download(h, npairs, out);
     cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
     return rc;
+}
+
+// ---- triangulation (next row f4: cv::triangulatePoints + depth gates) -------------------------------
+int b2orb_set_projection(b2orb_handle* h, const double* P1, const double* P2, double max_depth) {
+    if (!h || h->root != h) return B2ORB_ERR_INVALID;
+    if (!P1 != !P2) return fail(h, B2ORB_ERR_INVALID, "b2orb_set_projection needs both matrices (or both NULL)");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    if (!P1) { h->proj_on = false; return B2ORB_OK; }
+    memcpy(h->proj.P1, P1, sizeof h->proj.P1);
+    memcpy(h->proj.P2, P2, sizeof h->proj.P2);
+    h->proj.max_depth = max_depth;
+    h->proj_on = true;   // passed by value with every launch: nothing in flight reads it
+    return B2ORB_OK;
+}
+
+int b2orb_triangulate(b2orb_handle* h, const double* P1, const double* P2, const double* pix_l, const double* pix_r,
+                      int n, double* points4d) {
+    if (!h || !P1 || !P2 || n < 0 || (n > 0 && (!pix_l || !pix_r || !points4d)))
+        return fail(h, B2ORB_ERR_INVALID, "bad triangulation arguments");
+    if (n == 0) return B2ORB_OK;   // cv::triangulatePoints on empty vectors yields a 4 x 0 matrix
+    B2_CUDA(h, cudaSetDevice(h->device));
+    if (n > h->tri_cap) {
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (h->d_tri_in) cudaFree(h->d_tri_in);
+        if (h->d_tri_out) cudaFree(h->d_tri_out);
+        h->d_tri_in = h->d_tri_out = nullptr;
+        h->tri_cap = 0;
+        const int want = std::max(n, 4096);
+        if (cudaMalloc(&h->d_tri_in, (size_t)want * 4 * sizeof(double)) != cudaSuccess ||
+            cudaMalloc(&h->d_tri_out, (size_t)want * 4 * sizeof(double)) != cudaSuccess)
+            return fail(h, B2ORB_ERR_NOMEM, "triangulation scratch");
+        h->tri_cap = want;
+    }
+    B2Projection pr;
+    memcpy(pr.P1, P1, sizeof pr.P1);
+    memcpy(pr.P2, P2, sizeof pr.P2);
+    pr.max_depth = 0;
+    cudaStream_t s = h->stream;
+    double* d_l = h->d_tri_in;
+    double* d_r = h->d_tri_in + (size_t)2 * n;
+    B2_CUDA(h, cudaMemcpyAsync(d_l, pix_l, (size_t)n * 16, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(d_r, pix_r, (size_t)n * 16, cudaMemcpyHostToDevice, s));
+    prof_mark(h, B2ORB_K_TRIANGULATE);
+    b2_launch_triangulate(pr, d_l, d_r, n, h->d_tri_out, s);
+    ++h->launches;
+    prof_mark(h, -1);
+    B2_CUDA(h, cudaGetLastError());
+    B2_CUDA(h, cudaMemcpyAsync(points4d, h->d_tri_out, (size_t)n * 32, cudaMemcpyDeviceToHost, s));
+    B2_CUDA(h, cudaStreamSynchronize(s));
+    return B2ORB_OK;
 }
 
 // ---- rectification (next row f1: cv::remap in front of the pyramid) --------------------------------

@@ -23,7 +23,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 
 OK, ERR_INVALID, ERR_CAPACITY, ERR_CUDA, ERR_NOMEM = 0, 1, 2, 3, 4
 KERNEL_NAMES = ("resize", "fast", "octree", "blur", "describe", "match_stereo", "stereo_filter", "match_temporal",
-                "circular", "fast_cells", "ingest")
+                "circular", "fast_cells", "ingest", "triangulate")
 
 
 class B2Config(C.Structure):
@@ -36,7 +36,7 @@ class B2Config(C.Structure):
 class B2StereoOut(C.Structure):
     _fields_ = [("cap", C.c_int32)] + [(n, C.c_void_p) for n in (
         "kp_l", "kp_r", "desc_l", "desc_r", "n_l", "n_r", "train_idx", "dist", "match_l", "match_r", "n_match",
-        "circ_cur", "circ_hist", "n_circ")]
+        "circ_cur", "circ_hist", "n_circ", "points4d", "point_cam", "depth_flags")]
 
 
 class B2Error(RuntimeError):
@@ -76,6 +76,10 @@ def lib():
         L.b2orb_extract_batch.argtypes = [vp, vp, i32, i32, i32, i32, sz, vp, vp, i32, vp]
         L.b2orb_match.restype = i32
         L.b2orb_match.argtypes = [vp, vp, i32, vp, i32, vp, vp]
+        L.b2orb_triangulate.restype = i32
+        L.b2orb_triangulate.argtypes = [vp, vp, vp, vp, vp, i32, vp]
+        L.b2orb_set_projection.restype = i32
+        L.b2orb_set_projection.argtypes = [vp, vp, vp, C.c_double]
         L.b2orb_set_rectification.restype = i32
         L.b2orb_set_rectification.argtypes = [vp, i32, i32, vp, vp, vp, vp]
         L.b2orb_cfsd_ingest.restype = i32
@@ -249,6 +253,28 @@ class Handle:
                                                C.byref(n), C.byref(nl), C.byref(nr)))
         return cc[:n.value].copy(), ch[:n.value].copy(), nl.value, nr.value
 
+    # ---- triangulation (next row f4)
+    def triangulate(self, P1, P2, pix_l, pix_r):
+        """cv::triangulatePoints(P1, P2, pixelsL, pixelsR, points4D) (src/feature-tracker.cpp:367, :489): pix_* are
+        (n, 2) float64 (vector<Point2d>); returns points4D as a (4, n) float64 array."""
+        P1 = np.ascontiguousarray(P1, np.float64).reshape(3, 4); P2 = np.ascontiguousarray(P2, np.float64).reshape(3, 4)
+        pl = np.ascontiguousarray(pix_l, np.float64).reshape(-1, 2); pr = np.ascontiguousarray(pix_r, np.float64).reshape(-1, 2)
+        assert len(pl) == len(pr)
+        out = np.zeros((4, len(pl)), np.float64)
+        self.check(self.L.b2orb_triangulate(self.h, _p(P1), _p(P2), _p(pl), _p(pr), len(pl), _p(out)))
+        return out
+
+    def set_projection(self, P1=None, P2=None, max_depth=20.0):
+        """CameraModel::_P1/_P2 + maxDepth: afterwards the stereo front end triangulates the kept matches on the device
+        (points4d / point_cam / depth_flags of the output).  No arguments: off."""
+        if P1 is None:
+            self.check(self.L.b2orb_set_projection(self.h, None, None, 0.0))
+            self._proj = False
+            return
+        P1 = np.ascontiguousarray(P1, np.float64).reshape(3, 4); P2 = np.ascontiguousarray(P2, np.float64).reshape(3, 4)
+        self.check(self.L.b2orb_set_projection(self.h, _p(P1), _p(P2), float(max_depth)))
+        self._proj = True
+
     # ---- fused stereo front-end
     def alloc_stereo_out(self, npairs, pinned=False, full=True):
         cap = self.keypoint_capacity
@@ -261,6 +287,9 @@ class Handle:
                       "desc_l": mk((npairs, cap, 32), np.uint8), "desc_r": mk((npairs, cap, 32), np.uint8),
                       "train_idx": mk((npairs, cap), np.int32), "dist": mk((npairs, cap), np.int32),
                       "circ_cur": mk((npairs, cap), np.int32), "circ_hist": mk((npairs, cap), np.int32)})
+        if getattr(self, "_proj", False):
+            a.update({"points4d": mk((npairs, 4, cap), np.float64), "point_cam": mk((npairs, cap, 3), np.float64),
+                      "depth_flags": mk((npairs, cap), np.uint8)})
         s = B2StereoOut()
         s.cap = cap
         for k, v in a.items():
@@ -427,7 +456,21 @@ class FeatureTracker:
         self._curPixelsR = np.stack([kr["x"][ir], kr["y"][ir]], 1).astype(np.float64)
         self._curDescriptorsL = o["desc_l"][0][il].copy()
         self._curDescriptorsR = o["desc_r"][0][ir].copy()
+        if "points4d" in o:
+            self._points4D = o["points4d"][0][:, :m].copy()
+            self._pointsCam = o["point_cam"][0][:m].copy()
+            self._depthFlags = o["depth_flags"][0][:m].copy()
         return o
+
+    def setProjection(self, P1, P2, maxDepth):
+        """CameraModel::_P1, _P2 and the maxDepth key: internalMatch then also triangulates on the device."""
+        self.h.set_projection(P1, P2, maxDepth)
+
+    def triangulate(self):
+        """cv::triangulatePoints(_P1, _P2, _curPixelsL, _curPixelsR, points4D) of featurePoolUpdate
+        (src/feature-tracker.cpp:365-379): returns (points4D 4 x M, point_wrt_cam M x 3, depth flags M) of the kept
+        matches of the last internalMatch — computed in that same device pass."""
+        return self._points4D, self._pointsCam, self._depthFlags
 
     def externalTrack(self):
         """Matching parts with useRANSAC=false; returns (curIdx, histIdx) of circular matches."""

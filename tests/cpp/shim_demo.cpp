@@ -1,6 +1,7 @@
 // Exercises the drop-in C++ shim exactly like the reference's call sites:
 //   FeatureTracker::extractORB     (src/feature-tracker.cpp:133-138)  (*_ORBextractorLeft)(img, cv::Mat(), kps, desc)
 //   FeatureTracker::internalMatch  (:161-164)                         matcher.match(descL, descR, matches)
+//   FeatureTracker::featurePoolUpdate (:365-371)                      triangulatePoints(P1, P2, pixelsL, pixelsR, points4D)
 // Input: raw u8 images (w h, then L and R pixel files); output: text dump compared by tests/test_cpp_shim.py.
 #include <cstdio>
 #include <cstdlib>
@@ -38,6 +39,20 @@ int main(int argc, char** argv) {
         for (int b = 0; b < 32; ++b) fprintf(f, " %d", dl.ptr((int)i)[b]);
         fprintf(f, " %d %d\n", matches[i].trainIdx, (int)matches[i].distance);
     }
+    // every match triangulated the way featurePoolUpdate does it (Point2f -> Point2d pixels, 3x4 CV_64F projections)
+    cv::Mat P1(3, 4, CV_64F), P2(3, 4, CV_64F);
+    const double fx = 435.2047, cx = 367.4517 * w / 752.0, cy = 252.2008 * h / 480.0, bfx = 47.9063;
+    P1.at<double>(0, 0) = P2.at<double>(0, 0) = fx; P1.at<double>(1, 1) = P2.at<double>(1, 1) = fx;
+    P1.at<double>(0, 2) = P2.at<double>(0, 2) = cx; P1.at<double>(1, 2) = P2.at<double>(1, 2) = cy;
+    P1.at<double>(2, 2) = P2.at<double>(2, 2) = 1.0; P2.at<double>(0, 3) = bfx;
+    std::vector<cv::Point2d> pixelsL, pixelsR;
+    for (auto& m : matches) { pixelsL.push_back(kl[m.queryIdx].pt); pixelsR.push_back(kr[m.trainIdx].pt); }
+    cv::Mat points4D;
+    b2orb::triangulatePoints(left.handle(), P1, P2, pixelsL, pixelsR, points4D);
+    fprintf(f, "P %.17g %.17g %.17g %.17g\n", fx, cx, cy, bfx);
+    for (int i = 0; i < points4D.cols; ++i)
+        fprintf(f, "T %.17g %.17g %.17g %.17g\n", points4D.at<double>(0, i), points4D.at<double>(1, i),
+                points4D.at<double>(2, i), points4D.at<double>(3, i));
     fclose(f);
     return 0;
 }

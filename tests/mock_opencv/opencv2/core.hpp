@@ -7,9 +7,16 @@
 #include <vector>
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_64F 6
 #define CV_Assert(x) assert(x)
 namespace cv {
 struct Point2f { float x, y; };
+struct Point2d {
+    double x, y;
+    Point2d() : x(0), y(0) {}
+    Point2d(double x_, double y_) : x(x_), y(y_) {}
+    Point2d(const Point2f& p) : x(p.x), y(p.y) {}   // the widening _curPixelsL.push_back(keypoint.pt) performs
+};
 struct KeyPoint {
     Point2f pt; float size, angle, response; int octave, class_id;
     KeyPoint() : pt{0, 0}, size(0), angle(-1), response(0), octave(0), class_id(-1) {}
@@ -24,20 +31,35 @@ class Mat {
 public:
     int rows = 0, cols = 0; size_t step = 0; unsigned char* data = nullptr;
     Mat() {}
-    Mat(int r, int c, int /*type*/) { create(r, c, CV_8U); }
-    Mat(int r, int c, int /*type*/, void* d, size_t s) : rows(r), cols(c), step(s), data((unsigned char*)d) {}
-    void create(int r, int c, int /*type*/) { rows = r; cols = c; step = c; buf_.assign((size_t)r * c, 0); data = buf_.data(); }
+    Mat(int r, int c, int type) { create(r, c, type); }
+    Mat(int r, int c, int type, void* d, size_t s) : rows(r), cols(c), step(s), data((unsigned char*)d), type_(type) {}
+    Mat(const Mat& o) { *this = o; }
+    Mat& operator=(const Mat& o) {   // deep copy keeps the mock simple (cv::Mat shares; nothing here depends on that)
+        if (this == &o) return *this;
+        rows = o.rows; cols = o.cols; type_ = o.type_;
+        if (o.buf_.empty() && o.data) { step = o.step; data = o.data; buf_.clear(); }
+        else { buf_ = o.buf_; step = o.step; data = buf_.empty() ? nullptr : buf_.data(); }
+        return *this;
+    }
+    void create(int r, int c, int type) {
+        rows = r; cols = c; type_ = type; step = (size_t)c * elemSize();
+        buf_.assign((size_t)r * step, 0); data = buf_.data();
+    }
     void release() { rows = cols = 0; buf_.clear(); data = nullptr; }
     bool empty() const { return rows == 0 || cols == 0; }
-    int type() const { return CV_8U; }
-    bool isContinuous() const { return step == (size_t)cols; }
-    Mat clone() const { Mat m; m.create(rows, cols, CV_8U); for (int i = 0; i < rows; ++i) std::memcpy(m.ptr(i), ptr(i), cols); return m; }
+    int type() const { return type_; }
+    size_t elemSize() const { return type_ == CV_64F ? 8 : 1; }
+    bool isContinuous() const { return step == (size_t)cols * elemSize(); }
+    Mat clone() const { Mat m; m.create(rows, cols, type_); for (int i = 0; i < rows; ++i) std::memcpy(m.ptr(i), ptr(i), cols * elemSize()); return m; }
+    template <typename T> T& at(int r, int c) { return ((T*)(data + (size_t)r * step))[c]; }
+    template <typename T> const T& at(int r, int c) const { return ((const T*)(data + (size_t)r * step))[c]; }
     unsigned char* ptr(int r) { return data + (size_t)r * step; }
     const unsigned char* ptr(int r) const { return data + (size_t)r * step; }
     Mat& getMat() { return *this; }
     const Mat& getMat() const { return *this; }
 private:
     std::vector<unsigned char> buf_;
+    int type_ = CV_8U;
 };
 typedef const Mat& InputArray;
 typedef Mat& OutputArray;

@@ -87,3 +87,10 @@ def test_shim_demo_matches_oracle(tmp_path, oracle, synth):
     assert np.array_equal(rows[:, 5].astype(np.int32), kl["octave"])
     assert np.array_equal(rows[:, 6:38].astype(np.uint8), dl)
     assert np.array_equal(rows[:, 38].astype(np.int32), ti) and np.array_equal(rows[:, 39].astype(np.int32), di)
+    # b2orb::triangulatePoints on every match == the oracle (itself pinned to cv2.triangulatePoints)
+    fx, cx, cy, bfx = [float(v) for v in next(ln for ln in lines if ln.startswith("P ")).split()[1:]]
+    P1 = np.array([[fx, 0, cx, 0], [0, fx, cy, 0], [0, 0, 1, 0.0]]); P2 = P1.copy(); P2[0, 3] = bfx
+    got = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("T ")]).T
+    pl = np.stack([kl["x"], kl["y"]], 1).astype(np.float64); pr = np.stack([kr["x"][ti], kr["y"][ti]], 1).astype(np.float64)
+    ref = oracle.triangulate(P1, P2, pl, pr)
+    assert got.shape == ref.shape and np.array_equal(got.view(np.uint64), ref.view(np.uint64))
