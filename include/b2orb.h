@@ -206,6 +206,10 @@ int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8
  * relative to the 16-px border (unordered).  Returns the count through *n. */
 int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* dst, int cap, int* n);
 
+/* Quadtree levels (since the library was loaded, on the handle's device) whose keypoints were so clustered that the
+ * count-pyramid path had to be redone with point passes (csrc/octree.cu).  Test / tuning aid. */
+uint64_t b2orb_debug_octree_fallbacks(b2orb_handle* h);
+
 /* The handle's CUDA stream (a cudaStream_t) so callers can record their own events on it. */
 void* b2orb_stream(const b2orb_handle* h);
 

@@ -28,7 +28,8 @@ struct B2Level {
     int sel_cap;              // quota + 4
     unsigned cand_off;        // first slot of this level in the per-image candidate array
     int cand_cap;
-    int node_cap;             // 4*quota + 8
+    int node_cap;             // max(quota + 3, 4*n_ini) + 1: the list never grows beyond that (octree.cu)
+    int ot_depth;             // depth D of the quadtree count pyramid (octree.cu); 0 = point passes only
     unsigned node_off;        // first node slot of this level in the per-image node workspace
     int n_ini;                // quadtree roots (src/ORBextractor.cc:543)
     float h_x;                // root width (src/ORBextractor.cc:545)
@@ -78,6 +79,7 @@ __device__ __forceinline__ const uint8_t* b2_level_ptr(const B2Geom& g, const B2
 struct B2Node {
     unsigned short x0, y0, x1, y1;  // UL.x, UL.y, BR.x, BR.y (relative to the 16-px border)
     unsigned cnt;                   // points inside
+    unsigned code;                  // depth << 28 | path (root index, then 2 bits per split): slot in the count pyramid
 };
 
 // One Hamming matching problem (BFMatcher.match call): rows are 32-byte descriptors.
@@ -140,5 +142,6 @@ void b2_launch_triangulate(const B2Projection& pr, const double* pix_l, const do
 void b2_launch_triangulate_matches(const B2Projection& pr, const void* kps, const int* match_l, const int* match_r,
                                    const int* n_match, int cap, int npairs, double* points4d, double* point_cam,
                                    uint8_t* flags, cudaStream_t s);
-#define B2_OT_WORDS 24   // quadtree workspace words per node slot (octree.cu)
+#define B2_OT_WORDS 26   // quadtree workspace words per node slot (octree.cu)
 int b2_octree_scratch_words(const B2Geom& g);
+unsigned long long b2_octree_fallbacks();   // per device, since the library was loaded

@@ -290,6 +290,12 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         L.node_off = node_off;
         node_off += L.node_cap;
         L.sel_cap = L.node_cap;
+        {   // count pyramid of the quadtree (octree.cu): deepest D <= 7 whose n_ini*(4^(D+1)-1)/3 counters fit into the
+            // 13*node_cap workspace words the point-pass path uses for its child counts
+            int D = 0;
+            while (D < 7 && (long long)L.n_ini * (((1LL << (2 * (D + 2))) - 1) / 3) <= 13LL * L.node_cap) ++D;
+            L.ot_depth = (long long)L.n_ini * (((1LL << (2 * (D + 1))) - 1) / 3) <= 13LL * L.node_cap ? D : 0;
+        }
         L.sel_base = sel;
         sel += L.sel_cap;
     }
@@ -1249,6 +1255,12 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
 }
 
 // ---- stream + per-kernel timing ------------------------------------------------------------------
+uint64_t b2orb_debug_octree_fallbacks(b2orb_handle* h) {
+    if (!h || cudaSetDevice(h->device) != cudaSuccess) return 0;
+    cudaStreamSynchronize(h->stream);
+    return b2_octree_fallbacks();
+}
+
 void* b2orb_stream(const b2orb_handle* h) { return h ? (void*)h->stream : nullptr; }
 
 void b2orb_profile_enable(b2orb_handle* h, int on) {

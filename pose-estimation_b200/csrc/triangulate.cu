@@ -20,18 +20,15 @@
 
 namespace {
 
+// lapack.cpp's file-local hypot: a > b ? a*sqrt(1+(b/a)^2) : b > 0 ? b*sqrt(1+(a/b)^2) : 0 on magnitudes — i.e. scale by
+// the larger one (equal magnitudes give ratio 1 on either path), written without branches.
 __device__ __forceinline__ double cv_lapack_hypot(double a, double b) {
     a = fabs(a);
     b = fabs(b);
-    if (a > b) {
-        b /= a;
-        return a * sqrt(1 + b * b);
-    }
-    if (b > 0) {
-        a /= b;
-        return b * sqrt(1 + a * a);
-    }
-    return 0;
+    const double hi = a > b ? a : b, lo = a > b ? b : a;
+    const double r = lo / hi;
+    const double v = hi * sqrt(1 + r * r);
+    return hi > 0 ? v : 0;
 }
 
 // One Jacobi rotation of columns (rows of At) i and j; returns whether it rotated.
@@ -44,15 +41,15 @@ __device__ __forceinline__ bool rotate_pair(double (&Ai)[4], double (&Aj)[4], do
     if (fabs(p) <= eps * sqrt(a * b)) return false;
     p *= 2;
     const double beta = a - b, gamma = cv_lapack_hypot(p, beta);
-    double c, s;
-    if (beta < 0) {
-        const double delta = (gamma - beta) * 0.5;
-        s = sqrt(delta / gamma);
-        c = p / (gamma * s * 2);
-    } else {
-        c = sqrt((gamma + beta) / (gamma * 2));
-        s = p / (gamma * c * 2);
-    }
+    // The reference's two branches are the same operations on swapped operands; one code path keeps the warp converged:
+    //   beta < 0:  delta = (gamma - beta)*0.5; s = sqrt(delta/gamma);       c = p/(gamma*s*2)
+    //   else:      c = sqrt((gamma + beta)/(gamma*2));                      s = p/(gamma*c*2)
+    const bool neg = beta < 0;
+    const double num = neg ? (gamma - beta) * 0.5 : (gamma + beta);
+    const double den = neg ? gamma : gamma * 2;
+    const double r = sqrt(num / den);
+    const double o = p / (gamma * r * 2);
+    const double c = neg ? o : r, s = neg ? r : o;
     a = b = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {

@@ -106,6 +106,8 @@ def lib():
         L.b2orb_debug_get_level.argtypes = [vp, i32, i32, i32, vp]
         L.b2orb_debug_get_candidates.restype = i32
         L.b2orb_debug_get_candidates.argtypes = [vp, i32, i32, vp, i32, C.POINTER(i32)]
+        L.b2orb_debug_octree_fallbacks.restype = C.c_uint64
+        L.b2orb_debug_octree_fallbacks.argtypes = [vp]
         L.b2orb_stream.restype = vp
         L.b2orb_stream.argtypes = [vp]
         L.b2orb_profile_enable.argtypes = [vp, i32]
@@ -369,6 +371,9 @@ class Handle:
         out = np.zeros((hh.value, w.value), np.uint8)
         self.check(self.L.b2orb_debug_get_level(self.h, slot, level, 1 if blurred else 0, _p(out)))
         return out
+
+    def debug_octree_fallbacks(self):
+        return int(self.L.b2orb_debug_octree_fallbacks(self.h))
 
     def debug_candidates(self, slot, level):
         n = C.c_int(0)

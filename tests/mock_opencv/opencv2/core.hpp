@@ -4,6 +4,7 @@
 #include <cassert>
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <vector>
 #define CV_8U 0
 #define CV_8UC1 0
@@ -33,19 +34,11 @@ public:
     Mat() {}
     Mat(int r, int c, int type) { create(r, c, type); }
     Mat(int r, int c, int type, void* d, size_t s) : rows(r), cols(c), step(s), data((unsigned char*)d), type_(type) {}
-    Mat(const Mat& o) { *this = o; }
-    Mat& operator=(const Mat& o) {   // deep copy keeps the mock simple (cv::Mat shares; nothing here depends on that)
-        if (this == &o) return *this;
-        rows = o.rows; cols = o.cols; type_ = o.type_;
-        if (o.buf_.empty() && o.data) { step = o.step; data = o.data; buf_.clear(); }
-        else { buf_ = o.buf_; step = o.step; data = buf_.empty() ? nullptr : buf_.data(); }
-        return *this;
-    }
     void create(int r, int c, int type) {
         rows = r; cols = c; type_ = type; step = (size_t)c * elemSize();
-        buf_.assign((size_t)r * step, 0); data = buf_.data();
+        buf_ = std::make_shared<std::vector<unsigned char>>((size_t)r * step, 0); data = buf_->data();
     }
-    void release() { rows = cols = 0; buf_.clear(); data = nullptr; }
+    void release() { rows = cols = 0; buf_.reset(); data = nullptr; }
     bool empty() const { return rows == 0 || cols == 0; }
     int type() const { return type_; }
     size_t elemSize() const { return type_ == CV_64F ? 8 : 1; }
@@ -58,7 +51,7 @@ public:
     Mat& getMat() { return *this; }
     const Mat& getMat() const { return *this; }
 private:
-    std::vector<unsigned char> buf_;
+    std::shared_ptr<std::vector<unsigned char>> buf_;   // copies share the pixels, like cv::Mat's reference counting
     int type_ = CV_8U;
 };
 typedef const Mat& InputArray;

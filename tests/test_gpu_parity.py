@@ -63,6 +63,30 @@ def test_extract_stages_match_oracle(case, fe, oracle, synth):
     hd.close()
 
 
+@pytest.mark.parametrize("mode", ["", "points"])
+def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth, monkeypatch):
+    """The quadtree has two sources of child counts (octree.cu): the count pyramid and the point passes (B2ORB_OCTREE=
+    points forces the latter).  Both must reproduce DistributeOctTree; the second image packs all texture into two
+    small patches, so nodes below the pyramid's depth have to be split and the kernel redoes those levels with point
+    passes on its own."""
+    monkeypatch.setenv("B2ORB_OCTREE", mode)
+    w, h, nf, ini, mn = 1241, 376, 2000, 12, 7
+    dense = synth.canvas(w, h, 17, 3)[:h, :w].copy()
+    clustered = np.full((h, w), 96, np.uint8)
+    for (y, x) in ((30, 60), (150, 420), (250, 800), (60, 1100)):
+        clustered[y:y + 90, x:x + 90] = dense[y:y + 90, x:x + 90]
+    ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    for tag, img in (("dense", dense), ("clustered", clustered)):
+        ref = ex(img)
+        assert len(ref[0]) > 500
+        before = hd.debug_octree_fallbacks()
+        assert_extract_equal(hd.extract(img), ref, f"{tag} [{mode or 'pyramid'}]")
+        redone = hd.debug_octree_fallbacks() - before
+        assert (redone > 0) == (tag == "clustered" and mode == ""), (tag, mode, redone)
+    hd.close()
+
+
 def test_extract_batch_and_resize_of_workspace(fe, oracle, synth):
     ls, rs = synth.sequence("cfsd", 3, seed=7)
     hd = fe.Handle(1000, 1.2, 8, 20, 7, 752, 480, max_images=6)
