@@ -87,6 +87,28 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth, monkeypatch):
     hd.close()
 
 
+@pytest.mark.parametrize("nfeat", [8000, 12000])
+def test_stress_4k_pair_matches_oracle(nfeat, fe, oracle, synth):
+    """BASELINE config 5: 3840x2160 stereo, 8000 features per eye, 8k x 8k brute-force Hamming per pair — the largest
+    shape the reference configs name.  12000 features push the level-0 quadtree workspace past the shared-memory budget
+    (global-memory workspace path of octree.cu)."""
+    w, h, _, ini, mn = synth.SHAPES["4k"]
+    ls, rs = synth.sequence("4k", 1, seed=2)
+    hd = fe.Handle(nfeat, 1.2, 8, ini, mn, w, h, max_images=2)
+    o = hd.stereo_frontend(ls, rs)
+    ex = oracle.OracleExtractor(nfeat, 1.2, 8, ini, mn)
+    kl, dl = ex(ls[0]); kr, dr = ex(rs[0])
+    nl, nr, m = int(o["n_l"][0]), int(o["n_r"][0]), int(o["n_match"][0])
+    assert nl >= nfeat and nr >= nfeat
+    assert_extract_equal((o["kp_l"][0, :nl], o["desc_l"][0, :nl]), (kl, dl), "4k left")
+    assert_extract_equal((o["kp_r"][0, :nr], o["desc_r"][0, :nr]), (kr, dr), "4k right")
+    ti, di = oracle.bf_match(dl, dr)
+    assert np.array_equal(o["train_idx"][0, :nl], ti) and np.array_equal(o["dist"][0, :nl], di)
+    ml, mr = oracle.stereo_filter(ti, di, kl, kr, 2.0, 30.0, 0.1)
+    assert m == len(ml) > 100 and np.array_equal(o["match_l"][0, :m], ml) and np.array_equal(o["match_r"][0, :m], mr)
+    hd.close()
+
+
 def test_extract_batch_and_resize_of_workspace(fe, oracle, synth):
     ls, rs = synth.sequence("cfsd", 3, seed=7)
     hd = fe.Handle(1000, 1.2, 8, 20, 7, 752, 480, max_images=6)
