@@ -147,6 +147,7 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
 
 __global__ void __launch_bounds__(BL_WARPS * 32)
 blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
+    b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[BL_WARPS][BL_SLOTS * BL_ROWB];
     const int lane = threadIdx.x & 31;
     const int task = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
@@ -175,5 +176,5 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
 
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s) {
     dim3 grid((g.total_blur_tasks + BL_WARPS - 1) / BL_WARPS, nimg);
-    blur_kernel<<<grid, BL_WARPS * 32, 0, s>>>(g, im);
+    b2_launch_pdl(blur_kernel, dim3(grid), dim3(BL_WARPS * 32), 0, s, g, im);
 }

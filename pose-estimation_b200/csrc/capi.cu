@@ -16,7 +16,16 @@
 #include "../../include/b2orb.h"
 #include "b2orb_internal.cuh"
 
+thread_local bool b2_pdl_on = false;
+
 namespace {
+
+// programmatic dependent launch for latency-sized batches only (b2orb_internal.cuh)
+constexpr int B2_PDL_MAX_IMAGES = 8;
+inline bool pdl_for(int nimg) {
+    static const int forced = [] { const char* e = getenv("B2ORB_PDL"); return e ? (atoi(e) ? 1 : 0) : -1; }();
+    return forced >= 0 ? forced != 0 : nimg <= B2_PDL_MAX_IMAGES;
+}
 
 inline int cv_round_f(float v) { return (int)lrintf(v); }   // cvRound: round-half-even
 inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
@@ -426,13 +435,15 @@ int bind_problems(b2orb_handle* h, int np) {
 int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     const B2Geom& g = h->geom;
     cudaStream_t s = h->stream;
+    b2_pdl_on = pdl_for(nimg);
+    // counters first: nothing between the resize chain and the FAST kernel breaks the programmatic launch chain
+    B2_CUDA(h, cudaMemsetAsync(h->d_raw_cnt, 0, h->raw_state_bytes, s));
     for (int l = 1; l < g.nlevels; ++l) {
         prof_mark(h, B2ORB_K_RESIZE);
         b2_launch_resize(g, im, l, h->d_xofs[l], h->d_xw[l], h->d_yofs[l], h->d_yw[l], nimg, s);
         ++h->launches;
     }
     prof_mark(h, -1);
-    B2_CUDA(h, cudaMemsetAsync(h->d_raw_cnt, 0, h->raw_state_bytes, s));
     prof_mark(h, B2ORB_K_FAST);
     if (g.total_cells > 0) {
         b2_launch_fast_score(g, im, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, nimg, s);
@@ -509,6 +520,7 @@ int upload_repack(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt
     const UploadPath path = upload_path(h, w, hgt, step, image_stride, on_device);
     const bool rect = rectifying(h, w, hgt, eye);
     if (!rect && path != UP_DEVICE && path != UP_TIGHT) return B2ORB_OK;
+    b2_pdl_on = pdl_for(2 * count);
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
     const uint8_t* from = path == UP_DEVICE ? src : h->d_raw + (size_t)slot0 * w * hgt;
     const int fstep = path == UP_DEVICE ? step : w;

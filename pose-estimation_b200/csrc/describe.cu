@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 2)
 describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
                 const int* __restrict__ sel_cnt, const unsigned* __restrict__ ic_table, KeyPointOut* __restrict__ kps,
                 uint8_t* __restrict__ desc, int* __restrict__ n_out) {
+    b2_pdl_wait();
     __shared__ unsigned s_ic[IC_WORDS];
     __shared__ unsigned s_wa[DS_WARPS][WA_ROWS * WA_WORDS];
     __shared__ unsigned s_wb[DS_WARPS][WB_ROWS * WB_WORDS + 2];
@@ -262,5 +263,5 @@ void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel
                         const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s) {
     const int per_cta = DS_WARPS * DS_KPW;
     dim3 grid((g.kp_cap + per_cta - 1) / per_cta, nimg);
-    describe_kernel<<<grid, DS_WARPS * 32, 0, s>>>(g, im, sel, sel_cnt, ic_table, static_cast<KeyPointOut*>(kps), desc, n_out);
+    b2_launch_pdl(describe_kernel, dim3(grid), dim3(DS_WARPS * 32), 0, s, g, im, sel, sel_cnt, ic_table, static_cast<KeyPointOut*>(kps), desc, n_out);
 }

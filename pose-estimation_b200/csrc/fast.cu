@@ -93,6 +93,7 @@ __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
 __global__ void __launch_bounds__(FS_WARPS * 32, 4)
 fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __restrict__ raw_list,
                   int* __restrict__ raw_cnt, uint8_t* __restrict__ cell_ini, int variant) {
+    b2_pdl_wait();
     __shared__ uint2 s_queue[FS_WARPS][FS_QUEUE];
     __shared__ unsigned s_ring[FS_WARPS][7][32];
     const int lane = threadIdx.x & 31;
@@ -274,6 +275,7 @@ __global__ void __launch_bounds__(FV_THREADS)
 fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw_list, const int* __restrict__ raw_cnt,
                  const uint8_t* __restrict__ cell_ini, uint32_t* __restrict__ cand, int* __restrict__ cand_cnt,
                  int chunks) {
+    b2_pdl_wait();
     const int level = blockIdx.x / chunks, chunk = blockIdx.x - level * chunks, b = blockIdx.y;
     const B2Level& L = g.lv[level];
     const int n = min(raw_cnt[b * g.nlevels + level], L.cand_cap);
@@ -327,7 +329,7 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* 
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
     const int variant = (long long)g.total_fast_tasks[1] * nimg >= 148LL * 16 * 4 ? 1 : 0;
     dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);
-    fast_score_kernel<<<grid, FS_WARPS * 32, 0, s>>>(g, im, raw, raw_cnt, cell_ini, variant);
+    b2_launch_pdl(fast_score_kernel, dim3(grid), dim3(FS_WARPS * 32), 0, s, g, im, raw, raw_cnt, cell_ini, variant);
 }
 
 void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
@@ -335,5 +337,5 @@ void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, 
     int chunks = 4;
     while (chunks < FV_MAX_CHUNKS && g.nlevels * chunks * nimg < 148 * 8) chunks *= 2;
     dim3 grid(g.nlevels * chunks, nimg);
-    fast_vote_kernel<<<grid, FV_THREADS, 0, s>>>(g, raw, raw_cnt, cell_ini, cand, cand_cnt, chunks);
+    b2_launch_pdl(fast_vote_kernel, dim3(grid), dim3(FV_THREADS), 0, s, g, raw, raw_cnt, cell_ini, cand, cand_cnt, chunks);
 }

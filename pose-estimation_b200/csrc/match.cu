@@ -42,6 +42,7 @@ __device__ __forceinline__ unsigned expand_q(unsigned w, int j) {
 
 __global__ void __launch_bounds__(MT_THREADS, 4)
 match_kernel(const B2MatchProblem* __restrict__ probs) {
+    b2_pdl_wait();
     __shared__ __align__(16) unsigned s_bits[MT_TILE * 8];   // train descriptors of the current pass
     __shared__ __align__(8) int s_cn[MT_TILE];                // (|t| << 22) + global train index, INT_MAX beyond nt
     const B2MatchProblem P = probs[blockIdx.y];
@@ -181,6 +182,7 @@ stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restri
                      const int* __restrict__ train_idx, const int* __restrict__ dist, int cap, float ratio,
                      float min_match, float max_dy, int* __restrict__ match_l, int* __restrict__ match_r,
                      int* __restrict__ n_match, uint8_t* __restrict__ cur_l, uint8_t* __restrict__ cur_r) {
+    b2_pdl_wait();
     __shared__ int s_red[SF_THREADS / 32];
     const int p = blockIdx.x;
     const int np = gridDim.x;
@@ -229,6 +231,7 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
                 const int* __restrict__ di_r, const int* __restrict__ n_cur, const int* __restrict__ n_hist, int cap,
                 float ratio, float min_match, int* __restrict__ circ_cur, int* __restrict__ circ_hist,
                 int* __restrict__ n_circ, int* __restrict__ n_left, int* __restrict__ n_right) {
+    b2_pdl_wait();
     __shared__ int s_red[SF_THREADS / 32];
     const int p = blockIdx.x;
     const int nc = n_cur[p], nh = n_hist[p];
@@ -336,6 +339,7 @@ constexpr int TC_THREADS = 2 * TC_ROWS;   // two thread groups: each expands hal
 
 __global__ void __launch_bounds__(TC_THREADS, 2)
 match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
+    b2_pdl_wait();
     extern __shared__ __align__(1024) uint8_t tc_smem[];       // A tile, then two B tiles
     __shared__ __align__(8) uint64_t s_mbar[2];
     __shared__ uint32_t s_tmem;
@@ -459,6 +463,7 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
 // Stereo problems [0,np): desc(left p) vs desc(right np+p).  Temporal problems [np, 3np): cur slot p+1 vs hist
 // slot p, left then right (src/feature-tracker.cpp:161-163, 258, 303).
 __global__ void bind_kernel(B2MatchProblem* pr, int np, B2BindBases b) {
+    b2_pdl_wait();
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= np) return;
     const size_t cap = b.cap, row = cap * 32;
@@ -468,7 +473,7 @@ __global__ void bind_kernel(B2MatchProblem* pr, int np, B2BindBases b) {
 }
 
 void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStream_t s) {
-    bind_kernel<<<(np + 127) / 128, 128, 0, s>>>(probs, np, b);
+    b2_launch_pdl(bind_kernel, dim3((np + 127) / 128), dim3(128), 0, s, probs, np, b);
 }
 
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s) {
@@ -476,20 +481,20 @@ void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStr
     static const bool use_imma = [] { const char* e = getenv("B2ORB_MATCH"); return e && e[0] == 'i'; }();
     if (use_imma) {   // warp-level IMMA version, kept for A/B measurements (B2ORB_MATCH=imma)
         dim3 grid((max_nq + MT_QPC - 1) / MT_QPC, nprob);
-        match_kernel<<<grid, MT_THREADS, 0, s>>>(probs);
+        b2_launch_pdl(match_kernel, dim3(grid), dim3(MT_THREADS), 0, s, probs);
         return;
     }
     const int smem = 3 * TC_TILE;
     cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device; cheap
     dim3 grid((max_nq + TC_ROWS - 1) / TC_ROWS, nprob);
-    match_tc_kernel<<<grid, TC_THREADS, smem, s>>>(probs);
+    b2_launch_pdl(match_tc_kernel, dim3(grid), dim3(TC_THREADS), smem, s, probs);
 }
 
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
                              const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,
                              int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, int npairs,
                              cudaStream_t s) {
-    stereo_filter_kernel<<<npairs, SF_THREADS, 0, s>>>(static_cast<const KeyPointIn*>(kps), desc, n_kp, train_idx, dist,
+    b2_launch_pdl(stereo_filter_kernel, dim3(npairs), dim3(SF_THREADS), 0, s, static_cast<const KeyPointIn*>(kps), desc, n_kp, train_idx, dist,
                                                        kp_cap, ratio, min_match, max_dy, match_l, match_r, n_match,
                                                        cur_l, cur_r);
 }
@@ -497,6 +502,6 @@ void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
                         const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
                         int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s) {
-    circular_kernel<<<nprob, SF_THREADS, 0, s>>>(ti_l, di_l, ti_r, di_r, n_cur, n_hist, cap, ratio, min_match,
+    b2_launch_pdl(circular_kernel, dim3(nprob), dim3(SF_THREADS), 0, s, ti_l, di_l, ti_r, di_r, n_cur, n_hist, cap, ratio, min_match,
                                                  circ_cur, circ_hist, n_circ, n_left, n_right);
 }

@@ -371,6 +371,7 @@ __global__ void __launch_bounds__(OT_THREADS)
 octree_kernel(const __grid_constant__ B2Geom g, const uint32_t* __restrict__ cand, const int* __restrict__ cand_cnt,
               unsigned short* __restrict__ pnode_all, unsigned* __restrict__ gscratch, int use_global,
               uint32_t* __restrict__ sel, int* __restrict__ sel_cnt, int force_legacy) {
+    b2_pdl_wait();
     extern __shared__ __align__(16) unsigned dyn[];
     __shared__ OtShared sh;
     __shared__ OtTables tab;
@@ -618,6 +619,6 @@ void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt
     const char* mode = getenv("B2ORB_OCTREE");   // "points" = point passes only (A/B runs, tests of the fallback path)
     const int force_legacy = mode && !strcmp(mode, "points") ? 1 : 0;
     dim3 grid(g.nlevels, nimg);
-    octree_kernel<<<grid, OT_THREADS, use_global ? 0 : smem, s>>>(g, cand, cand_cnt, pnode, scratch, use_global, sel,
+    b2_launch_pdl(octree_kernel, dim3(grid), dim3(OT_THREADS), use_global ? 0 : smem, s, g, cand, cand_cnt, pnode, scratch, use_global, sel,
                                                               sel_cnt, force_legacy);
 }

@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(RS_WARPS * 32)
 resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, int band_rows,
               const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
               const short* __restrict__ yw) {
+    b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
     const B2Level& L = g.lv[level];
     const int lane = threadIdx.x & 31;
@@ -150,6 +151,7 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
 __global__ void __launch_bounds__(256)
 repack_kernel(const uint8_t* __restrict__ src, int step, size_t stride, uint8_t* __restrict__ dst, int dpitch,
               size_t dstride, int w, int h) {
+    b2_pdl_wait();
     const int words = dpitch >> 2;
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= words * h) return;
@@ -171,6 +173,7 @@ repack_kernel(const uint8_t* __restrict__ src, int step, size_t stride, uint8_t*
 __global__ void __launch_bounds__(256)
 remap_kernel(const uint8_t* __restrict__ src, int step, size_t stride, const short2* __restrict__ map1,
              const unsigned short* __restrict__ map2, uint8_t* __restrict__ dst, int dpitch, size_t dstride, int w, int h) {
+    b2_pdl_wait();
     const int words = dpitch >> 2;
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= words * h) return;
@@ -207,6 +210,7 @@ ingest_bgra_kernel(const uint8_t* __restrict__ frames, int sstep, size_t sstride
                    const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
                    const short* __restrict__ yw, uint8_t* __restrict__ dst_l, uint8_t* __restrict__ dst_r, int dpitch,
                    size_t dstride, int half_w, int dh) {
+    b2_pdl_wait();
     const int words = dpitch >> 2;
     int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= 2 * words * dh) return;
@@ -248,14 +252,14 @@ void b2_launch_ingest_bgra(const uint8_t* frames, int sstep, size_t sstride, int
                            const int* yofs, const short* yw, uint8_t* dst_l, uint8_t* dst_r, int dpitch, size_t dstride,
                            int half_w, int dh, int count, cudaStream_t s) {
     dim3 grid((2 * (dpitch >> 2) * dh + 255) / 256, count);
-    ingest_bgra_kernel<<<grid, 256, 0, s>>>(frames, sstep, sstride, sw, sh, xofs, xw, yofs, yw, dst_l, dst_r, dpitch, dstride,
+    b2_launch_pdl(ingest_bgra_kernel, dim3(grid), dim3(256), 0, s, frames, sstep, sstride, sw, sh, xofs, xw, yofs, yw, dst_l, dst_r, dpitch, dstride,
                                             half_w, dh);
 }
 
 void b2_launch_remap(const uint8_t* src, int step, size_t stride, const void* map1, const void* map2, uint8_t* dst,
                      int dpitch, size_t dstride, int w, int h, int count, cudaStream_t s) {
     dim3 grid(((dpitch >> 2) * h + 255) / 256, count);
-    remap_kernel<<<grid, 256, 0, s>>>(src, step, stride, static_cast<const short2*>(map1),
+    b2_launch_pdl(remap_kernel, dim3(grid), dim3(256), 0, s, src, step, stride, static_cast<const short2*>(map1),
                                       static_cast<const unsigned short*>(map2), dst, dpitch, dstride, w, h);
 }
 
@@ -269,11 +273,11 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
     while (band > 4 && (long long)strips * ((L.h + band - 1) / band) * nimg < 148 * 48) band >>= 1;
     const int tasks = strips * ((L.h + band - 1) / band);
     dim3 grid((tasks + RS_WARPS - 1) / RS_WARPS, nimg);
-    resize_kernel<<<grid, RS_WARPS * 32, 0, s>>>(g, im, level, band, xofs, xw, yofs, yw);
+    b2_launch_pdl(resize_kernel, dim3(grid), dim3(RS_WARPS * 32), 0, s, g, im, level, band, xofs, xw, yofs, yw);
 }
 
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s) {
     dim3 grid(((dpitch >> 2) * h + 255) / 256, count);
-    repack_kernel<<<grid, 256, 0, s>>>(src, step, stride, dst, dpitch, dstride, w, h);
+    b2_launch_pdl(repack_kernel, dim3(grid), dim3(256), 0, s, src, step, stride, dst, dpitch, dstride, w, h);
 }

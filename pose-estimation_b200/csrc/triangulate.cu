@@ -158,6 +158,7 @@ __device__ __forceinline__ void store_point(const double (&X)[4], double max_dep
 // Generic form: n Point2d pairs -> 4 x n row-major points4D.
 __global__ void __launch_bounds__(128) triangulate_kernel(B2Projection pr, const double2* __restrict__ pix_l,
                                                           const double2* __restrict__ pix_r, int n, double* points4d) {
+    b2_pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double2 l = pix_l[i], r = pix_r[i];
@@ -174,6 +175,7 @@ __global__ void __launch_bounds__(128) triangulate_matches_kernel(B2Projection p
                                                                   const int* __restrict__ match_r,
                                                                   const int* __restrict__ n_match, int cap, int npairs,
                                                                   double* points4d, double* point_cam, uint8_t* flags) {
+    b2_pdl_wait();
     const int p = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_match[p]) return;
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(128) triangulate_matches_kernel(B2Projection p
 void b2_launch_triangulate(const B2Projection& pr, const double* pix_l, const double* pix_r, int n, double* points4d,
                            cudaStream_t s) {
     if (n <= 0) return;
-    triangulate_kernel<<<(n + 127) / 128, 128, 0, s>>>(pr, reinterpret_cast<const double2*>(pix_l),
+    b2_launch_pdl(triangulate_kernel, dim3((n + 127) / 128), dim3(128), 0, s, pr, reinterpret_cast<const double2*>(pix_l),
                                                        reinterpret_cast<const double2*>(pix_r), n, points4d);
 }
 
@@ -199,6 +201,6 @@ void b2_launch_triangulate_matches(const B2Projection& pr, const void* kps, cons
                                    uint8_t* flags, cudaStream_t s) {
     if (npairs <= 0) return;
     dim3 grid((cap + 127) / 128, npairs);
-    triangulate_matches_kernel<<<grid, 128, 0, s>>>(pr, static_cast<const b2orb_keypoint*>(kps), match_l, match_r, n_match,
+    b2_launch_pdl(triangulate_matches_kernel, dim3(grid), dim3(128), 0, s, pr, static_cast<const b2orb_keypoint*>(kps), match_l, match_r, n_match,
                                                     cap, npairs, points4d, point_cam, flags);
 }
