@@ -31,6 +31,8 @@
 //   keeps a corner iff b > ini or its cell's flag is clear and appends x | y<<12 | (b-1)<<24 to the candidate list
 //   (warp-aggregated atomics).  Candidate order is irrelevant downstream: the quadtree breaks response ties with
 //   a key that reproduces the reference's cell-row-major order.
+#include <cuda_fp16.h>
+#include <cstdlib>
 #include "b2orb_internal.cuh"
 
 namespace {
@@ -45,13 +47,31 @@ __device__ __forceinline__ unsigned vmax2(unsigned a, unsigned b) { return __vma
 __device__ __forceinline__ unsigned vmin3(unsigned a, unsigned b, unsigned c) { return __vimin3_u16x2(a, b, c); }
 __device__ __forceinline__ unsigned vmax3(unsigned a, unsigned b, unsigned c) { return __vimax3_u16x2(a, b, c); }
 
+// Pixels travel as 0x6400 | v per u16 lane: as an unsigned short that orders like v (VIMNMX.U16x2 on the ALU pipe),
+// and as a binary16 it IS the number 1024 + v, exactly — so the same registers can also be compared on the FMA pipe,
+// which this ALU-bound kernel leaves idle:  d = relu(a - b) (HFMA2.RELU),  max = b + d,  min = a - d (HADD2).
+// Every intermediate is an integer below 2048, hence exact in binary16, and the results carry the same 0x6400 tag.
+__device__ __forceinline__ void hminmax2(unsigned a, unsigned b, unsigned& mn, unsigned& mx) {
+    const __half2 ha = *reinterpret_cast<const __half2*>(&a), hb = *reinterpret_cast<const __half2*>(&b);
+    const __half2 d = __hfma2_relu(hb, __floats2half2_rn(-1.f, -1.f), ha);
+    const __half2 hx = __hadd2(hb, d), hn = __hsub2(ha, d);
+    mx = *reinterpret_cast<const unsigned*>(&hx);
+    mn = *reinterpret_cast<const unsigned*>(&hn);
+}
+
 // b for the two pixels packed in c (u16 lanes), ring pixels v[0..15] in circle order (same packing).
+// NQ of the 8 first-layer (min, max) pairs and NE of the 8 arc-end (min, max) pairs go to the FMA pipe.
+template <int NQ, int NE>
 __device__ __forceinline__ unsigned fast_b_pair(const unsigned (&v)[16], unsigned c) {
     unsigned qn[8], qx[8];     // min / max of v[j], v[j+1] for odd j = 2i+1
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        qn[i] = vmin2(v[2 * i + 1], v[(2 * i + 2) & 15]);
-        qx[i] = vmax2(v[2 * i + 1], v[(2 * i + 2) & 15]);
+        if (i < NQ) {
+            hminmax2(v[2 * i + 1], v[(2 * i + 2) & 15], qn[i], qx[i]);
+        } else {
+            qn[i] = vmin2(v[2 * i + 1], v[(2 * i + 2) & 15]);
+            qx[i] = vmax2(v[2 * i + 1], v[(2 * i + 2) & 15]);
+        }
     }
     unsigned rn[8], rx[8];     // min / max of v[j .. j+3]
 #pragma unroll
@@ -64,12 +84,19 @@ __device__ __forceinline__ unsigned fast_b_pair(const unsigned (&v)[16], unsigne
     for (int i = 0; i < 8; ++i) {
         // arcs k = 2i and k+1 share v[k+1 .. k+8] = rn[i], rn[i+2]; the ends are v[k] and v[k+9]
         const unsigned a = v[2 * i], e = v[(2 * i + 9) & 15];
-        pn[i] = vmin3(rn[i], rn[(i + 2) & 7], vmax2(a, e));   // max(min9[k], min9[k+1])
-        px[i] = vmax3(rx[i], rx[(i + 2) & 7], vmin2(a, e));   // min(max9[k], max9[k+1])
+        unsigned en, ex;
+        if (i < NE) {
+            hminmax2(a, e, en, ex);
+        } else {
+            en = vmin2(a, e);
+            ex = vmax2(a, e);
+        }
+        pn[i] = vmin3(rn[i], rn[(i + 2) & 7], ex);   // max(min9[k], min9[k+1])
+        px[i] = vmax3(rx[i], rx[(i + 2) & 7], en);   // min(max9[k], max9[k+1])
     }
     const unsigned rmax = vmax3(vmax3(pn[0], pn[1], pn[2]), vmax3(pn[3], pn[4], pn[5]), vmax2(pn[6], pn[7]));
     const unsigned rmin = vmin3(vmin3(px[0], px[1], px[2]), vmin3(px[3], px[4], px[5]), vmin2(px[6], px[7]));
-    return vmax2(rmax, c) - vmin2(rmin, c);   // per-lane non-negative: no borrow between the halves
+    return vmax2(rmax, c) - vmin2(rmin, c);   // per-lane non-negative (the 0x6400 tags cancel): no borrow between the halves
 }
 
 // one 4-byte async copy + its own commit group
@@ -90,6 +117,7 @@ __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
     return b & (one * 255u);
 }
 
+template <int NQ, int NE>
 __global__ void __launch_bounds__(FS_WARPS * 32, 4)
 fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __restrict__ raw_list,
                   int* __restrict__ raw_cnt, uint8_t* __restrict__ cell_ini, int variant) {
@@ -165,7 +193,7 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
         fs_cp_async4(ring_s + (((p) + FS_PF) % 7) * 128, col0 + min(off, offmax));                              \
         off += pitch;                                                                                           \
         const unsigned R1 = fs_wait_lds(ring_s + (p) * 128);                                                    \
-        const unsigned E1 = __byte_perm(R1, 0u, 0x4240), O1 = __byte_perm(R1, 0u, 0x4341);                      \
+        const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);                      \
         const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);    \
         const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                      \
         P[p][0] = __shfl_up_sync(0xFFFFFFFFu, O1, 1);                                                           \
@@ -217,12 +245,12 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
         {                                                                                                    \
             const unsigned v[16] = {P[s3][3], P[s3][4], P[s2][5], P[s1][6], P[s0][6], P[t1][6], P[t2][5], P[t3][4], \
                                     P[t3][3], P[t3][2], P[t2][1], P[t1][0], P[s0][0], P[s1][0], P[s2][1], P[s3][2]}; \
-            bE = fast_b_pair(v, P[s0][3]);                                                                   \
+            bE = fast_b_pair<NQ, NE>(v, P[s0][3]);                                                                   \
         }                                                                                                    \
         {                                                                                                    \
             const unsigned v[16] = {P[s3][4], P[s3][5], P[s2][6], P[s1][7], P[s0][7], P[t1][7], P[t2][6], P[t3][5], \
                                     P[t3][4], P[t3][3], P[t2][2], P[t1][1], P[s0][1], P[s1][1], P[s2][2], P[s3][3]}; \
-            bO = fast_b_pair(v, P[s0][4]);                                                                   \
+            bO = fast_b_pair<NQ, NE>(v, P[s0][4]);                                                                   \
         }                                                                                                    \
         const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1); \
         const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;                                              \
@@ -265,6 +293,204 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
 #undef B2_FAST_PAIRS
 #undef B2_FAST_FLAGS
 #undef B2_FAST_FLUSH
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fast_score_win_kernel — same strip / lane ownership, arithmetic, NMS, queue and flag logic as above, but the 7-row
+// window of pixel pairs lives in SHARED memory instead of registers.  Why: the register window forces a 7-phase
+// unrolled loop (static register indices), 36-40 KB of SASS for the loop alone — more than the 32 KB instruction
+// cache level, and ncu showed "no instruction" as the top stall once the min/max work was spread over both math
+// pipes.  Here the loop body exists once (~5 KB): each lane keeps its 8 pairs of the six older rows in a private
+// 6-slot ring (two 16-byte units per row: Q = pairs 2,5,3,4, W = pairs 1,6,0,7; lane stride 16 B, conflict-free
+// LDS.128 / STS.128), re-reads the 9 units the ring pixels of this step need, and overwrites the oldest slot with the
+// new row.  Slot addresses rotate through six registers (moves on the FMA pipe).  Only the lane itself reads what it
+// stored, so no warp synchronisation is involved.  Half the registers -> more resident warps.
+constexpr int FW_SLOTS = 6;
+constexpr int FW_RING = 8;      // cp.async staging slots per lane (power of two: slot = row & 7)
+#ifndef FW_MINB
+#define FW_MINB 5
+#endif
+
+__device__ __forceinline__ uint4 fw_lds128(unsigned a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint2 fw_lds64(unsigned a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fw_sts128(unsigned a, unsigned x, unsigned y, unsigned z, unsigned w) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+
+template <int NQ, int NE>
+__global__ void __launch_bounds__(FS_WARPS * 32, FW_MINB)
+fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __restrict__ raw_list,
+                      int* __restrict__ raw_cnt, uint8_t* __restrict__ cell_ini, int variant) {
+    b2_pdl_wait();
+    __shared__ uint2 s_queue[FS_WARPS][FS_QUEUE];
+    __shared__ unsigned s_ring[FS_WARPS][FW_RING][32];
+    __shared__ uint4 s_win[FS_WARPS][FW_SLOTS][64];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int task = blockIdx.x * FS_WARPS + wid;
+    if (task >= g.total_fast_tasks[variant]) return;
+    const int band_rows = B2_FAST_BAND << variant;
+    const int b = blockIdx.y;
+    int level = 0;
+    while (level + 1 < g.nlevels && task >= g.lv[level + 1].fast_task_base[variant]) ++level;
+    const B2Level& L = g.lv[level];
+    const int t = task - L.fast_task_base[variant];
+    const int band = t / L.fast_strips, strip = t - band * L.fast_strips;
+    int pitch;
+    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
+    uint2* queue = s_queue[wid];
+    int qn = 0;                                                // queue fill, warp-uniform
+    uint2* out = raw_list + (size_t)b * g.cand_total + L.cand_off;
+    int* out_cnt = raw_cnt + b * g.nlevels + level;
+    uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
+    const int w = L.w, h = L.h;
+    const int x = B2_BORDER - 8 + strip * 112 + lane * 4;      // lanes 2..29 own columns x .. x+3
+    const int ya = B2_EDGE + band * band_rows;                 // output rows [ya, yb)
+    const int yb = min(ya + band_rows, h - B2_EDGE);
+    const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
+    const int xo = min(x, pitch - 4);
+
+    unsigned inE = 0, inO = 0, mlE = 0, mlO = 0, mrE = 0, mrO = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int X = x + j;
+        const bool in = X >= B2_EDGE && X < w - B2_EDGE;
+        const int cx = (X - B2_EDGE) % L.w_cell;
+        const bool left = in && cx != 0;
+        const bool right = in && cx != L.w_cell - 1 && X + 1 < w - B2_EDGE;
+        const unsigned lanebits = (j & 2) ? 0xFFFF0000u : 0x0000FFFFu;
+        if (j & 1) { if (in) inO |= lanebits; if (left) mlO |= lanebits; if (right) mrO |= lanebits; }
+        else       { if (in) inE |= lanebits; if (left) mlE |= lanebits; if (right) mrE |= lanebits; }
+    }
+    const int cjA = max(x - B2_EDGE, 0) / L.w_cell;
+    unsigned sameA = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        if (max(x + j - B2_EDGE, 0) / L.w_cell == cjA) sameA |= 1u << j;
+    const unsigned kini = 0x00FF00FFu - (unsigned)g.ini_th * 0x00010001u;
+    const unsigned lt_mask = (1u << lane) - 1;
+    unsigned accE = 0, accO = 0;
+    const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
+    const bool store_lane = lane >= 2 && lane <= 29 && x < w - B2_BORDER;
+
+    const uint8_t* col0 = img + xo + (size_t)(ya - 4) * pitch;
+    const unsigned offmax = (unsigned)(nsteps - 1) * (unsigned)pitch;
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(&s_ring[wid][0][lane]);
+    unsigned off = 0;
+#pragma unroll
+    for (int i = 0; i < FS_PF; ++i) {
+        fs_cp_async4(ring_s + i * 128, col0 + min(off, offmax));
+        off += pitch;
+    }
+    // slot addresses by age: a1 = previous row (dy = +2 of the output row) ... a6 = oldest (dy = -3)
+    unsigned a1 = (unsigned)__cvta_generic_to_shared(&s_win[wid][0][lane]);
+    unsigned a2 = a1 + 1024, a3 = a1 + 2048, a4 = a1 + 3072, a5 = a1 + 4096, a6 = a1 + 5120;
+
+    unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
+    int y = ya;
+    int ci = (band * band_rows) / L.h_cell;
+    int cy = band * band_rows - ci * L.h_cell;
+    unsigned meta = (unsigned)(x - B2_BORDER) | ((unsigned)(ya - B2_BORDER) << 12) | ((unsigned)ci << 24);
+    const int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
+    int since_flush = 0;
+
+#define B2_FW_FLAGS()                                                                                          \
+    {                                                                                                           \
+        const unsigned hit = ((accE >> 8) & 1u) | ((accO >> 7) & 2u) | ((accE >> 22) & 4u) | ((accO >> 21) & 8u); \
+        if (store_lane && (hit & sameA)) flags[ci * L.n_cols + cjA] = 1;                                       \
+        if (store_lane && (hit & ~sameA)) flags[ci * L.n_cols + cjA + 1] = 1;                                  \
+        accE = accO = 0;                                                                                        \
+    }
+#define B2_FW_FLUSH()                                                                                          \
+    {                                                                                                           \
+        __syncwarp();                                                                                           \
+        if (qn) {                                                                                               \
+            int base = 0;                                                                                       \
+            if (lane == 0) base = atomicAdd(out_cnt, qn);                                                       \
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);                                                           \
+            for (int i = lane; i < qn; i += 32)                                                                 \
+                if (base + i < L.cand_cap) out[base + i] = queue[i];                                            \
+            __syncwarp();                                                                                       \
+            qn = 0;                                                                                             \
+        }                                                                                                       \
+    }
+
+#pragma unroll 1
+    for (int r = 0; r < nsteps; ++r) {
+        fs_cp_async4(ring_s + (((r + FS_PF) & (FW_RING - 1)) << 7), col0 + min(off, offmax));
+        off += pitch;
+        const unsigned R1 = fs_wait_lds(ring_s + ((r & (FW_RING - 1)) << 7));
+        const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);
+        const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);
+        const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);
+        const unsigned n0 = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
+        const unsigned n1 = __shfl_up_sync(0xFFFFFFFFu, c2, 1);
+        const unsigned n2 = __shfl_up_sync(0xFFFFFFFFu, c3, 1);
+        // new row's pairs: n0, n1, n2, E1, O1, c2, c3, E2  (P[0..7] of the register version)
+        if (r >= 6) {
+            // unit Q = pairs (2, 5, 3, 4), unit W = pairs (1, 6, 0, 7): every load asks for exactly what it uses
+            // (ptxas splits a partly used LDS.128 into scalar loads, 4-way bank conflicts at this lane stride)
+            const uint2 q1 = fw_lds64(a1), w1 = fw_lds64(a1 + 512);       // dy +2: pairs 2,5 | 1,6
+            const uint4 w2 = fw_lds128(a2 + 512);                          // dy +1: pairs 1,6,0,7
+            const uint2 q3 = fw_lds64(a3 + 8);                             // dy  0: pairs 3,4
+            const uint4 w3 = fw_lds128(a3 + 512);                          //        pairs 1,6,0,7
+            const uint4 w4 = fw_lds128(a4 + 512);                          // dy -1
+            const uint2 q5 = fw_lds64(a5), w5 = fw_lds64(a5 + 512);       // dy -2
+            const uint4 q6 = fw_lds128(a6);                                // dy -3: pairs 2,5,3,4
+            unsigned bE, bO;
+            {
+                const unsigned v[16] = {E1, O1, q1.y, w2.y, w3.y, w4.y, q5.y, q6.w,
+                                        q6.z, q6.x, w5.x, w4.z, w3.z, w2.z, w1.x, n2};
+                bE = fast_b_pair<NQ, NE>(v, q3.x);
+            }
+            {
+                const unsigned v[16] = {O1, c2, w1.y, w2.w, w3.w, w4.w, w5.y, q6.y,
+                                        q6.w, q6.z, q5.x, w4.x, w3.x, w2.x, q1.x, E1};
+                bO = fast_b_pair<NQ, NE>(v, q3.y);
+            }
+            const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1);
+            const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;
+            const unsigned rE = bO & mrE;
+            const unsigned lO = bE & mlO;
+            const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;
+            const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);
+            if (r >= 8) {
+                const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;
+                const unsigned dn = (cy != hcell1 && y != ylast) ? 0xFFFFFFFFu : 0u;
+                const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));
+                const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));
+                const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;
+                const unsigned m4 = __byte_perm(oE, oO, 0x6240);
+                accE |= oE + kini; accO |= oO + kini;
+                const bool has = store_lane && m4 != 0;
+                const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);
+                if (has) queue[qn + __popc(bal & lt_mask)] = make_uint2(m4, meta);
+                qn += __popc(bal);
+                ++y;
+                meta += 0x1000u;
+                if (cy == hcell1) { B2_FW_FLAGS() cy = 0; ++ci; meta += 0x1000000u; } else ++cy;
+                if (++since_flush == FS_FLUSH) { B2_FW_FLUSH() since_flush = 0; }
+            }
+            rmE_a = rmE_b; rmO_a = rmO_b;
+            rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;
+            sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);
+        }
+        fw_sts128(a6, n2, c2, E1, O1);          // Q = pairs 2, 5, 3, 4
+        fw_sts128(a6 + 512, n1, c3, n0, E2);    // W = pairs 1, 6, 0, 7
+        const unsigned tmp = a6;
+        a6 = a5; a5 = a4; a4 = a3; a3 = a2; a2 = a1; a1 = tmp;
+    }
+    B2_FW_FLUSH()
+    B2_FW_FLAGS()
+#undef B2_FW_FLAGS
+#undef B2_FW_FLUSH
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -329,7 +555,20 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* 
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
     const int variant = (long long)g.total_fast_tasks[1] * nimg >= 148LL * 16 * 4 ? 1 : 0;
     dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);
-    b2_launch_pdl(fast_score_kernel, dim3(grid), dim3(FS_WARPS * 32), 0, s, g, im, raw, raw_cnt, cell_ini, variant);
+    // Default: shared-memory window kernel, first-layer (min, max) pairs on the FMA pipe.  A/B switches:
+    // B2ORB_FAST=regs -> the register-window kernel (all min/max on the ALU pipe); B2ORB_FAST_FMA=<NQ><NE> -> how many
+    // first-layer / arc-end pairs of the window kernel use the FMA pipe (0, 80, 88).
+    static const int mix = [] { const char* e = getenv("B2ORB_FAST_FMA"); return e ? atoi(e) : 80; }();
+    static const bool regs = [] { const char* e = getenv("B2ORB_FAST"); return e && e[0] == 'r'; }();
+    const dim3 block(FS_WARPS * 32);
+    if (regs)
+        b2_launch_pdl(fast_score_kernel<0, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
+    else if (mix == 0)
+        b2_launch_pdl(fast_score_win_kernel<0, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
+    else if (mix == 88)
+        b2_launch_pdl(fast_score_win_kernel<8, 8>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
+    else
+        b2_launch_pdl(fast_score_win_kernel<8, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
 }
 
 void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
