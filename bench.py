@@ -127,6 +127,7 @@ def main():
     ap.add_argument("--triangulate", action="store_true",
                     help="next row f4: cv::triangulatePoints + depth gate of the kept matches in the same device pass")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
+    ap.add_argument("--latency-calls", type=int, default=200, help="single-pair calls of the latency leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")
     args = ap.parse_args()
 
@@ -300,6 +301,30 @@ def main():
     e2e_value = world * nh * Be * e2e_steps / float(te.item())
     clocks = sampler.stop() if sampler else None
 
+    # ---------------- p50 frame latency: ONE stereo pair per C-ABI call, pinned host images in, host results out --------
+    # (the second half of BASELINE.json's metric; what visual-inertial-slam.cpp sees per frame)
+    latency = None
+    if not args.skip_e2e:
+        hl = fe.Handle(*cfg, w, h, max_images=2, device=local)
+        if rect_maps is not None:
+            hl.set_rectification(rect_maps[0][0], rect_maps[0][1], rect_maps[1][0], rect_maps[1][1])
+        if proj is not None:
+            hl.set_projection(*proj)
+        out1 = hl.alloc_stereo_out(1, pinned=True)
+        lat = []
+        for k in range(args.latency_calls + 20):
+            i = k % pool
+            t0 = time.perf_counter()
+            hl.check(hl.L.b2orb_stereo_frontend(hl.h, pin_l[i:].ctypes.data, pin_r[i:].ctypes.data, 1, w, h, w, img_bytes,
+                                                1 if temporal else 0, out1[1]))
+            lat.append((time.perf_counter() - t0) * 1e3)
+        lat = sorted(lat[20:])
+        latency = {"p50_ms": round(lat[len(lat) // 2], 4), "p95_ms": round(lat[int(len(lat) * 0.95)], 4),
+                   "max_ms": round(lat[-1], 4), "calls": len(lat), "device_ms_last_call": round(hl.last_device_ms, 4),
+                   "what": "b2orb_stereo_frontend, 1 pair per call, pinned host images in -> keypoints, descriptors, "
+                           "matches on the host; wall clock around the call"}
+        hl.close()
+
     # context for the e2e number: what the host link delivers for a plain pinned H2D copy of one call's images
     link_src = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
     link_dst = torch.empty_like(link_src, device="cuda")
@@ -355,6 +380,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * img_bytes * Be, "d2h_bytes_per_step": d2h_per_pair * Be,
                 "pairs_per_call": Be, "host_threads": nh, "steps": e2e_steps * nh,
                 "h2d_link_gbs": round(h2d_gbs, 2), "h2d_link_bound": round(h2d_gbs * 1e9 / (2 * img_bytes), 1)},
+        "latency": latency,
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -378,6 +404,8 @@ def main():
         t0 = time.perf_counter()
         orc.run_pairs(cfg, fl, fr, synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST, 1, 2, temporal)
         fdt = time.perf_counter() - t0
+        if latency is not None:
+            latency["cpu_port_ms"] = round(fdt / 6 * 1e3, 2)   # one pair on the host, reference structure (2 threads)
         line["cpu_baseline"]["faithful"] = {"value": 6 / fdt, "unit": UNIT, "cores": 2,
                                             "sample": f"6 pairs sequentially, L/R extraction on 2 threads, {fdt:.2f} s"}
     print(json.dumps(line))

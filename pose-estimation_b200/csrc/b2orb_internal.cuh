@@ -122,6 +122,8 @@ struct B2MatchProblem {
 };
 
 // ---- kernel launchers (each file documents the reference lines it restates) --------------------
+bool b2_launch_pyramid_chain(const B2Geom& g, const B2Images& im, int* const* xofs, short* const* xw, int* const* yofs,
+                             short* const* yw, int nimg, cudaStream_t s);
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s);
 // cv::remap with fixed-point maps (map1: short2 per pixel, map2: u16 per pixel), source and output of size w x h

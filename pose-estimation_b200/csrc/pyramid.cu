@@ -32,27 +32,22 @@ __device__ __forceinline__ void rs_wait() { asm volatile("cp.async.wait_group %0
 // weights (a0 | a1 << 16).  Every source row is interpolated once and used by the 1-2 output rows that need it.
 // Vertical pass: two IMAD.HI with the weights pre-shifted by 16, one add; the rounding shift is folded into a
 // multiply by 64 so the result byte can be picked with PRMT.
-__global__ void __launch_bounds__(RS_WARPS * 32)
-resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, int band_rows,
-              const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
-              const short* __restrict__ yw) {
-    b2_pdl_wait();
-    __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
+// One task = (band, strip) of `level` of image b, run by the calling warp with its private ring.
+__device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im, int b, int level, int band_rows, int task,
+                                            const int* __restrict__ xofs, const short* __restrict__ xw,
+                                            const int* __restrict__ yofs, const short* __restrict__ yw, uint8_t* ring) {
     const B2Level& L = g.lv[level];
     const int lane = threadIdx.x & 31;
     const int strips = (L.w + 127) >> 7;
-    const int task = blockIdx.x * RS_WARPS + (threadIdx.x >> 5);
     const int band = task / strips, strip = task - band * strips;
     const int dy0 = band * band_rows;
     if (dy0 >= L.h) return;
     const int dy1 = min(dy0 + band_rows, L.h);
-    const int b = blockIdx.y;
     int spitch;
     const uint8_t* src = b2_level_ptr(g, im, b, level - 1, spitch);
     const int sh = g.lv[level - 1].h;
     uint8_t* dst = im.pyr + (size_t)b * g.slab + L.off;
     const int dx0 = strip * 128 + lane * 4;
-    uint8_t* ring = s_ring[threadIdx.x >> 5];
 
     // source span of the strip, 16-byte aligned; lane c copies chunk c of every source row
     const int gx0 = xofs[strip * 128] & ~15;
@@ -200,6 +195,54 @@ remap_kernel(const uint8_t* __restrict__ src, int step, size_t stride, const sho
 }
 
 // cfsd live ingest (next row f2), src/cfsd-state-estimation.cpp:117-127: CV_8UC4 frame with both eyes side by side ->
+__global__ void __launch_bounds__(RS_WARPS * 32)
+resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, int band_rows,
+              const int* __restrict__ xofs, const short* __restrict__ xw, const int* __restrict__ yofs,
+              const short* __restrict__ yw) {
+    b2_pdl_wait();
+    __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
+    resize_task(g, im, blockIdx.y, level, band_rows, blockIdx.x * RS_WARPS + (threadIdx.x >> 5), xofs, xw, yofs, yw,
+                s_ring[threadIdx.x >> 5]);
+}
+
+// Latency path (a few images per call): the seven per-level launches above are a chain of tiny dependent kernels, ~8 us
+// each for one stereo pair.  Here ONE thread-block cluster per image walks the whole chain: the cluster's warps share
+// the (band, strip) tasks of level l, then meet at a cluster barrier (arrive.release / wait.acquire orders the global
+// stores of level l before the cp.async.cg reads of level l+1, which bypass L1) and go on to level l+1.
+constexpr int PC_WARPS = 8;
+struct B2ResizeTables {
+    const int* xofs[B2_MAX_LEVELS];
+    const short* xw[B2_MAX_LEVELS];
+    const int* yofs[B2_MAX_LEVELS];
+    const short* yw[B2_MAX_LEVELS];
+};
+
+__global__ void __launch_bounds__(PC_WARPS * 32)
+pyramid_chain_kernel(const __grid_constant__ B2Geom g, const B2Images im, const __grid_constant__ B2ResizeTables tb) {
+    b2_pdl_wait();
+    __shared__ __align__(16) uint8_t s_ring[PC_WARPS][RS_SLOTS * RS_ROWB];
+    unsigned crank, csize;
+    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    asm("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
+    const int wid = threadIdx.x >> 5;
+    const int cw = (int)crank * PC_WARPS + wid, ncw = (int)csize * PC_WARPS;
+    const int b = blockIdx.y;
+    for (int level = 1; level < g.nlevels; ++level) {
+        const B2Level& L = g.lv[level];
+        const int strips = (L.w + 127) >> 7;
+        const int nb = max(ncw / strips, 1);
+        const int band = max((L.h + nb - 1) / nb, 4);
+        const int tasks = strips * ((L.h + band - 1) / band);
+        for (int task = cw; task < tasks; task += ncw) {
+            resize_task(g, im, b, level, band, task, tb.xofs[level], tb.xw[level], tb.yofs[level], tb.yw[level], s_ring[wid]);
+            rs_wait<0>();
+            __syncwarp();
+        }
+        if (level + 1 < g.nlevels)
+            asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+}
+
 // cv::resize(INTER_LINEAR) to 2*half_w x dh -> cvtColor(BGR2GRAY) -> left / right halves, fused: one thread per output
 // word of one eye; four 32-bit pixel loads per output pixel, the Q11 resize arithmetic of resize_kernel per channel
 // (H = S0*wx0 + S1*wx1;  v = ((wy0*(H0>>4))>>16) + ((wy1*(H1>>4))>>16) + 2) >> 2), then OpenCV 4.x's 15-bit grey
@@ -274,6 +317,45 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
     const int tasks = strips * ((L.h + band - 1) / band);
     dim3 grid((tasks + RS_WARPS - 1) / RS_WARPS, nimg);
     b2_launch_pdl(resize_kernel, dim3(grid), dim3(RS_WARPS * 32), 0, s, g, im, level, band, xofs, xw, yofs, yw);
+}
+
+// Whole resize chain in one launch (latency path).  Returns false when the cluster launch is not available, and the
+// caller falls back to the per-level launches.
+bool b2_launch_pyramid_chain(const B2Geom& g, const B2Images& im, int* const* xofs, short* const* xw, int* const* yofs,
+                             short* const* yw, int nimg, cudaStream_t s) {
+    static int cluster = -1;    // largest usable cluster size (16, 8) or 0
+    if (cluster < 0) {
+        cluster = 0;
+        if (cudaFuncSetAttribute(pyramid_chain_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+            cudaGetLastError();
+        for (int c : {16, 8}) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(c, 1);
+            cfg.blockDim = dim3(PC_WARPS * 32);
+            cudaLaunchAttribute a[1];
+            a[0].id = cudaLaunchAttributeClusterDimension;
+            a[0].val.clusterDim.x = c; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
+            cfg.attrs = a; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, pyramid_chain_kernel, &cfg) == cudaSuccess && n > 0) { cluster = c; break; }
+            cudaGetLastError();
+        }
+    }
+    if (cluster == 0) return false;
+    B2ResizeTables tb = {};
+    for (int l = 1; l < g.nlevels; ++l) { tb.xofs[l] = xofs[l]; tb.xw[l] = xw[l]; tb.yofs[l] = yofs[l]; tb.yw[l] = yw[l]; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster, nimg);
+    cfg.blockDim = dim3(PC_WARPS * 32);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = b2_pdl_on ? 2 : 1;
+    return cudaLaunchKernelEx(&cfg, pyramid_chain_kernel, g, im, tb) == cudaSuccess;
 }
 
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,

@@ -257,6 +257,40 @@ def test_pipelined_host_path_equals_single_call(chunk, lanes, fe, synth, monkeyp
     ref.close(); pip.close()
 
 
+@pytest.mark.parametrize("npairs", [1, 3])
+def test_direct_export_to_pinned_outputs_equals_copy_path(npairs, fe, synth):
+    """Latency path: with pinned output arrays one kernel stores the valid prefixes straight into host memory instead
+    of ~14 device-to-host copies.  Same results as the copy path (pageable arrays), temporal chain and triangulated
+    points included; only entries [0, n) are defined on either path."""
+    w, h, nf, ini, mn = synth.SHAPES["cfsd"]
+    ls, rs = synth.sequence("cfsd", 2 * npairs, seed=5)
+    fx = 0.58 * w
+    P1 = [[fx, 0, 0.49 * w, 0], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]
+    P2 = [[fx, 0, 0.49 * w, 0.537 * fx], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]
+    a_hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    b_hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    for hd in (a_hd, b_hd):
+        hd.set_projection(P1, P2, 20.0)
+    pinned = b_hd.alloc_stereo_out(npairs, pinned=True)
+    for arr in pinned[0].values():
+        arr.view(np.uint8)[...] = 0xAB
+    for rep in range(2):                                   # second call: temporal history + cached export plan
+        i = rep * npairs
+        a = a_hd.stereo_frontend(ls[i:i + npairs], rs[i:i + npairs], temporal=True)
+        b = b_hd.stereo_frontend(ls[i:i + npairs], rs[i:i + npairs], temporal=True, out=pinned)
+        _stereo_equal(a, b, npairs)
+        for p in range(npairs):
+            n = int(a["n_match"][p])
+            assert n > 10
+            assert np.array_equal(a["points4d"][p, :, :n].view(np.uint64), b["points4d"][p, :, :n].view(np.uint64))
+            assert np.array_equal(a["point_cam"][p, :n].view(np.uint64), b["point_cam"][p, :n].view(np.uint64))
+            assert np.array_equal(a["depth_flags"][p, :n], b["depth_flags"][p, :n])
+            nl = int(a["n_l"][p])
+            assert np.all(b["desc_l"][p, nl:] == 0xAB)     # nothing beyond the valid prefix is touched
+    assert a["n_circ"].min() > 5
+    a_hd.close(); b_hd.close()
+
+
 def test_temporal_track_entry_point(fe, oracle):
     rng = np.random.default_rng(5)
     hist_l = rng.integers(0, 256, (300, 32), dtype=np.uint8); hist_r = rng.integers(0, 256, (300, 32), dtype=np.uint8)
