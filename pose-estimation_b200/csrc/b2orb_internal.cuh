@@ -36,7 +36,8 @@ inline cudaError_t b2_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block
 #define B2_MAX_LEVELS 12
 #define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
 #define B2_BORDER 16        // EDGE_THRESHOLD-3 = minBorderX/Y, src/ORBextractor.cc:773-776
-#define B2_FAST_BAND 32     // corner-map rows per FAST score task (fast.cu): variant v uses B2_FAST_BAND << v rows
+#define B2_FAST_BAND 16     // corner-map rows per FAST score task (fast.cu): variant v uses B2_FAST_BAND << v rows
+#define B2_FAST_VARIANTS 3  // 16 rows (latency-sized calls), 32, 64 (large batches: less halo work)
 #define B2_BLUR_BAND 32     // output rows per blur task (blur.cu)
 #define B2_HALF_PATCH 15    // HALF_PATCH_SIZE, src/ORBextractor.cc:73
 
@@ -48,7 +49,7 @@ struct B2Level {
     int n_cols, n_rows;       // FAST cell grid (src/ORBextractor.cc:784-787)
     int w_cell, h_cell;
     int cell_base;            // first flattened cell index of this level
-    int fast_task_base[2];    // first flattened FAST score task (band, strip) of this level, per band variant
+    int fast_task_base[B2_FAST_VARIANTS];    // first flattened FAST score task (band, strip) of this level, per band variant
     int fast_strips;          // 112-px strips per row band (fast.cu)
     int blur_task_base;       // first flattened blur task (band, strip) of this level
     int blur_strips;          // 128-px strips per row band
@@ -71,7 +72,7 @@ struct B2Geom {
     int ini_th, min_th;
     int total_cells;          // over all levels
     int total_blur_tasks;
-    int total_fast_tasks[2];  // per band variant (short bands for small batches, long bands for less halo work)
+    int total_fast_tasks[B2_FAST_VARIANTS];  // per band variant (short bands for small batches, long bands for less halo work)
     int sel_total;            // per-image selected-keypoint slots (sum of sel_cap)
     int kp_cap;               // per-image output capacity
     unsigned cand_total;      // per-image candidate slots

@@ -105,6 +105,9 @@ struct b2orb_handle {
     int bound_np = -1;                                   // batch size the problem table is bound to
     // optional per-kernel timing (b2orb_profile_*): events recorded between launches on the handle's stream
     bool profiling = false;
+    // latency path: the blur only needs the pyramid, so it runs on a side stream next to FAST -> vote -> quadtree
+    cudaStream_t s_aux = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<cudaEvent_t> prof_ev;                    // pool
     std::vector<int> prof_tag;                           // tag of the launch that FOLLOWS event i (-1 = none)
     size_t prof_used = 0;
@@ -266,7 +269,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         memcpy(g.tapv, v, sizeof v);
     }
     unsigned off = 0, cand_off = 0, node_off = 0;
-    int cells = 0, tiles = 0, sel = 0, ftasks[2] = {0, 0};
+    int cells = 0, tiles = 0, sel = 0, ftasks[B2_FAST_VARIANTS] = {};
     for (int l = 0; l < c.nlevels; ++l) {
         B2Level& L = g.lv[l];
         // ComputePyramid :1111-1112: Size(cvRound((float)cols*scale), cvRound((float)rows*scale))
@@ -287,8 +290,8 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
         const int n_cols = width > 0 ? (int)(width / 30.f) : 0, n_rows = height > 0 ? (int)(height / 30.f) : 0;
         L.cell_base = cells;
-        L.fast_task_base[0] = ftasks[0];   // levels without cells own zero tasks but must keep the list monotonic
-        L.fast_task_base[1] = ftasks[1];
+        for (int v = 0; v < B2_FAST_VARIANTS; ++v)
+            L.fast_task_base[v] = ftasks[v];   // levels without cells own zero tasks but must keep the list monotonic
         L.n_ini = 1;
         L.h_x = 1.f;
         if (n_cols >= 1 && n_rows >= 1) {   // else: the reference divides by zero; the level yields no keypoints
@@ -300,13 +303,14 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
             if ((long long)n_cols * n_rows * L.w_cell * L.h_cell >= (1 << 24)) return "level too large for 24-bit order keys";
             cells += n_cols * n_rows;
             L.fast_strips = (L.w - 2 * B2_BORDER + 111) / 112;
-            for (int v = 0; v < 2; ++v)
+            for (int v = 0; v < B2_FAST_VARIANTS; ++v)
                 ftasks[v] += L.fast_strips * ((L.h - 2 * B2_EDGE + (B2_FAST_BAND << v) - 1) / (B2_FAST_BAND << v));
             // DistributeOctTree :543-545
             L.n_ini = (int)std::round((float)(maxBX - minB) / (maxBY - minB));
             if (L.n_ini < 1) {   // taller than 2:1 -> the reference divides by zero; no keypoints
                 L.n_ini = 1; L.n_cols = L.n_rows = 0; cells -= n_cols * n_rows;
-                ftasks[0] = L.fast_task_base[0]; ftasks[1] = L.fast_task_base[1]; L.fast_strips = 0;
+                for (int v = 0; v < B2_FAST_VARIANTS; ++v) ftasks[v] = L.fast_task_base[v];
+                L.fast_strips = 0;
             } else if (L.n_ini > 256) return "aspect ratio above 256:1";
             L.h_x = (float)(maxBX - minB) / L.n_ini;
         }
@@ -330,8 +334,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     if (w > 4096 + B2_BORDER || hgt > 4096 + B2_BORDER) return "image larger than 4096 px";
     g.total_cells = cells;
     g.total_blur_tasks = tiles;
-    g.total_fast_tasks[0] = ftasks[0];
-    g.total_fast_tasks[1] = ftasks[1];
+    for (int v = 0; v < B2_FAST_VARIANTS; ++v) g.total_fast_tasks[v] = ftasks[v];
     g.sel_total = sel;
     g.kp_cap = sel;
     g.cand_total = cand_off;
@@ -473,6 +476,16 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
         ++h->launches;
     }
     prof_mark(h, -1);
+    // B2ORB_FORK=<max images>: blur on the side stream for latency-sized calls (not while profiling per kernel)
+    static const int fork_max = [] { const char* e = getenv("B2ORB_FORK"); return e ? atoi(e) : 8; }();
+    const bool fork = nimg <= fork_max && !h->profiling && h->s_aux;
+    if (fork) {
+        B2_CUDA(h, cudaEventRecord(h->ev_fork, s));
+        B2_CUDA(h, cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
+        b2_launch_blur(g, im, nimg, h->s_aux);
+        ++h->launches;
+        B2_CUDA(h, cudaEventRecord(h->ev_join, h->s_aux));
+    }
     prof_mark(h, B2ORB_K_FAST);
     if (g.total_cells > 0) {
         b2_launch_fast_score(g, im, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, nimg, s);
@@ -483,9 +496,13 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     prof_mark(h, B2ORB_K_OCTREE);
     b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
     ++h->launches;
-    prof_mark(h, B2ORB_K_BLUR);
-    b2_launch_blur(g, im, nimg, s);
-    ++h->launches;
+    if (fork) {
+        B2_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));
+    } else {
+        prof_mark(h, B2ORB_K_BLUR);
+        b2_launch_blur(g, im, nimg, s);
+        ++h->launches;
+    }
     prof_mark(h, B2ORB_K_DESCRIBE);
     b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_ic_table, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
     ++h->launches;
@@ -761,6 +778,9 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
     cudaEventCreate(&h->ev0);
     cudaEventCreate(&h->ev1);
     cudaEventCreateWithFlags(&h->ev_hist, cudaEventDisableTiming);
+    cudaStreamCreateWithFlags(&h->s_aux, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming);
@@ -788,6 +808,9 @@ void b2orb_destroy(b2orb_handle* h) {
     for (void* p : {(void*)h->d_ing_xofs, (void*)h->d_ing_yofs, (void*)h->d_ing_xw, (void*)h->d_ing_yw})
         if (p) cudaFree(p);
     if (h->ev_hist) cudaEventDestroy(h->ev_hist);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->s_aux) cudaStreamDestroy(h->s_aux);
     if (h->ev_done) cudaEventDestroy(h->ev_done);
     if (h->ev_in) cudaEventDestroy(h->ev_in);
     if (h->ev_out) cudaEventDestroy(h->ev_out);

@@ -552,8 +552,12 @@ fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw
 void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
                           cudaStream_t s) {
     if (g.total_fast_tasks[0] <= 0) return;
+    static const int forced = [] { const char* e = getenv("B2ORB_FAST_BAND"); return e ? atoi(e) : -1; }();   // A/B runs
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
-    const int variant = (long long)g.total_fast_tasks[1] * nimg >= 148LL * 16 * 4 ? 1 : 0;
+    // and short ones while a 32-row launch would not even give every SM two CTAs (per-CTA latency is what counts then)
+    int variant = (long long)g.total_fast_tasks[2] * nimg >= 148LL * 16 * 4 ? 2
+                  : (long long)g.total_fast_tasks[1] * nimg >= 148LL * 2 * 4 ? 1 : 0;
+    if (forced >= 0 && forced < B2_FAST_VARIANTS) variant = forced;
     dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);
     // Default: shared-memory window kernel, first-layer (min, max) pairs on the FMA pipe.  A/B switches:
     // B2ORB_FAST=regs -> the register-window kernel (all min/max on the ALU pipe); B2ORB_FAST_FMA=<NQ><NE> -> how many
