@@ -462,7 +462,9 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     B2_CUDA(h, cudaMemsetAsync(h->d_raw_cnt, 0, h->raw_state_bytes, s));
     // B2ORB_CHAIN=<max images>: the whole resize chain in one cluster launch (pyramid.cu).  Off by default: measured
     // 38 us for a KITTI pair against ~45 us for the seven programmatically chained launches it replaces, and the
-    // single-pair latency did not move (per-task table loads + cp.async prologue are the floor of every level).
+    // single-pair latency did not move (per-task table loads + cp.async prologue are the floor of every level).  A third
+    // variant (one CTA per row band of the image across all levels, thread per output word, 7 __syncthreads instead of
+    // 7 launches) measured 35 us and was dropped: with programmatic dependent launch the 7 launches cost ~18 us.
     static const int chain_max = [] { const char* e = getenv("B2ORB_CHAIN"); return e ? atoi(e) : 0; }();
     bool chained = false;
     if (nimg <= chain_max && g.nlevels > 1) {

@@ -140,7 +140,7 @@ match_kernel(const B2MatchProblem* __restrict__ probs) {
     }
 }
 
-constexpr int SF_THREADS = 256;
+constexpr int SF_THREADS = 1024;   // one CTA per pair: the passes over ~2000 matches are latency chains, so use the widest CTA
 
 __device__ __forceinline__ int block_min(int v, int* s_red) {
 #pragma unroll

@@ -7,7 +7,7 @@ import json
 import subprocess
 import sys
 
-TAGS = {"resize_kernel": "resize", "fast_score_kernel": "fast", "fast_vote_kernel": "fast_cells", "octree_kernel": "octree",
+TAGS = {"resize_kernel": "resize", "fast_score_kernel": "fast", "fast_score_win_kernel": "fast", "match_tc_kernel": "match_stereo", "fast_vote_kernel": "fast_cells", "octree_kernel": "octree",
         "blur_kernel": "blur", "describe_kernel": "describe", "match_kernel": "match_stereo",
         "stereo_filter_kernel": "stereo_filter", "circular_kernel": "circular", "repack_kernel": "ingest"}
 
@@ -22,7 +22,7 @@ def main():
     out = {}
     seen_match = 0
     for r in rows[2:]:
-        name = r[ik].split("(")[0].replace("<unnamed>::", "").strip()
+        name = next((k for k in sorted(TAGS, key=len, reverse=True) if k + "(" in r[ik] or k + "<" in r[ik]), None)
         tag = TAGS.get(name)
         if tag is None:
             continue
