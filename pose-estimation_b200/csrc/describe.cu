@@ -12,7 +12,7 @@
 
 namespace {
 
-__device__ const signed char kPattern[1024] = {
+__device__ __align__(16) const signed char kPattern[1024] = {
 #include "orb_pattern.inc"
 };
 
@@ -110,11 +110,7 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     __shared__ unsigned s_ic[IC_WORDS];
     __shared__ unsigned s_wa[DS_WARPS][WA_ROWS * WA_WORDS];
     __shared__ unsigned s_wb[DS_WARPS][WB_ROWS * WB_WORDS + 2];
-    // rotated-BRIEF pattern as floats, transposed to [coordinate][lane]: one conflict-free LDS per use instead of a
-    // scattered global byte load + I2F (the quarter-rate XU pipe was the limiter)
-    __shared__ float s_pat[32 * 32];
     for (int i = threadIdx.x; i < IC_WORDS; i += DS_WARPS * 32) s_ic[i] = ic_table[i];
-    for (int i = threadIdx.x; i < 1024; i += DS_WARPS * 32) s_pat[(i & 31) * 32 + (i >> 5)] = (float)kPattern[i];
     __syncthreads();
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -132,6 +128,17 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     unsigned* wa = s_wa[wid];
     unsigned* wb = s_wb[wid];
     const uint8_t* wb8 = reinterpret_cast<const uint8_t*>(wb);
+    // Rotated-BRIEF pattern: output byte `lane` uses the 32 coordinates kPattern[32 * lane ..], the same for every
+    // keypoint, so they stay in 8 registers as offset-128 bytes.  A coordinate becomes a float without the XU pipe and
+    // without a shared-memory read (the kernel is bound by LSU wavefronts): PRMT drops the byte into the mantissa of
+    // 1.5 * 2^23 and one FADD removes the bias, exactly.
+    unsigned pk[8];
+    {
+        const uint4* pp = reinterpret_cast<const uint4*>(kPattern + lane * 32);
+        const uint4 p0 = pp[0], p1 = pp[1];
+        pk[0] = p0.x ^ 0x80808080u; pk[1] = p0.y ^ 0x80808080u; pk[2] = p0.z ^ 0x80808080u; pk[3] = p0.w ^ 0x80808080u;
+        pk[4] = p1.x ^ 0x80808080u; pk[5] = p1.y ^ 0x80808080u; pk[6] = p1.z ^ 0x80808080u; pk[7] = p1.w ^ 0x80808080u;
+    }
     const int ra_row = lane / 9, ra_col = lane - ra_row * 9;      // staging roles (fixed per lane)
     const int rb_row = lane / 10, rb_col = lane - rb_row * 10;
 
@@ -224,14 +231,15 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
         float ca, sn;
         glibc_sincosf(__fmul_rn(angle, factorPI), sn, ca);
         const uint8_t* centre = wb8 + 18 * (WB_WORDS * 4) + 18 + ab;
-        const float* pat = s_pat + lane;
         unsigned val = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             int t[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-                const float px = pat[(4 * j + 2 * e) * 32], py = pat[(4 * j + 2 * e + 1) * 32];
+                const int c = 4 * j + 2 * e;                  // compile-time after unrolling
+                const float px = __fadd_rn(__uint_as_float(__byte_perm(pk[c >> 2], 0x4B400000u, 0x7650 + (c & 3))), -12583040.f);
+                const float py = __fadd_rn(__uint_as_float(__byte_perm(pk[c >> 2], 0x4B400000u, 0x7651 + (c & 3))), -12583040.f);
                 // cvRound == round-half-even; |value| <= 18.4, so adding 1.5 * 2^23 rounds exactly like cvtss2si
                 // and leaves the integer in the low mantissa bits (FADD + IADD instead of an XU-pipe F2I)
                 const float fy = __fadd_rn(__fadd_rn(__fmul_rn(px, sn), __fmul_rn(py, ca)), 12582912.f);
