@@ -83,27 +83,42 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
     const int s_last = min(yofs[dy1 - 1] + 1, sh - 1);
     const int nrows = s_last - s_first + 1;
     const uint8_t* gsrc = src + (size_t)s_first * spitch + (copier ? cb : 0);   // next source row to issue
+    // Loop invariants the compiler would otherwise rebuild every row (shared-window base via S2R, constant-bank
+    // reloads of the level geometry): pinned in registers.
+    unsigned cdst_r = cdst;
+    int sh1 = sh - 1, dpitch = L.pitch, sp = spitch;
+    asm volatile("" : "+r"(cdst_r), "+r"(sh1), "+r"(dpitch), "+r"(sp));
     int issued = 0;
 #pragma unroll
     for (int i = 0; i < RS_PF; ++i) {
-        if (issued < nrows && copier) rs_cp_async16(cdst + i * RS_ROWB, gsrc);
+        if (issued < nrows && copier) rs_cp_async16(cdst_r + i * RS_ROWB, gsrc);
         rs_commit();
-        gsrc += spitch;
+        gsrc += sp;
         ++issued;
     }
     unsigned H0[4] = {0, 0, 0, 0}, H1[4] = {0, 0, 0, 0};
-    uint8_t* dptr = dst + (size_t)dy0 * L.pitch + dx0;                    // next output row of this lane
-    const bool store = dx0 < L.w;
-    const int* yo = yofs + dy0;
-    const short* ywp = yw + 2 * dy0;
+    uint8_t* dptr = dst + (size_t)dy0 * dpitch + dx0;                     // next output row of this lane
+    int store = dx0 < L.w;
+    asm volatile("" : "+r"(store));
+    // vertical table of the band in registers: lane i holds (source row, weights) of output row dy0 + 32 * blk + i and
+    // hands them out by shuffle — no dependent global loads or 64-bit pointer arithmetic in the emit loop
+    int ty = 0;
+    unsigned tw = 0;
+    {
+        const int dy = min(dy0 + lane, dy1 - 1);
+        ty = yofs[dy];
+        tw = *reinterpret_cast<const unsigned*>(yw + 2 * dy);
+    }
     int left = dy1 - dy0;                                                 // output rows still to emit
-    int sy = s_first;                                                     // source row of the next output row
-    unsigned b0 = (unsigned)ywp[0] << 16, b1 = (unsigned)ywp[1] << 16;
+    int e = 0;                                                            // index of the next output row in the band
+    int sy = __shfl_sync(0xFFFFFFFFu, ty, 0);                             // source row of the next output row
+    unsigned wcur = __shfl_sync(0xFFFFFFFFu, tw, 0);
+    unsigned b0 = wcur << 16, b1 = wcur & 0xFFFF0000u;
     unsigned slot = 0;                                                    // ring byte offset of source row s
     for (int s = s_first; s <= s_last; ++s) {
-        if (issued < nrows && copier) rs_cp_async16(cdst + ((slot + RS_PF * RS_ROWB) & (RS_SLOTS * RS_ROWB - 1)), gsrc);
+        if (issued < nrows && copier) rs_cp_async16(cdst_r + ((slot + RS_PF * RS_ROWB) & (RS_SLOTS * RS_ROWB - 1)), gsrc);
         rs_commit();
-        gsrc += spitch;
+        gsrc += sp;
         ++issued;
         rs_wait<RS_PF>();
         __syncwarp();
@@ -117,26 +132,32 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
         H1[2] = __dp2a_lo(A[2], __byte_perm(wb0, wb1, sel[2]), 0u) >> 4;
         H1[3] = __dp2a_lo(A[3], __byte_perm(wb0, wb1, sel[3]), 0u) >> 4;
         // emit the output rows whose source pair is (s-1, s); on the last source row of the level also those clamped
-        // to (s, s) (their second weight is 0)
-        const bool last = s == sh - 1;
-        while (left > 0 && (sy == s - 1 || (last && sy == s))) {
+        // to (s, s) (their second weight is 0): rows come in ascending source order, so once sy == s the pair (s-1, s)
+        // is no longer needed and H0 simply becomes H1
+        const auto emit = [&]() {
             unsigned u[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const unsigned h0 = sy == s ? H1[j] : H0[j];
-                u[j] = (__umulhi(b0, h0) + __umulhi(b1, H1[j]) + 2u) * 64u;                   // byte 1 = (..) >> 2
-            }
+            for (int j = 0; j < 4; ++j) u[j] = (__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) * 64u;   // byte 1 = (..) >> 2
             const unsigned lo = __byte_perm(u[0], u[1], 0x0051), hi = __byte_perm(u[2], u[3], 0x0051);
             if (store) *reinterpret_cast<unsigned*>(dptr) = __byte_perm(lo, hi, 0x5410);
-            dptr += L.pitch;
+            dptr += dpitch;
             --left;
-            ++yo;
-            ywp += 2;
-            if (left > 0) {
-                sy = *yo;
-                b0 = (unsigned)ywp[0] << 16;
-                b1 = (unsigned)ywp[1] << 16;
+            ++e;
+            if ((e & 31) == 0 && left > 0) {                              // bands longer than a warp: next block of rows
+                const int dy = min(dy0 + e + lane, dy1 - 1);
+                ty = yofs[dy];
+                tw = *reinterpret_cast<const unsigned*>(yw + 2 * dy);
             }
+            sy = __shfl_sync(0xFFFFFFFFu, ty, e & 31);
+            wcur = __shfl_sync(0xFFFFFFFFu, tw, e & 31);
+            b0 = wcur << 16;
+            b1 = wcur & 0xFFFF0000u;
+        };
+        while (left > 0 && sy == s - 1) emit();
+        if (s == sh1) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) H0[j] = H1[j];
+            while (left > 0 && sy == s) emit();
         }
     }
 }
