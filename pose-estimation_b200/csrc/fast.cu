@@ -398,8 +398,11 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
     int ci = (band * band_rows) / L.h_cell;
     int cy = band * band_rows - ci * L.h_cell;
     unsigned meta = (unsigned)(x - B2_BORDER) | ((unsigned)(ya - B2_BORDER) << 12) | ((unsigned)ci << 24);
-    const int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
+    int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
     int since_flush = 0;
+    // loop invariants the compiler would otherwise rebuild from the constant bank / special registers every row
+    unsigned thr2_r = thr2, kini_r = kini, queue_s = (unsigned)__cvta_generic_to_shared(queue);
+    asm volatile("" : "+r"(hcell1), "+r"(ylast), "+r"(thr2_r), "+r"(kini_r), "+r"(queue_s));
 
 #define B2_FW_FLAGS()                                                                                          \
     {                                                                                                           \
@@ -464,14 +467,16 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
             if (r >= 8) {
                 const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;
                 const unsigned dn = (cy != hcell1 && y != ylast) ? 0xFFFFFFFFu : 0u;
-                const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));
-                const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));
+                const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2_r));
+                const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2_r));
                 const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;
                 const unsigned m4 = __byte_perm(oE, oO, 0x6240);
-                accE |= oE + kini; accO |= oO + kini;
+                accE |= oE + kini_r; accO |= oO + kini_r;
                 const bool has = store_lane && m4 != 0;
                 const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);
-                if (has) queue[qn + __popc(bal & lt_mask)] = make_uint2(m4, meta);
+                if (has)
+                    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(queue_s + 8u * (unsigned)(qn + __popc(bal & lt_mask))),
+                                 "r"(m4), "r"(meta) : "memory");
                 qn += __popc(bal);
                 ++y;
                 meta += 0x1000u;
