@@ -159,7 +159,11 @@ typedef struct b2orb_stereo_out {
  * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 64 pairs are processed as a pipeline
  * of chunks on internal streams so that the H2D copy, the kernels and the D2H copy of different chunks overlap;
  * results do not depend on the chunking.  Environment: B2ORB_PIPE_CHUNK (pairs per chunk, 0 = off, read at
- * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3). */
+ * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3).
+ * Calls of up to 4 pairs whose output arrays are all pinned host memory (b2orb_host_alloc, cudaHostAlloc,
+ * cudaHostRegister) return their results through one kernel that writes entries [0, n) of every array directly
+ * into the caller's buffers; otherwise whole arrays are copied back.  Either way only entries [0, n) are defined.
+ * B2ORB_EXPORT=0 forces the copy path. */
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
                           int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
 
