@@ -93,6 +93,33 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def bind_near_gpu(gpu_index):
+    """Multi-GPU runs: keep this rank's threads — and with them its pinned host buffers, which Linux places on the
+    node of the allocating thread — on the CPUs next to its GPU, so the H2D / D2H DMA of the e2e leg does not cross the
+    socket interconnect.  Returns the previous affinity (restored before the CPU baseline) or None."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(gpu_index)
+        try:
+            bus = "%08X:%02X:%02X.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            hnd = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            hnd = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        ncpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(hnd, (ncpu + 63) // 64)
+        cpus = [i for i in range(ncpu) if (mask[i // 64] >> (i % 64)) & 1]
+        prev = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in prev]
+        if cpus and len(cpus) < len(prev):
+            os.sched_setaffinity(0, cpus)
+            return prev, len(cpus)
+    except Exception:
+        pass
+    return None, 0
+
+
 def cpu_baseline(synth, orc, shape, cfg, temporal, workers, target_s):
     """Oracle on host cores, bounded sample sized from a 1-round probe (about `target_s` seconds)."""
     probe_n = max(workers, 2)
@@ -127,6 +154,7 @@ def main():
     ap.add_argument("--triangulate", action="store_true",
                     help="next row f4: cv::triangulatePoints + depth gate of the kept matches in the same device pass")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
+    ap.add_argument("--bind", action="store_true", help="pin the process to the CPUs local to its GPU also at N=1")
     ap.add_argument("--latency-calls", type=int, default=200, help="single-pair calls of the latency leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")
     args = ap.parse_args()
@@ -174,6 +202,9 @@ def main():
     import torch
     fe = importlib.import_module("pose-estimation_b200.frontend")
     torch.cuda.set_device(local)
+    prev_aff, near_cpus = bind_near_gpu(local) if (world > 1 or args.bind) else (None, 0)
+    if near_cpus:
+        config["host_affinity"] = f"rank threads + pinned buffers on the {near_cpus} CPUs local to the GPU"
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -392,6 +423,8 @@ def main():
                      "frac_of_hbm_peak": b_pair * value / world / 1e9 / peak},
         "results": {"keypoints_left": int(summ[0]), "stereo_matches": int(summ[1]), "circular_matches": int(summ[2])},
     }
+    if prev_aff is not None:
+        os.sched_setaffinity(0, prev_aff)
     if not args.no_cpu_baseline and world >= 1:
         from oracle import oracle as orc
         workers = os.cpu_count() or 1
