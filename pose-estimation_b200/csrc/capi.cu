@@ -23,7 +23,7 @@ namespace {
 // programmatic dependent launch for latency-sized batches only (b2orb_internal.cuh)
 constexpr int B2_PDL_MAX_IMAGES = 8;
 inline bool pdl_for(int nimg) {
-    static const int forced = [] { const char* e = getenv("B2ORB_PDL"); return e ? (atoi(e) ? 1 : 0) : -1; }();
+    const int forced = [] { const char* e = getenv("B2ORB_PDL"); return e ? (atoi(e) ? 1 : 0) : -1; }();
     return forced >= 0 ? forced != 0 : nimg <= B2_PDL_MAX_IMAGES;
 }
 
@@ -465,7 +465,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     // single-pair latency did not move (per-task table loads + cp.async prologue are the floor of every level).  A third
     // variant (one CTA per row band of the image across all levels, thread per output word, 7 __syncthreads instead of
     // 7 launches) measured 35 us and was dropped: with programmatic dependent launch the 7 launches cost ~18 us.
-    static const int chain_max = [] { const char* e = getenv("B2ORB_CHAIN"); return e ? atoi(e) : 0; }();
+    const int chain_max = [] { const char* e = getenv("B2ORB_CHAIN"); return e ? atoi(e) : 0; }();
     bool chained = false;
     if (nimg <= chain_max && g.nlevels > 1) {
         prof_mark(h, B2ORB_K_RESIZE);
@@ -479,7 +479,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     }
     prof_mark(h, -1);
     // B2ORB_FORK=<max images>: blur on the side stream for latency-sized calls (not while profiling per kernel)
-    static const int fork_max = [] { const char* e = getenv("B2ORB_FORK"); return e ? atoi(e) : 8; }();
+    const int fork_max = [] { const char* e = getenv("B2ORB_FORK"); return e ? atoi(e) : 8; }();
     const bool fork = nimg <= fork_max && !h->profiling && h->s_aux;
     if (fork) {
         B2_CUDA(h, cudaEventRecord(h->ev_fork, s));
@@ -723,7 +723,7 @@ bool export_plan(b2orb_handle* h, int np, const b2orb_stereo_out* o, B2ExportPla
 // Results of `np` pairs to the caller and wait: direct export for latency-sized calls with pinned outputs, else the
 // copy path (b2orb_stereo_download).
 int finish_outputs(b2orb_handle* h, int np, const b2orb_stereo_out* o) {
-    static const int export_max = [] { const char* e = getenv("B2ORB_EXPORT"); return e ? atoi(e) : 4; }();
+    const int export_max = [] { const char* e = getenv("B2ORB_EXPORT"); return e ? atoi(e) : 4; }();
     if (o && np <= export_max && o->cap >= h->geom.kp_cap) {
         static_assert(sizeof(B2ExportPlan) < 3500, "plan must fit the kernel parameter space");
         const bool same = h->exp_np == np && memcmp(&h->exp_out, o, sizeof(*o)) == 0;

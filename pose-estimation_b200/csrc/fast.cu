@@ -502,11 +502,14 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
 constexpr int FV_THREADS = 256;
 constexpr int FV_MAX_CHUNKS = 32;  // CTAs per (image, level): 4 for large batches, more when few images are in flight
 
+constexpr int FV_Q = 256;          // per-warp staging queue (entries); one iteration adds at most 96
+
 __global__ void __launch_bounds__(FV_THREADS)
 fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw_list, const int* __restrict__ raw_cnt,
                  const uint8_t* __restrict__ cell_ini, uint32_t* __restrict__ cand, int* __restrict__ cand_cnt,
                  int chunks) {
     b2_pdl_wait();
+    __shared__ uint32_t s_q[FV_THREADS / 32][FV_Q];
     const int level = blockIdx.x / chunks, chunk = blockIdx.x - level * chunks, b = blockIdx.y;
     const B2Level& L = g.lv[level];
     const int n = min(raw_cnt[b * g.nlevels + level], L.cand_cap);
@@ -518,38 +521,69 @@ fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw
     uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
     int* out_cnt = cand_cnt + b * g.nlevels + level;
     const int lane = threadIdx.x & 31;
+    uint32_t* q = s_q[threadIdx.x >> 5];
     const unsigned lt_mask = (1u << lane) - 1;
     const unsigned ini = (unsigned)g.ini_th;
+    const int wc = L.w_cell, cap = L.cand_cap;
     // cell column by multiplication: exact for n < 2^20 / w_cell (n < 4096, w_cell < 60)
-    const unsigned magic = ((1u << 20) + (unsigned)L.w_cell - 1u) / (unsigned)L.w_cell;
+    const unsigned magic = ((1u << 20) + (unsigned)wc - 1u) / (unsigned)wc;
+    int qn = 0;                                                 // queue fill, warp-uniform
+    const auto flush = [&]() {
+        __syncwarp();
+        if (qn) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(out_cnt, qn);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            for (int i = lane; i < qn; i += 32)
+                if (base + i < cap) out[base + i] = q[i];
+            __syncwarp();
+            qn = 0;
+        }
+    };
+    uint2 nxt = make_uint2(0u, 0u);
+    if (lo + (int)threadIdx.x < hi) nxt = raw[lo + threadIdx.x];
     for (int i0 = lo; i0 < lo + per; i0 += FV_THREADS) {       // whole warps iterate together (ballots below)
-        const int i = i0 + (int)threadIdx.x;
-        uint2 e = make_uint2(0u, 0u);
-        if (i < hi) e = raw[i];
+        const uint2 e = nxt;
+        const int in = i0 + FV_THREADS + (int)threadIdx.x;      // next word in flight while this one is voted on
+        nxt = make_uint2(0u, 0u);
+        if (in < hi) nxt = raw[in];
         // NMS leaves at most three corners in a word of 4 horizontally adjacent pixels (neighbours in different
-        // cells do not suppress each other, so two may be adjacent across a cell boundary)
+        // cells do not suppress each other, so two may be adjacent across a cell boundary).  The word spans at most two
+        // cells (w_cell >= 30): pixels [0, jb) lie in cell column colA, the rest in colA + 1.
         uint32_t keep[3];
         int nk = 0;
-        unsigned m4 = e.x;
-        const unsigned rowbase = (e.y >> 24) * (unsigned)L.n_cols;
-        while (m4) {
-            const int j = (__ffs(m4) - 1) >> 3;
-            const unsigned bv = (m4 >> (8 * j)) & 0xFFu;
-            m4 &= ~(0xFFu << (8 * j));
-            const unsigned X = (e.y & 0xFFFu) + j;              // relative to the 16-px border
-            const bool k = bv > ini || flags[rowbase + (((X - (B2_EDGE - B2_BORDER)) * magic) >> 20)] == 0;
-            if (k && nk < 3) keep[nk++] = X | (e.y & 0x00FFF000u) | ((bv - 1u) << 24);
+        const unsigned m4 = e.x;
+        if (m4) {
+            const unsigned xb = e.y & 0xFFFu;                   // relative to the 16-px border
+            const unsigned rowbase = (e.y >> 24) * (unsigned)L.n_cols;
+            // (the first word of a row starts left of the first cell: its leading pixels are always 0)
+            const unsigned colA = ((max(xb, (unsigned)(B2_EDGE - B2_BORDER)) - (B2_EDGE - B2_BORDER)) * magic) >> 20;
+            const int jb = (int)((colA + 1u) * (unsigned)wc + (B2_EDGE - B2_BORDER)) - (int)xb;
+            // a flag is only needed for corners that pass minThFAST but not iniThFAST
+            const unsigned le = __vcmpleu4(m4, ini * 0x01010101u) & __vcmpne4(m4, 0u);
+            unsigned fA = 1, fB = 1;                            // "iniThFAST found something in the cell"
+            if (le) {
+                fA = flags[rowbase + colA];
+                if (jb < 4) fB = flags[rowbase + colA + 1];
+            }
+            const unsigned ypart = e.y & 0x00FFF000u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const unsigned bv = (m4 >> (8 * j)) & 0xFFu;
+                const unsigned f = j < jb ? fA : fB;
+                if (bv != 0 && (bv > ini || f == 0) && nk < 3) keep[nk++] = (xb + j) | ypart | ((bv - 1u) << 24);
+            }
         }
         const unsigned b0 = __ballot_sync(0xFFFFFFFFu, nk & 1), b1 = __ballot_sync(0xFFFFFFFFu, nk & 2);
         const int total = __popc(b0) + 2 * __popc(b1);
-        if (total == 0) continue;
-        int base = 0;
-        if (lane == 0) base = atomicAdd(out_cnt, total);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        int pos = base + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask);
-        for (int k = 0; k < nk; ++k, ++pos)
-            if (pos < L.cand_cap) out[pos] = keep[k];
+        int pos = qn + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask);
+        if (nk > 0) q[pos] = keep[0];
+        if (nk > 1) q[pos + 1] = keep[1];
+        if (nk > 2) q[pos + 2] = keep[2];
+        qn += total;
+        if (qn > FV_Q - 96) flush();
     }
+    flush();
 }
 
 }  // namespace
@@ -557,7 +591,7 @@ fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw
 void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
                           cudaStream_t s) {
     if (g.total_fast_tasks[0] <= 0) return;
-    static const int forced = [] { const char* e = getenv("B2ORB_FAST_BAND"); return e ? atoi(e) : -1; }();   // A/B runs
+    const int forced = [] { const char* e = getenv("B2ORB_FAST_BAND"); return e ? atoi(e) : -1; }();   // A/B runs
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
     // and short ones while a 32-row launch would not even give every SM two CTAs (per-CTA latency is what counts then)
     int variant = (long long)g.total_fast_tasks[2] * nimg >= 148LL * 16 * 4 ? 2
@@ -567,8 +601,8 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* 
     // Default: shared-memory window kernel, first-layer (min, max) pairs on the FMA pipe.  A/B switches:
     // B2ORB_FAST=regs -> the register-window kernel (all min/max on the ALU pipe); B2ORB_FAST_FMA=<NQ><NE> -> how many
     // first-layer / arc-end pairs of the window kernel use the FMA pipe (0, 80, 88).
-    static const int mix = [] { const char* e = getenv("B2ORB_FAST_FMA"); return e ? atoi(e) : 80; }();
-    static const bool regs = [] { const char* e = getenv("B2ORB_FAST"); return e && e[0] == 'r'; }();
+    const int mix = [] { const char* e = getenv("B2ORB_FAST_FMA"); return e ? atoi(e) : 80; }();
+    const bool regs = [] { const char* e = getenv("B2ORB_FAST"); return e && e[0] == 'r'; }();
     const dim3 block(FS_WARPS * 32);
     if (regs)
         b2_launch_pdl(fast_score_kernel<0, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);

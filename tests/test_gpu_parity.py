@@ -87,6 +87,31 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth, monkeypatch):
     hd.close()
 
 
+@pytest.mark.parametrize("env", [{"B2ORB_FAST_BAND": "0"}, {"B2ORB_FAST_BAND": "1"}, {"B2ORB_FAST_BAND": "2"},
+                                 {"B2ORB_FAST": "regs"}, {"B2ORB_FAST_FMA": "0"}, {"B2ORB_FAST_FMA": "88"},
+                                 {"B2ORB_CHAIN": "8"}, {"B2ORB_FORK": "0"}, {"B2ORB_PDL": "0"}],
+                         ids=lambda e: ",".join(f"{k[6:]}={v}" for k, v in e.items()))
+def test_kernel_variants_agree_with_oracle(env, fe, oracle, synth, monkeypatch):
+    """Every launch-time choice the library makes by batch size (FAST band length, side-stream blur, programmatic
+    launch chain) and every A/B kernel kept in the tree (register-window FAST, FMA-pipe mixes, cluster resize chain)
+    must give the oracle's bits: forced one at a time on a low-texture image (both FAST thresholds in play)."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    w, h = 400, 300
+    ls, rs = synth.sequence((w, h), 2, seed=21, passes=8)
+    hd = fe.Handle(500, 1.2, 8, 20, 7, w, h, max_images=4)
+    ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
+    out = hd.stereo_frontend(ls, rs, temporal=True)
+    for p in range(2):
+        for img, kk, dk, nk in ((ls[p], "kp_l", "desc_l", "n_l"), (rs[p], "kp_r", "desc_r", "n_r")):
+            k, d = ex(img)
+            n = int(out[nk][p])
+            assert n == len(k) and n > 100
+            assert out[kk][p, :n].tobytes() == k.tobytes()
+            assert np.array_equal(out[dk][p, :n], d)
+    hd.close()
+
+
 @pytest.mark.parametrize("nfeat", [8000, 12000])
 def test_stress_4k_pair_matches_oracle(nfeat, fe, oracle, synth):
     """BASELINE config 5: 3840x2160 stereo, 8000 features per eye, 8k x 8k brute-force Hamming per pair — the largest
