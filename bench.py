@@ -153,7 +153,7 @@ def main():
                     help="next row f1: inputs are raw camera frames, cv::remap runs on the device in front of the pyramid")
     ap.add_argument("--triangulate", action="store_true",
                     help="next row f4: cv::triangulatePoints + depth gate of the kept matches in the same device pass")
-    ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (one handle each) driving the e2e leg")
+    ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (one handle each) driving the e2e leg")
     ap.add_argument("--bind", action="store_true", help="pin the process to the CPUs local to its GPU also at N=1")
     ap.add_argument("--latency-calls", type=int, default=200, help="single-pair calls of the latency leg")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: device-resident leg alone (line has e2e null)")

@@ -50,7 +50,7 @@ struct B2Level {
     int w_cell, h_cell;
     int cell_base;            // first flattened cell index of this level
     int fast_task_base[B2_FAST_VARIANTS];    // first flattened FAST score task (band, strip) of this level, per band variant
-    int fast_strips;          // 112-px strips per row band (fast.cu)
+    int fast_strips;          // 120-px strips per row band (fast.cu)
     int blur_task_base;       // first flattened blur task (band, strip) of this level
     int blur_strips;          // 128-px strips per row band
     int quota;                // mnFeaturesPerLevel[level]

@@ -302,7 +302,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
             if (L.w_cell > 64 || L.h_cell > 64) return "FAST cell larger than 64 px";
             if ((long long)n_cols * n_rows * L.w_cell * L.h_cell >= (1 << 24)) return "level too large for 24-bit order keys";
             cells += n_cols * n_rows;
-            L.fast_strips = (L.w - 2 * B2_BORDER + 111) / 112;
+            L.fast_strips = (L.w - 2 * B2_BORDER + 119) / 120;
             for (int v = 0; v < B2_FAST_VARIANTS; ++v)
                 ftasks[v] += L.fast_strips * ((L.h - 2 * B2_EDGE + (B2_FAST_BAND << v) - 1) / (B2_FAST_BAND << v));
             // DistributeOctTree :543-545

@@ -12,7 +12,7 @@
 //
 // Organised around instructions per pixel (the stage is ALU-pipe bound, not HBM bound):
 //
-// fast_score_kernel — one WARP owns a 112-px strip (lanes 2..29 produce 4 px each, lanes 0/1/30/31 only feed
+// fast_score_kernel — one WARP owns a 120-px strip (lanes 1..30 produce 4 px each; lanes 0 and 31 only feed
 //   the halo of the score and of the fused NMS) and marches down a band of rows.  Per image row a lane loads one 32-bit word, splits it into two
 //   u16x2 "pixel pairs" (x,x+2) and (x+1,x+3) and gets the six neighbouring pairs by shuffle, so the 16 ring
 //   pixels of TWO output pixels are always one register each; the last 7 rows of pairs live in registers
@@ -40,7 +40,7 @@ namespace {
 constexpr int FS_WARPS = 4;
 constexpr int FS_PF = 5;        // rows in flight per warp (ring of 7 slots, slot = row % 7 = unroll phase)
 constexpr int FS_FLUSH = 7;     // output rows between queue flushes (one pass of the 7-phase unrolled loop)
-constexpr int FS_QUEUE = 28 * FS_FLUSH;   // at most one non-zero word per storing lane and row
+constexpr int FS_QUEUE = 30 * FS_FLUSH;   // at most one non-zero word per storing lane and row
 
 __device__ __forceinline__ unsigned vmin2(unsigned a, unsigned b) { return __vminu2(a, b); }
 __device__ __forceinline__ unsigned vmax2(unsigned a, unsigned b) { return __vmaxu2(a, b); }
@@ -142,7 +142,7 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
     int* out_cnt = raw_cnt + b * g.nlevels + level;
     uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
     const int w = L.w, h = L.h;
-    const int x = B2_BORDER - 8 + strip * 112 + lane * 4;      // lanes 2..29 own columns x .. x+3
+    const int x = B2_BORDER - 4 + strip * 120 + lane * 4;      // lanes 1..30 own columns x .. x+3
     const int ya = B2_EDGE + band * band_rows;                 // M rows [ya, yb)
     const int yb = min(ya + band_rows, h - B2_EDGE);
     const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
@@ -172,7 +172,7 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
     const unsigned lt_mask = (1u << lane) - 1;
     unsigned accE = 0, accO = 0;
     const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
-    const bool store_lane = lane >= 2 && lane <= 29 && x < w - B2_BORDER;   // b valid on lanes 1..30, NMS on 2..29
+    const bool store_lane = lane >= 1 && lane <= 30 && x < w - B2_BORDER;   // b valid on lanes 1..30 + the facing pixels of 0 and 31
 
     unsigned P[7][8];            // pairs (p[a], p[a+2]) for a = x-3 .. x+4, last 7 rows
     // Rows are addressed by a 32-bit offset that is clamped to the last row of the band, so the prefetch needs no
@@ -196,9 +196,10 @@ fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __
         const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);                      \
         const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);    \
         const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                      \
-        P[p][0] = __shfl_up_sync(0xFFFFFFFFu, O1, 1);                                                           \
-        P[p][1] = __shfl_up_sync(0xFFFFFFFFu, c2, 1);                                                           \
-        P[p][2] = __shfl_up_sync(0xFFFFFFFFu, c3, 1);                                                           \
+        const unsigned Ep = __shfl_up_sync(0xFFFFFFFFu, E1, 1), Op = __shfl_up_sync(0xFFFFFFFFu, O1, 1);        \
+        P[p][0] = Op;                                           /* (x-3, x-1) */                                \
+        P[p][1] = __byte_perm(Ep, E1, 0x5432);                  /* (x-2, x): high half is this lane's own pixel */ \
+        P[p][2] = __byte_perm(Op, O1, 0x5432);                  /* (x-1, x+1) */                                \
         P[p][3] = E1; P[p][4] = O1; P[p][5] = c2; P[p][6] = c3; P[p][7] = E2;                                   \
     }
     // prologue: pixel rows 0..5 only fill the window
@@ -351,7 +352,7 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
     int* out_cnt = raw_cnt + b * g.nlevels + level;
     uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
     const int w = L.w, h = L.h;
-    const int x = B2_BORDER - 8 + strip * 112 + lane * 4;      // lanes 2..29 own columns x .. x+3
+    const int x = B2_BORDER - 4 + strip * 120 + lane * 4;      // lanes 1..30 own columns x .. x+3
     const int ya = B2_EDGE + band * band_rows;                 // output rows [ya, yb)
     const int yb = min(ya + band_rows, h - B2_EDGE);
     const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
@@ -378,7 +379,7 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
     const unsigned lt_mask = (1u << lane) - 1;
     unsigned accE = 0, accO = 0;
     const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
-    const bool store_lane = lane >= 2 && lane <= 29 && x < w - B2_BORDER;
+    const bool store_lane = lane >= 1 && lane <= 30 && x < w - B2_BORDER;
 
     const uint8_t* col0 = img + xo + (size_t)(ya - 4) * pitch;
     const unsigned offmax = (unsigned)(nsteps - 1) * (unsigned)pitch;
@@ -433,9 +434,9 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
         const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);
         const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);
         const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);
-        const unsigned n0 = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
-        const unsigned n1 = __shfl_up_sync(0xFFFFFFFFu, c2, 1);
-        const unsigned n2 = __shfl_up_sync(0xFFFFFFFFu, c3, 1);
+        const unsigned Ep = __shfl_up_sync(0xFFFFFFFFu, E1, 1), n0 = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
+        const unsigned n1 = __byte_perm(Ep, E1, 0x5432);       // (x-2, x): the high half is this lane's own pixel,
+        const unsigned n2 = __byte_perm(n0, O1, 0x5432);       // (x-1, x+1)   so lane 0's last pixel gets a valid score
         // new row's pairs: n0, n1, n2, E1, O1, c2, c3, E2  (P[0..7] of the register version)
         if (r >= 6) {
             // unit Q = pairs (2, 5, 3, 4), unit W = pairs (1, 6, 0, 7): every load asks for exactly what it uses
