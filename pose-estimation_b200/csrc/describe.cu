@@ -86,7 +86,14 @@ __device__ __forceinline__ void glibc_sincosf(float y, float& sn, float& cs) {
 }
 
 constexpr int DS_WARPS = 8;
+#ifndef DS_MINB
+#define DS_MINB 3
+#endif
 constexpr int IC_WORDS = 4 * 16 * 9 * 2;   // [alignment][|v|][word][wu, wm]
+
+__device__ __forceinline__ void ds_cp_async4(unsigned smem_addr, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr), "l"(gmem) : "memory");
+}
 
 __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned bytes x signed bytes
     int d;
@@ -102,14 +109,14 @@ constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..c
 // The descriptor's 512 single-byte gathers and the orientation's 31 short rows are L1-wavefront bound when done
 // straight from global memory (ncu: lg/mio throttle), so each warp first copies the two windows of its keypoint into
 // shared memory with coalesced 32-bit loads and gathers from there.
-__global__ void __launch_bounds__(DS_WARPS * 32, 2)
+__global__ void __launch_bounds__(DS_WARPS * 32, DS_MINB)
 describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
                 const int* __restrict__ sel_cnt, const unsigned* __restrict__ ic_table, KeyPointOut* __restrict__ kps,
                 uint8_t* __restrict__ desc, int* __restrict__ n_out) {
     b2_pdl_wait();
     __shared__ unsigned s_ic[IC_WORDS];
-    __shared__ unsigned s_wa[DS_WARPS][WA_ROWS * WA_WORDS];
-    __shared__ unsigned s_wb[DS_WARPS][WB_ROWS * WB_WORDS + 2];
+    __shared__ unsigned s_wa[DS_WARPS][2][WA_ROWS * WA_WORDS];      // double-buffered: keypoint k+1 lands while k is worked on
+    __shared__ unsigned s_wb[DS_WARPS][2][WB_ROWS * WB_WORDS + 2];
     for (int i = threadIdx.x; i < IC_WORDS; i += DS_WARPS * 32) s_ic[i] = ic_table[i];
     __syncthreads();
     const int b = blockIdx.y;
@@ -125,9 +132,8 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     }
     const int total = __shfl_sync(0xFFFFFFFFu, pre, 15);   // nlevels <= 12: lane 15 holds the sum
     if (blockIdx.x == 0 && threadIdx.x == 0) n_out[b] = min(total, g.kp_cap);
-    unsigned* wa = s_wa[wid];
-    unsigned* wb = s_wb[wid];
-    const uint8_t* wb8 = reinterpret_cast<const uint8_t*>(wb);
+    const unsigned wa_s = (unsigned)__cvta_generic_to_shared(&s_wa[wid][0][lane]);   // lane's staging slot, buffer 0
+    const unsigned wb_s = (unsigned)__cvta_generic_to_shared(&s_wb[wid][0][lane]);
     // Rotated-BRIEF pattern: output byte `lane` uses the 32 coordinates kPattern[32 * lane ..], the same for every
     // keypoint, so they stay in 8 registers as offset-128 bytes.  A coordinate becomes a float without the XU pipe and
     // without a shared-memory read (the kernel is bound by LSU wavefronts): PRMT drops the byte into the mantissa of
@@ -142,16 +148,16 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     const int ra_row = lane / 9, ra_col = lane - ra_row * 9;      // staging roles (fixed per lane)
     const int rb_row = lane / 10, rb_col = lane - rb_row * 10;
 
-    // Software pipeline over the warp's keypoints: the window loads of keypoint k+1 are issued right after the
-    // windows of keypoint k went to shared memory, so their latency hides behind k's orientation + descriptor math.
+    // Software pipeline over the warp's keypoints: the windows of keypoint k+1 are copied global -> shared with 4-byte
+    // cp.async into the other buffer while k's orientation + descriptor math runs (no staging registers, no STS).
     struct Kp { int slot, level, cx, cy; float response; bool valid; };
-    unsigned ra[11], rb[13];
     const auto fetch = [&](int it) {
+        const unsigned bufa = (it & 1) * (unsigned)sizeof(s_wa[0][0]), bufb = (it & 1) * (unsigned)sizeof(s_wb[0][0]);
         Kp k;
         k.slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;      // output slot in this image
         k.valid = it < DS_KPW && k.slot < total && k.slot < g.kp_cap;
         k.level = 0; k.cx = k.cy = 0; k.response = 0.f;
-        if (!k.valid) return k;
+        if (!k.valid) { asm volatile("cp.async.commit_group;" ::: "memory"); return k; }
         // level = number of levels whose inclusive prefix is <= slot
         k.level = __popc(__ballot_sync(0xFFFFFFFFu, lane < g.nlevels && pre <= k.slot));
         const int base = k.level ? __shfl_sync(0xFFFFFFFFu, pre, k.level - 1) : 0;
@@ -170,18 +176,20 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
         const int bx = (k.cx - 18) & ~3;
         const uint8_t* pa = img + (size_t)(k.cy - B2_HALF_PATCH + ra_row) * pitch + ax + 4 * ra_col;
         const bool oka = lane < 27 && (ra_col < 8 || a >= 2);
+        // (words that are skipped keep stale but finite bytes; their IC_Angle weights are zero)
 #pragma unroll
         for (int i = 0; i < 11; ++i) {
-            ra[i] = (oka && 3 * i + ra_row < WA_ROWS) ? *reinterpret_cast<const unsigned*>(pa) : 0u;
+            if (oka && 3 * i + ra_row < WA_ROWS) ds_cp_async4(wa_s + bufa + i * (27 * 4), pa);
             pa += 3 * pitch;
         }
         const uint8_t* pb = bl + (size_t)(k.cy - 18 + rb_row) * bp + bx + 4 * rb_col;
         const bool okb = lane < 30;
 #pragma unroll
         for (int i = 0; i < 13; ++i) {
-            rb[i] = (okb && 3 * i + rb_row < WB_ROWS) ? *reinterpret_cast<const unsigned*>(pb) : 0u;
+            if (okb && 3 * i + rb_row < WB_ROWS) ds_cp_async4(wb_s + bufb + i * (30 * 4), pb);
             pb += 3 * bp;
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         return k;
     };
 
@@ -193,15 +201,12 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
         const float response = cur.response;
         const B2Level& L = g.lv[level];
         const int a = (cx - B2_HALF_PATCH) & 3, ab = (cx - 18) & 3;
-        __syncwarp();                                   // previous keypoint's gathers are done
-#pragma unroll
-        for (int k = 0; k < 11; ++k)
-            if (lane < 27 && 3 * k + ra_row < WA_ROWS) wa[(3 * k + ra_row) * WA_WORDS + ra_col] = ra[k];
-#pragma unroll
-        for (int k = 0; k < 13; ++k)
-            if (lane < 30 && 3 * k + rb_row < WB_ROWS) wb[(3 * k + rb_row) * WB_WORDS + rb_col] = rb[k];
-        __syncwarp();
-        nxt = fetch(it + 1);                            // loads in flight during the math below
+        asm volatile("cp.async.wait_group 0;" ::: "memory");   // this keypoint's windows have landed (this lane's words)
+        __syncwarp();                                   // ... every lane's; and the previous keypoint's gathers are done
+        nxt = fetch(it + 1);                            // copies in flight during the math below
+        const unsigned* wa = s_wa[wid][it & 1];
+        const unsigned* wb = s_wb[wid][it & 1];
+        const uint8_t* wb8 = reinterpret_cast<const uint8_t*>(wb);
 
         // ---- IC_Angle (src/ORBextractor.cc:77-104): lane = patch row v = lane-15, IDP.4A against per-(alignment, |v|)
         // weights: wu = u inside the disc |u| <= umax[|v|] (-> m10), wm = 1 inside the disc (-> row sum -> m01)
