@@ -316,6 +316,38 @@ def test_direct_export_to_pinned_outputs_equals_copy_path(npairs, fe, synth):
     a_hd.close(); b_hd.close()
 
 
+def test_bench_sized_batch_matches_oracle_and_single_calls(fe, oracle, synth):
+    """The throughput configuration itself: 136 pairs in ONE call (default pipeline: chunks of 64 + 64 + 8 over the
+    internal lanes, 64-row FAST bands, no programmatic launch chain, copy-path outputs).  Every 9th pair is checked
+    against the oracle, and the whole batch against the same pairs sent one call at a time (16-row bands, PDL,
+    side-stream blur): batching must not change a bit."""
+    w, h, nf, ini, mn = synth.SHAPES["cfsd"]
+    n = 136
+    ls, rs = synth.sequence("cfsd", n, seed=77)
+    big = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * n)
+    one = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    a = big.stereo_frontend(ls, rs, temporal=True)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
+    for p in range(0, n, 9):
+        kl, dl = ex(ls[p]); kr, dr = ex(rs[p])
+        nl, nr = int(a["n_l"][p]), int(a["n_r"][p])
+        assert nl == len(kl) and nr == len(kr)
+        assert a["kp_l"][p, :nl].tobytes() == kl.tobytes() and a["kp_r"][p, :nr].tobytes() == kr.tobytes()
+        assert np.array_equal(a["desc_l"][p, :nl], dl) and np.array_equal(a["desc_r"][p, :nr], dr)
+        ti, di = oracle.bf_match(dl, dr)
+        assert np.array_equal(a["train_idx"][p, :nl], ti) and np.array_equal(a["dist"][p, :nl], di)
+    for p in range(n):
+        b = one.stereo_frontend(ls[p], rs[p], temporal=True)
+        for key, cnt in (("kp_l", "n_l"), ("desc_l", "n_l"), ("kp_r", "n_r"), ("desc_r", "n_r"), ("train_idx", "n_l"),
+                         ("dist", "n_l"), ("match_l", "n_match"), ("match_r", "n_match"), ("circ_cur", "n_circ"),
+                         ("circ_hist", "n_circ")):
+            m = int(a[cnt][p])
+            assert m == int(b[cnt][0]), f"pair {p}: {cnt}"
+            assert np.array_equal(a[key][p, :m], b[key][0, :m]), f"pair {p}: {key}"
+    assert a["n_circ"][1:].min() > 5
+    big.close(); one.close()
+
+
 def test_temporal_track_entry_point(fe, oracle):
     rng = np.random.default_rng(5)
     hist_l = rng.integers(0, 256, (300, 32), dtype=np.uint8); hist_r = rng.integers(0, 256, (300, 32), dtype=np.uint8)
