@@ -570,11 +570,13 @@ fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw
                 if (jb < 4) fB = flags[rowbase + colA + 1];
             }
             const unsigned ypart = e.y & 0x00FFF000u;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            unsigned m = m4;                                    // usually a single corner per word: visit set bytes only
+            while (m) {
+                const int j = (__ffs(m) - 1) >> 3;
                 const unsigned bv = (m4 >> (8 * j)) & 0xFFu;
+                m &= ~(0xFFu << (8 * j));
                 const unsigned f = j < jb ? fA : fB;
-                if (bv != 0 && (bv > ini || f == 0) && nk < 3) keep[nk++] = (xb + j) | ypart | ((bv - 1u) << 24);
+                if ((bv > ini || f == 0) && nk < 3) keep[nk++] = (xb + j) | ypart | ((bv - 1u) << 24);
             }
         }
         const unsigned b0 = __ballot_sync(0xFFFFFFFFu, nk & 1), b1 = __ballot_sync(0xFFFFFFFFu, nk & 2);
