@@ -59,10 +59,8 @@ struct b2orb_handle {
     std::string err;
     uint64_t launches = 0;
     float last_ms = 0.f;
-    // direct export (latency path): last b2orb_stereo_out whose pointers were verified to be device-visible pinned memory
-    b2orb_stereo_out exp_out = {};
+    // direct export (latency path): segment table of the current call
     B2ExportPlan exp_plan;
-    int exp_np = 0;
     bool exp_ok = false;
 
     // ctor tables
@@ -186,7 +184,6 @@ bool dev_alloc(b2orb_handle* h, T** p, size_t count) {
 }
 
 void free_workspace(b2orb_handle* h) {
-    h->exp_np = 0;   // cached export plan points into the workspace
     for (void* p : h->owned) cudaFree(p);
     h->owned.clear();
     h->d_xofs.clear(); h->d_yofs.clear(); h->d_xw.clear(); h->d_yw.clear();
@@ -726,12 +723,9 @@ int finish_outputs(b2orb_handle* h, int np, const b2orb_stereo_out* o) {
     const int export_max = [] { const char* e = getenv("B2ORB_EXPORT"); return e ? atoi(e) : 4; }();
     if (o && np <= export_max && o->cap >= h->geom.kp_cap) {
         static_assert(sizeof(B2ExportPlan) < 3500, "plan must fit the kernel parameter space");
-        const bool same = h->exp_np == np && memcmp(&h->exp_out, o, sizeof(*o)) == 0;
-        if (!same) {   // pointer attributes are queried once per distinct set of output arrays
-            h->exp_ok = export_plan(h, np, o, h->exp_plan);
-            h->exp_out = *o;
-            h->exp_np = np;
-        }
+        // The pointer attributes are queried on every call (a few hundred ns each): a cached verdict would go stale when
+        // the caller frees a pinned array and a pageable one lands on the same address, or toggles b2orb_set_projection.
+        h->exp_ok = export_plan(h, np, o, h->exp_plan);
         if (h->exp_ok) {
             b2_launch_pdl(export_kernel, dim3(h->exp_plan.nseg, np, 4), dim3(256), 0, h->stream, h->exp_plan);
             ++h->launches;
