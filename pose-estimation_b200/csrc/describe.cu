@@ -102,7 +102,7 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned
 }
 
 
-constexpr int DS_KPW = 8;            // keypoints per warp (amortises the weight-table copy)
+constexpr int DS_KPW = 16;           // keypoints per warp in large batches (amortises the weight-table copy); 4 when latency counts
 constexpr int WA_ROWS = 31, WA_WORDS = 9;    // un-blurred window: rows cy-15..cy+15, 36 bytes from (cx-15) & ~3
 constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..cy+18, 40 bytes from (cx-18) & ~3
 
@@ -112,7 +112,7 @@ constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..c
 __global__ void __launch_bounds__(DS_WARPS * 32, DS_MINB)
 describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint32_t* __restrict__ sel,
                 const int* __restrict__ sel_cnt, const unsigned* __restrict__ ic_table, KeyPointOut* __restrict__ kps,
-                uint8_t* __restrict__ desc, int* __restrict__ n_out) {
+                uint8_t* __restrict__ desc, int* __restrict__ n_out, int kpw) {
     b2_pdl_wait();
     __shared__ unsigned s_ic[IC_WORDS];
     __shared__ unsigned s_wa[DS_WARPS][2][WA_ROWS * WA_WORDS];      // double-buffered: keypoint k+1 lands while k is worked on
@@ -154,8 +154,8 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     const auto fetch = [&](int it) {
         const unsigned bufa = (it & 1) * (unsigned)sizeof(s_wa[0][0]), bufb = (it & 1) * (unsigned)sizeof(s_wb[0][0]);
         Kp k;
-        k.slot = (blockIdx.x * DS_WARPS + wid) * DS_KPW + it;      // output slot in this image
-        k.valid = it < DS_KPW && k.slot < total && k.slot < g.kp_cap;
+        k.slot = (blockIdx.x * DS_WARPS + wid) * kpw + it;      // output slot in this image
+        k.valid = it < kpw && k.slot < total && k.slot < g.kp_cap;
         k.level = 0; k.cx = k.cy = 0; k.response = 0.f;
         if (!k.valid) { asm volatile("cp.async.commit_group;" ::: "memory"); return k; }
         // level = number of levels whose inclusive prefix is <= slot
@@ -194,7 +194,7 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
     };
 
     Kp nxt = fetch(0);
-    for (int it = 0; it < DS_KPW; ++it) {
+    for (int it = 0; it < kpw; ++it) {
         const Kp cur = nxt;
         if (!cur.valid) break;
         const int slot = cur.slot, level = cur.level, cx = cur.cx, cy = cur.cy;
@@ -274,7 +274,9 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
 
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,
                         const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s) {
-    const int per_cta = DS_WARPS * DS_KPW;
+    // few images: short warps on many SMs (latency); large batches: long warps (the per-CTA table copy amortises)
+    const int kpw = (long long)g.kp_cap * nimg <= 148LL * DS_WARPS * 16 ? 4 : DS_KPW;
+    const int per_cta = DS_WARPS * kpw;
     dim3 grid((g.kp_cap + per_cta - 1) / per_cta, nimg);
-    b2_launch_pdl(describe_kernel, dim3(grid), dim3(DS_WARPS * 32), 0, s, g, im, sel, sel_cnt, ic_table, static_cast<KeyPointOut*>(kps), desc, n_out);
+    b2_launch_pdl(describe_kernel, dim3(grid), dim3(DS_WARPS * 32), 0, s, g, im, sel, sel_cnt, ic_table, static_cast<KeyPointOut*>(kps), desc, n_out, kpw);
 }
