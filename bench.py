@@ -417,6 +417,9 @@ def main():
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms_per_launch,
+                     "note": "the path is byte/integer stencil work that streams each pixel once: HBM is the roofline the "
+                             "metric asks for, but every kernel is instruction-issue bound on B200 (FAST: ALU pipe 76 %, "
+                             "FMA pipe 21 %, issue 72 %, DRAM 4 %; profiles/r1/m_ncu_full_summary.csv, DESIGN.md 4)",
                      "kernel_time_shares": shares,
                      "kernel_us_per_pair": {k: round(v[0] * 1e3 / (psteps * prof_pairs), 3) for k, v in prof.items() if v[1]}},
         "pipeline": {"algorithmic_bytes_per_pair": b_pair, "achieved_gbs": b_pair * value / world / 1e9,
