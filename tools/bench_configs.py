@@ -4,7 +4,7 @@
     images in, host results out): p50 / p95 / max over N calls — config 3 asks whether the 5 ms period of the
     200 Hz cfsd stream is met;
   * throughput of the same call with a batch of pairs (host buffers, copies inside);
-  * parity of the first pair against the CPU oracle (checker only).
+  * parity of the first pair against the CPU oracle (checker only, through tests/parity_configs.py).
 One JSON object per shape on stdout.  Needs a GPU.  Usage: python tools/bench_configs.py [--calls 200] [--batch 64]
 """
 import argparse
@@ -69,16 +69,9 @@ def main():
         if shape == "cfsd":
             line["deadline_5ms_met"] = bool(lat[int(len(lat) * 0.95)] < 5.0)
         if not args.no_parity:
-            from oracle import oracle as orc
-            ex = orc.OracleExtractor(nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn)
-            kl, dl = ex(ls[0]); kr, dr = ex(rs[0])
-            o = outb[0]
-            nl, nr = int(o["n_l"][0]), int(o["n_r"][0])
-            ok = nl == len(kl) and nr == len(kr) and np.array_equal(o["desc_l"][0, :nl], dl) and \
-                np.array_equal(o["desc_r"][0, :nr], dr) and all(np.array_equal(o["kp_l"][0, :nl][f], kl[f]) for f in ("x", "y", "angle", "octave", "response"))
-            ti, di = orc.bf_match(dl, dr)
-            ok = ok and np.array_equal(o["train_idx"][0, :nl], ti) and np.array_equal(o["dist"][0, :nl], di)
-            line["bit_exact_vs_oracle_pair0"] = bool(ok)
+            from tests.parity_configs import stereo_pair_bit_exact   # the oracle stays behind tests/
+            line["bit_exact_vs_oracle_pair0"] = stereo_pair_bit_exact((nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn),
+                                                                      ls[0], rs[0], outb[0])
         print(json.dumps(line), flush=True)
         hd.close()
     if "cfsd" in args.shapes.split(","):
@@ -112,13 +105,9 @@ def cfsd_live(args, synth, fe):
             "h2d_bytes_per_frame": sw * sh * 4, "deadline_5ms_met": bool(lat[int(len(lat) * 0.95)] < 5.0),
             "keypoints_left": int(out1[0]["n_l"][0])}
     if not args.no_parity:
-        from oracle import oracle as orc
-        t0 = time.perf_counter()
-        gl, gr = orc.cfsd_ingest(frames[0], 2 * w, h)
-        rl, rr = orc.remap(gl, *maps[0]), orc.remap(gr, *maps[1])
-        line["cpu_port_ingest_rectify_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
-        ex = orc.OracleExtractor(nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn)
-        kl, dl = ex(rl)
+        from tests.parity_configs import cfsd_live_reference
+        kl, dl, ms = cfsd_live_reference((nf, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn), frames[0], w, h, maps)
+        line["cpu_port_ingest_rectify_ms"] = round(ms, 2)
         hd.check(hd.L.b2orb_stereo_frontend_packed(hd.h, frames.ctypes.data, 1, sw, sh, sw * 4, sw * sh * 4, w, h, 0, out1[1]))
         n = int(out1[0]["n_l"][0])
         line["bit_exact_vs_oracle"] = bool(n == len(kl) and np.array_equal(out1[0]["desc_l"][0, :n], dl))
