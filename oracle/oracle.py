@@ -41,6 +41,8 @@ def lib():
         L.orc_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
         L.orc_destroy.argtypes = [vp]
         L.orc_set_taps.argtypes = [vp, i32p]
+        L.orc_set_tie_mode.argtypes = [vp, C.c_int]
+        L.orc_get_ties.argtypes = [vp, i32p]
         L.orc_tables.argtypes = [vp, f32p, f32p, i32p, i32p]
         L.orc_extract.restype = C.c_int
         L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
@@ -87,7 +89,8 @@ def _p(a):
 
 
 def _img(a):
-    a = np.ascontiguousarray(a, dtype=np.uint8)
+    if not (isinstance(a, np.ndarray) and a.dtype == np.uint8 and a.ndim == 2 and a.strides[1] == 1 and a.strides[0] >= a.shape[1]):
+        a = np.ascontiguousarray(a, dtype=np.uint8)   # row-strided views (cv::Mat ROIs) are passed through as they are
     assert a.ndim == 2
     return a
 
@@ -95,13 +98,22 @@ def _img(a):
 class OracleExtractor:
     """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:45-111) on the CPU oracle."""
 
-    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, taps=None):
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, taps=None, tie_mode=1):
         self.L = lib()
         self.nfeatures, self.nlevels = nfeatures, nlevels
         self.h = self.L.orc_create(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast)
         if taps is not None:
             t = (C.c_int * 7)(*taps)
             self.L.orc_set_taps(self.h, t)
+        if tie_mode != 1:
+            self.L.orc_set_tie_mode(self.h, tie_mode)
+
+    def ties(self):
+        """Per level of the last call: how many equal-count comparisons the quadtree's final partial pass consumed
+        (0 = the reference's pointer tie-break at src/ORBextractor.cc:684 could not matter on that level)."""
+        t = (C.c_int * self.nlevels)()
+        self.L.orc_get_ties(self.h, t)
+        return np.array(t[:], np.int32)
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -137,6 +149,97 @@ class OracleExtractor:
         out = np.zeros((cap, 3), np.float32)
         n = self.L.orc_get_raw(self.h, level, _p(out), cap)
         return out[:n].copy()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# oracle/_ref: the reference's own src/ORBextractor.cc, compiled unmodified against tests/mock_opencv (oracle/ref/)
+# ------------------------------------------------------------------------------------------------------------------
+REF_SRC = "/root/reference/src/ORBextractor.cc"
+_REF_DIR = os.path.join(_HERE, "_ref")
+_REF_LIBS = {1: "libref_orb.so", -1: "libref_orb_desc.so", 0: "libref_orb_sysmalloc.so"}
+_ref_libs = {}
+
+
+def build_ref():
+    """(Re)build oracle/_ref/*.so when the reference tree is mounted (this container); on the GPU box the prebuilt
+    files travel with the snapshot.  Returns True when the libraries exist afterwards."""
+    lib()
+    if os.path.exists(REF_SRC):
+        subprocess.check_call(["make", "-C", os.path.join(_HERE, "ref"), "-s"])
+    return all(os.path.exists(os.path.join(_REF_DIR, n)) for n in _REF_LIBS.values())
+
+
+def ref_lib(arena=1):
+    """arena: +1 ascending heap addresses (the documented tie rule), -1 descending, 0 the process malloc."""
+    if arena not in _ref_libs:
+        if not build_ref():
+            return None
+        L = C.CDLL(os.path.join(_REF_DIR, _REF_LIBS[arena]))
+        vp, i32p, f32p = C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_float)
+        L.ref_create.restype = vp
+        L.ref_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.ref_destroy.argtypes = [vp]
+        L.ref_set_taps.argtypes = [i32p]
+        L.ref_tables.argtypes = [vp, f32p, f32p, f32p, f32p, i32p, i32p]
+        L.ref_extract.restype = C.c_int
+        L.ref_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
+        L.ref_level_size.argtypes = [vp, C.c_int, i32p, i32p]
+        L.ref_get_level.argtypes = [vp, C.c_int, vp]
+        L.ref_get_level_bordered.argtypes = [vp, C.c_int, vp]
+        assert L.ref_arena_mode() == arena
+        _ref_libs[arena] = L
+    return _ref_libs[arena]
+
+
+def ref_available():
+    return ref_lib(1) is not None
+
+
+class RefExtractor:
+    """ORB_SLAM2::ORBextractor of the reference itself (oracle/_ref), same call surface as OracleExtractor."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, taps=None, arena=1):
+        self.L = ref_lib(arena)
+        if self.L is None:
+            raise RuntimeError("oracle/_ref is not built and /root/reference is not mounted")
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.taps = tuple(taps) if taps is not None else TAPS_CV4
+        self.h = self.L.ref_create(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        """(scale, inv_scale, sigma2, inv_sigma2, quota, umax) — src/ORBextractor.cc:415-469."""
+        nl = self.nlevels
+        f = [(C.c_float * nl)() for _ in range(4)]
+        q = (C.c_int * nl)(); u = (C.c_int * 16)()
+        self.L.ref_tables(self.h, f[0], f[1], f[2], f[3], q, u)
+        return tuple(np.array(a[:], np.float32) for a in f) + (np.array(q[:], np.int32), np.array(u[:], np.int32))
+
+    def __call__(self, image):
+        image = _img(image)
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        self.L.ref_set_taps((C.c_int * 7)(*self.taps))
+        n = self.L.ref_extract(self.h, _p(image), image.shape[1], image.shape[0], image.strides[0],
+                               _p(kps), _p(desc), cap)
+        assert n >= 0, "capacity exceeded"
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, level, bordered=False):
+        w, h = C.c_int(), C.c_int()
+        self.L.ref_level_size(self.h, level, C.byref(w), C.byref(h))
+        if bordered:
+            out = np.zeros((h.value + 38, w.value + 38), np.uint8)
+            self.L.ref_get_level_bordered(self.h, level, _p(out))
+        else:
+            out = np.zeros((h.value, w.value), np.uint8)
+            self.L.ref_get_level(self.h, level, _p(out))
+        return out
 
 
 def resize(src, dw, dh):

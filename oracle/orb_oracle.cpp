@@ -6,12 +6,21 @@
 // together with the OpenCV primitives those files delegate to (resize, FAST, GaussianBlur,
 // fastAtan2, cvRound, BFMatcher) and glibc's cosf/sinf, restated from their published
 // algorithms.  OpenCV is an un-vendored system dependency of the reference (CMakeLists.txt:136;
-// "opencv 3.2.0" per Dockerfile.amd64:20) and cannot be built here, so each primitive is pinned
-// against the cv2 4.13.0 wheel of this image by tests/test_oracle_vs_cv2.py, and the whole
-// pipeline is pinned by golden vectors under tests/golden/ (generated by
-// tools/gen_golden.py).  The reference has no tests or golden vectors of its own for this path
-// (test/vio-test.cpp is empty) and cannot be run here: with respect to the reference itself PARITY IS UNPINNED; what
-// this oracle is pinned to is "cv2 4.13 + glibc 2.39" (the real OpenCV kernels behind the same call sites), see DESIGN.md 2.
+// "opencv 3.2.0" per Dockerfile.amd64:20) and cannot be built here.
+//
+// HOW THIS ORACLE IS PINNED
+//   1. To the reference's own code: /root/reference/src/ORBextractor.cc is compiled UNMODIFIED against a mock of the
+//      OpenCV headers into oracle/_ref/libref_orb.so (oracle/ref/Makefile, ref_glue.cpp) and run next to this file on
+//      seven synthetic shapes, six real camera frames shipped with the reference, odd shapes / strided inputs / other
+//      pyramid parameters, under both heap-address orders that the quadtree's pointer tie-break (:684) can see:
+//      keypoints, order, descriptors and pyramid levels are bit-identical (tests/test_ref_parity.py).  Its outputs are
+//      committed as tests/golden/ref/*.npz (tools/gen_ref_golden.py) so the check also runs where the tree is absent.
+//   2. The OpenCV primitives under both (resize, FAST, GaussianBlur, fastAtan2, BFMatcher, remap, triangulatePoints)
+//      to the real OpenCV 4.13 kernels of the cv2 wheel of this image (tests/test_oracle_vs_cv2.py), and the whole
+//      pipeline to cv2-assembled golden vectors (tools/gen_golden.py -> tests/golden/*.npz).
+//   The reference has no tests or golden vectors of its own (test/vio-test.cpp is empty).  What stays outside any pin
+//   on this box: OpenCV 3.2's Gaussian taps (the version the Dockerfile names; 4.x taps are the default, 3.2's are a
+//   runtime option restated from the published 3.2 algorithm) and musl's cosf/sinf (glibc 2.39 is what is here).
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this library.  The product (pose-estimation_b200/csrc) never links or calls it.
@@ -392,8 +401,14 @@ static void divide_node(const Node& p, Node& n1, Node& n2, Node& n3, Node& n4) {
 }
 
 // DistributeOctTree, src/ORBextractor.cc:539-763.
+// tie_mode: +1 = among equal point counts the node created LATER is expanded first (default; models heap addresses
+// that grow with allocation order), -1 = the node created EARLIER first (addresses that shrink).  Both orders are
+// checked against the reference's own code under the matching allocator (oracle/ref/ref_glue.cpp).
+// *ties (optional) counts the equal-count neighbours in the sorted vector that the expansion loop actually
+// consumed or stopped at, i.e. whether the pointer comparison could influence this call's result at all.
 static std::vector<KeyPoint> distribute_octtree(const std::vector<KeyPoint>& in, int minX, int maxX,
-                                                int minY, int maxY, int N) {
+                                                int minY, int maxY, int N, int tie_mode = 1, int* ties = nullptr) {
+    if (ties) *ties = 0;
     std::vector<KeyPoint> result;
     const int nIni = (int)std::round((float)(maxX - minX) / (maxY - minY));
     if (nIni < 1 || in.empty()) return result;  // reference divides by zero / indexes an empty vector here
@@ -433,7 +448,7 @@ static std::vector<KeyPoint> distribute_octtree(const std::vector<KeyPoint>& in,
             nodes.push_front(n);
             if (n.keys.size() > 1) {
                 ++nToExpand;
-                sizeAndNode.push_back({{(int)n.keys.size(), nodes.front().seq}, &nodes.front()});
+                sizeAndNode.push_back({{(int)n.keys.size(), tie_mode * nodes.front().seq}, &nodes.front()});
                 nodes.front().lit = nodes.begin();
             }
         }
@@ -462,6 +477,7 @@ static std::vector<KeyPoint> distribute_octtree(const std::vector<KeyPoint>& in,
                               return a.first < b.first;
                           });
                 for (int j = (int)prev.size() - 1; j >= 0; --j) {
+                    if (ties && j > 0 && prev[j].first.first == prev[j - 1].first.first) ++*ties;
                     Node n1, n2, n3, n4;
                     divide_node(*prev[j].second, n1, n2, n3, n4);
                     Node* kids[4] = {&n1, &n2, &n3, &n4};
@@ -501,6 +517,8 @@ struct Extractor {
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
     std::vector<int> mnFeaturesPerLevel, umax;
     int taps[7];
+    int tie_mode = 1;            // see distribute_octtree
+    std::vector<int> ties;       // per level: equal-count comparisons that mattered in the last extract
     // intermediates kept for tests (the reference keeps mvImagePyramid as a public member too)
     std::vector<Img> pyramid, blurred;
     std::vector<std::vector<KeyPoint>> raw;  // vToDistributeKeys per level (coords rel. to border)
@@ -585,6 +603,7 @@ struct Extractor {
     void compute_keypoints(std::vector<std::vector<KeyPoint>>& all) {
         all.assign(nlevels, {});
         raw.assign(nlevels, {});
+        ties.assign(nlevels, 0);
         const float W = 30;
         for (int level = 0; level < nlevels; ++level) {
             const Img& im = pyramid[level];
@@ -618,7 +637,7 @@ struct Extractor {
             }
             std::vector<KeyPoint>& kps = all[level];
             kps = distribute_octtree(toDistribute, minBorderX, maxBorderX, minBorderY, maxBorderY,
-                                     mnFeaturesPerLevel[level]);
+                                     mnFeaturesPerLevel[level], tie_mode, &ties[level]);
             const int scaledPatchSize = (int)(PATCH_SIZE * mvScaleFactor[level]);
             for (KeyPoint& kp : kps) {
                 kp.x += minBorderX;
@@ -888,6 +907,13 @@ extern "C" {
 void* orc_create(int nf, float sf, int nl, int ini, int mn) { return new Extractor(nf, sf, nl, ini, mn); }
 void orc_destroy(void* h) { delete (Extractor*)h; }
 void orc_set_taps(void* h, const int* taps) { std::memcpy(((Extractor*)h)->taps, taps, 7 * sizeof(int)); }
+void orc_set_tie_mode(void* h, int mode) { ((Extractor*)h)->tie_mode = mode < 0 ? -1 : 1; }
+// ties[nlevels] of the last orc_extract: 0 = the reference's pointer comparison (src/ORBextractor.cc:684) could not
+// have influenced that level, whatever the heap layout
+void orc_get_ties(void* h, int* ties) {
+    Extractor* e = (Extractor*)h;
+    for (int i = 0; i < e->nlevels; ++i) ties[i] = i < (int)e->ties.size() ? e->ties[i] : 0;
+}
 
 // tables: scale[nl], inv_scale[nl], quota[nl], umax[16]
 void orc_tables(void* h, float* scale, float* inv, int* quota, int* umax) {
