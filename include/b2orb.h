@@ -57,7 +57,8 @@ typedef struct b2orb_config {
     int32_t max_width;    /* largest image accepted (<= 4096) */
     int32_t max_height;   /* (<= 4096) */
     int32_t max_images;   /* images resident per launch set; a stereo pair needs 2 */
-    int32_t blur_taps[7]; /* 7-tap integer Gaussian, sum 256; all zero = OpenCV 4.x {18,34,48,56,48,34,18} */
+    int32_t blur_taps[7]; /* symmetric 7-tap integer Gaussian (Q8); all zero = OpenCV 4.x {18,34,48,56,48,34,18}; OpenCV 3.2 (the
+                             version Dockerfile.amd64:20 names) rounds to {18,34,49,55,49,34,18} = 257, results saturate at 255 */
     float match_ratio;              /* matchRatio */
     float min_match_dist;           /* minMatchDist */
     float max_vertical_pixel_dist;  /* maxVerticalPixelDist */

@@ -80,6 +80,7 @@ struct B2Geom {
     unsigned slab;            // bytes of one image's pyramid (levels 1..) / blur (levels 0..) slab
     int umax[16];             // src/ORBextractor.cc:454-469
     int taps[7];
+    int tap_sat;              // taps sum to more than 256: the blur saturates its result (OpenCV 3.2 kernel)
     unsigned tapv[10];        // blur.cu: u8x4 tap vectors for the 4 output pixels of a lane (host-built)
     B2Level lv[B2_MAX_LEVELS];
 };

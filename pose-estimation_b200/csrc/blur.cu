@@ -1,7 +1,7 @@
 // 7x7 Gaussian blur of every pyramid level — GaussianBlur(workingMat, workingMat, Size(7,7), 2, 2,
 // BORDER_REFLECT_101), src/ORBextractor.cc:1085-1086 (K6).  OpenCV's 8-bit fixed-point path: separable
-// integer taps (sum 256); horizontal pass exact in Q8 (<= 65280), vertical pass accumulates in Q16 and
-// rounds with (acc + 32768) >> 16.  Both passes are exact integer sums with ONE rounding at the end, so any
+// integer taps (sum 256 in OpenCV 4.x; 257 for the kernel OpenCV 3.2 rounds, which then needs the saturating cast);
+// horizontal pass exact in Q8, vertical pass accumulates in Q16 and rounds with (acc + 32768) >> 16.  Both passes are exact integer sums with ONE rounding at the end, so any
 // evaluation order is bit-identical.
 //
 // The kernel is instruction-issue bound, not HBM bound, so it is organised around instructions per pixel:
@@ -41,7 +41,7 @@ __device__ __forceinline__ int reflect101_once(int i, int n) {
     return min(max(i, 0), n - 1);
 }
 
-template <bool EDGE>
+template <bool EDGE, bool SAT>
 __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int spitch, uint8_t* __restrict__ dst,
                                           int dpitch, int w, int h, int x, int y0, int rows, int lane, uint8_t* ring,
                                           const B2Geom& g) {
@@ -134,8 +134,11 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
                         const int e1 = hw[(p + 6) % 7][j] + hw[(p + 2) % 7][j];
                         const int e2 = hw[(p + 5) % 7][j] + hw[(p + 3) % 7][j];
                         o[j] = (unsigned)(g.taps[0] * e0 + g.taps[1] * e1 + g.taps[2] * e2 + g.taps[3] * hw[(p + 4) % 7][j] + 32768);
+                        // taps summing to more than 256 (OpenCV 3.2 rounds the sigma-2 kernel to a sum of 257) can push
+                        // the rounded value past 255: saturate_cast<uchar>, as FixedPtCastEx does
+                        if (SAT) o[j] = min(o[j], 0x00FFFFFFu);
                     }
-                    // bits 16..23 of each accumulator are the result (taps sum to 256 -> never above 255)
+                    // bits 16..23 of each accumulator are the result (never above 255 when the taps sum to <= 256)
                     const unsigned lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
                     const unsigned packed = __byte_perm(lo, hi, 0x5410);
                     if (x < w) *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * dpitch + x) = packed;
@@ -168,8 +171,13 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
     // a strip needs the border code if it touches column 0 or its last lane's halo reaches beyond w-1
     const bool edge = strip == 0 || strip * 128 + 128 + 3 > L.w - 1;
     uint8_t* ring = s_ring[threadIdx.x >> 5];
-    if (edge) blur_task<true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
-    else blur_task<false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+    if (g.tap_sat) {   // warp-uniform (whole launch)
+        if (edge) blur_task<true, true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+        else blur_task<false, true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+    } else {
+        if (edge) blur_task<true, false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+        else blur_task<false, false>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
+    }
 }
 
 }  // namespace

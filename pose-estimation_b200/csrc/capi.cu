@@ -257,7 +257,9 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     static const int def_taps[7] = {18, 34, 48, 56, 48, 34, 18};
     bool zero = true;
     for (int i = 0; i < 7; ++i) zero = zero && c.blur_taps[i] == 0;
-    for (int i = 0; i < 7; ++i) g.taps[i] = zero ? def_taps[i] : c.blur_taps[i];
+    int tap_sum = 0;
+    for (int i = 0; i < 7; ++i) { g.taps[i] = zero ? def_taps[i] : c.blur_taps[i]; tap_sum += g.taps[i]; }
+    g.tap_sat = tap_sum > 256;
     {   // blur.cu: output pixel j of a lane sees columns x+j-3 .. x+j+3 of the words W0|W1|W2 = columns x-4 .. x+7
         const int k0 = g.taps[0], k1 = g.taps[1], k2 = g.taps[2], k3 = g.taps[3];
         auto tv = [](int a, int b, int c2, int d) { return (unsigned)a | ((unsigned)b << 8) | ((unsigned)c2 << 16) | ((unsigned)d << 24); };
@@ -656,6 +658,11 @@ export_kernel(const __grid_constant__ B2ExportPlan plan) {
     const long long bytes = (long long)n * sg.elem;
     const uint8_t* src = sg.src + (sg.count ? p * sg.src_pair : 0);
     uint8_t* dst = sg.dst + (sg.count ? p * sg.dst_pair : 0);
+    if ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 3) {
+        // 1-byte segments (depth flags) of pair p start at p * cap, which need not be a multiple of 4: byte copies
+        for (long long i = blockIdx.z * 256 + threadIdx.x; i < bytes; i += 256 * gridDim.z) dst[i] = src[i];
+        return;
+    }
     const int words = (int)(bytes >> 2);
     const unsigned* s4 = reinterpret_cast<const unsigned*>(src);
     unsigned* d4 = reinterpret_cast<unsigned*>(dst);
@@ -672,7 +679,7 @@ bool export_plan(b2orb_handle* h, int np, const b2orb_stereo_out* o, B2ExportPla
     auto devptr = [&](void* host) -> uint8_t* {
         cudaPointerAttributes a;
         if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { cudaGetLastError(); ok = false; return nullptr; }
-        if (a.type != cudaMemoryTypeHost || !a.devicePointer || ((uintptr_t)a.devicePointer & 3)) { ok = false; return nullptr; }
+        if (a.type != cudaMemoryTypeHost || !a.devicePointer) { ok = false; return nullptr; }
         return static_cast<uint8_t*>(a.devicePointer);
     };
     auto add = [&](void* host, const void* src, int elem, long long src_pair_elems, long long dst_pair_elems,
@@ -753,14 +760,15 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
         cfg->ini_th_fast < 1 || cfg->min_th_fast < 1 || cfg->min_th_fast > cfg->ini_th_fast ||
         cfg->ini_th_fast > 254 || cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_images < 1)
         return B2ORB_ERR_INVALID;
-    {   // blur taps: all zero (default) or a symmetric u8 kernel with sum 256 (exact Q8 x Q8 arithmetic, blur.cu)
+    {   // blur taps: all zero (default = OpenCV 4.x {18,34,48,56,48,34,18}) or a symmetric u8 kernel whose Q8 x Q8
+        // accumulation fits 32 bits; sums above 256 (OpenCV 3.2's {18,34,49,55,49,34,18} = 257) saturate (blur.cu)
         int sum = 0; bool zero = true, ok = true;
         for (int i = 0; i < 7; ++i) {
             zero = zero && cfg->blur_taps[i] == 0;
             ok = ok && cfg->blur_taps[i] >= 0 && cfg->blur_taps[i] <= 255 && cfg->blur_taps[i] == cfg->blur_taps[6 - i];
             sum += cfg->blur_taps[i];
         }
-        if (!zero && (!ok || sum != 256)) return B2ORB_ERR_INVALID;
+        if (!zero && (!ok || sum < 1 || sum > 1024)) return B2ORB_ERR_INVALID;
     }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return B2ORB_ERR_CUDA;
@@ -918,6 +926,7 @@ int b2orb_stereo_frontend_device(b2orb_handle* h, const uint8_t* d_images_l, con
         return fail(h, B2ORB_ERR_INVALID, "bad stereo arguments");
     if (2 * npairs > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*npairs exceeds max_images");
     if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    if (npairs == 1) image_stride = (size_t)step * height;
     B2_CUDA(h, cudaSetDevice(h->device));
     int rc = configure(h, width, height);
     if (rc) return rc;
@@ -1087,6 +1096,7 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
         return fail(h, B2ORB_ERR_INVALID, "bad stereo arguments");
     if (2 * npairs > h->cfg.max_images) return fail(h, B2ORB_ERR_CAPACITY, "2*npairs exceeds max_images");
     if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    if (npairs == 1) image_stride = (size_t)step * height;   // unused for one pair: keep the one-copy upload paths
     B2_CUDA(h, cudaSetDevice(h->device));
     if (h->pipe_chunk > 0 && npairs > h->pipe_chunk && h->root == h)
         return stereo_frontend_pipelined(h, images_l, images_r, npairs, width, height, step, image_stride, temporal, out);

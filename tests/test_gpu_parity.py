@@ -316,6 +316,31 @@ def test_direct_export_to_pinned_outputs_equals_copy_path(npairs, fe, synth):
     a_hd.close(); b_hd.close()
 
 
+def test_direct_export_with_capacity_not_a_multiple_of_four(fe, synth):
+    """750 features -> capacity 782: the 1-byte depth-flag rows of pairs 1.. start at addresses that are not word
+    aligned; the export kernel must fall back to byte copies there instead of faulting."""
+    w, h, nf, ini, mn = 672, 376, 750, 20, 7
+    npairs = 3
+    ls, rs = synth.sequence("cfsd", npairs, seed=15)
+    fx = 0.58 * w
+    P1 = [[fx, 0, 0.49 * w, 0], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]
+    P2 = [[fx, 0, 0.49 * w, 0.537 * fx], [0, fx, 0.49 * h, 0], [0, 0, 1, 0]]
+    a_hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    b_hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    assert a_hd.keypoint_capacity % 4 != 0
+    for hd in (a_hd, b_hd):
+        hd.set_projection(P1, P2, 20.0)
+    pinned = b_hd.alloc_stereo_out(npairs, pinned=True)
+    a = a_hd.stereo_frontend(ls, rs, temporal=True)
+    b = b_hd.stereo_frontend(ls, rs, temporal=True, out=pinned)
+    _stereo_equal(a, b, npairs)
+    for p in range(npairs):
+        n = int(a["n_match"][p])
+        assert n > 10 and np.array_equal(a["depth_flags"][p, :n], b["depth_flags"][p, :n])
+        assert np.array_equal(a["points4d"][p, :, :n].view(np.uint64), b["points4d"][p, :, :n].view(np.uint64))
+    a_hd.close(); b_hd.close()
+
+
 def test_bench_sized_batch_matches_oracle_and_single_calls(fe, oracle, synth):
     """The throughput configuration itself: 136 pairs in ONE call (default pipeline: chunks of 64 + 64 + 8 over the
     internal lanes, 64-row FAST bands, no programmatic launch chain, copy-path outputs).  Every 9th pair is checked
