@@ -159,12 +159,12 @@ typedef struct b2orb_stereo_out {
  * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers (pinned memory, see
  * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 64 pairs are processed as a pipeline
  * of chunks on internal streams so that the H2D copy, the kernels and the D2H copy of different chunks overlap;
- * results do not depend on the chunking.  Environment: B2ORB_PIPE_CHUNK (pairs per chunk, 0 = off, read at
- * b2orb_create), B2ORB_PIPE_LANES (2..8 workspaces, default 3).
+ * results do not depend on the chunking (b2orb_debug_set: "pipe_chunk" pairs per chunk, 0 = off; "pipe_lanes" 2..8
+ * workspaces, default 3).
  * Calls of up to 4 pairs whose output arrays are all pinned host memory (b2orb_host_alloc, cudaHostAlloc,
  * cudaHostRegister) return their results through one kernel that writes entries [0, n) of every array directly
  * into the caller's buffers; otherwise whole arrays are copied back.  Either way only entries [0, n) are defined.
- * B2ORB_EXPORT=0 forces the copy path. */
+ * b2orb_debug_set(h, "export_max", 0) forces the copy path. */
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
                           int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
 
@@ -210,6 +210,14 @@ int b2orb_debug_get_level(b2orb_handle* h, int slot, int level, int which, uint8
 /* raw per-cell FAST corners of a level before the quadtree: packed x | y<<12 | response<<24 with x,y
  * relative to the 16-px border (unordered).  Returns the count through *n. */
 int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* dst, int cap, int* n);
+
+/* Launch-time choices the library normally makes by batch size, pinned per handle for tests and A/B runs (nothing is
+ * read from the environment; two handles on two threads may differ).  Keys: "pdl" (-1 auto / 0 / 1 programmatic
+ * dependent launch), "fork_max" (blur on a side stream for calls of at most this many images), "export_max" (direct
+ * export into pinned outputs for calls of at most this many pairs), "fast_band" (-1 auto, 0 / 1 / 2 = 16 / 32 / 64-row
+ * FAST bands), "octree_points" (1 = quadtree by point passes only), "pipe_chunk" / "pipe_lanes" (pipelined host path,
+ * before its first use), "pipe_trace". */
+int b2orb_debug_set(b2orb_handle* h, const char* key, int value);
 
 /* Quadtree levels (since the library was loaded, on the handle's device) whose keypoints were so clustered that the
  * count-pyramid path had to be redone with point passes (csrc/octree.cu).  Test / tuning aid. */

@@ -11,7 +11,8 @@
 // global memory before the previous grid has completed and flushed, so the result is the one of plain stream order.
 // Early-scheduled CTAs hold SM slots while they wait, which costs throughput when another stream could have used
 // them (measured: -5 % on 128-pair batches over two streams), so the C-ABI layer switches the attribute on only for
-// small batches (b2_pdl_on, per host thread; B2ORB_PDL=0/1 overrides).  Without the attribute the wait is a no-op.
+// small batches (b2_pdl_on, per host thread; b2orb_debug_set(h, "pdl", 0/1) overrides).  Without the attribute the wait
+// is a no-op.
 extern thread_local bool b2_pdl_on;
 #ifdef __CUDACC__
 __device__ __forceinline__ void b2_pdl_wait() {
@@ -124,8 +125,6 @@ struct B2MatchProblem {
 };
 
 // ---- kernel launchers (each file documents the reference lines it restates) --------------------
-bool b2_launch_pyramid_chain(const B2Geom& g, const B2Images& im, int* const* xofs, short* const* xw, int* const* yofs,
-                             short* const* yw, int nimg, cudaStream_t s);
 void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int* xofs, const short* xw,
                       const int* yofs, const short* yw, int nimg, cudaStream_t s);
 // cv::remap with fixed-point maps (map1: short2 per pixel, map2: u16 per pixel), source and output of size w x h
@@ -142,11 +141,11 @@ void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t 
 // the per-cell "iniThFAST found something" flags; fast_vote applies the per-cell threshold vote and expands the words
 // into candidates x | y<<12 | (b-1)<<24
 void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
-                          cudaStream_t s);
+                          int forced_band, cudaStream_t s);
 void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,
                          int* cand_cnt, int nimg, cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
-                      B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s);
+                      unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, int force_legacy, cudaStream_t s);
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,
                         const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
 #define B2_IC_WORDS (4 * 16 * 9 * 2)   // IC_Angle weight table, describe.cu

@@ -20,12 +20,7 @@ thread_local bool b2_pdl_on = false;
 
 namespace {
 
-// programmatic dependent launch for latency-sized batches only (b2orb_internal.cuh)
-constexpr int B2_PDL_MAX_IMAGES = 8;
-inline bool pdl_for(int nimg) {
-    const int forced = [] { const char* e = getenv("B2ORB_PDL"); return e ? (atoi(e) ? 1 : 0) : -1; }();
-    return forced >= 0 ? forced != 0 : nimg <= B2_PDL_MAX_IMAGES;
-}
+constexpr int B2_PDL_MAX_IMAGES = 8;   // programmatic dependent launch for latency-sized batches only (b2orb_internal.cuh)
 
 inline int cv_round_f(float v) { return (int)lrintf(v); }   // cvRound: round-half-even
 inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
@@ -51,8 +46,22 @@ struct B2ExportPlan {
     int nseg;
 };
 
+// Launch-time choices the library normally makes by batch size; tests and A/B runs pin them per handle with
+// b2orb_debug_set (no environment variables, nothing process-global: two handles on two threads can differ).
+struct B2Tuning {
+    int pdl = -1;            // programmatic dependent launch: -1 = by batch size (<= 8 images), 0 / 1 = forced
+    int fork_max = 8;        // blur on the side stream for calls of at most this many images
+    int export_max = 4;      // direct export into pinned outputs for calls of at most this many pairs
+    int fast_band = -1;      // FAST band variant 0 / 1 / 2 (16 / 32 / 64 rows), -1 = by batch size
+    int octree_points = 0;   // 1 = quadtree by point passes only (the count-pyramid path's fallback)
+    int pipe_chunk = 64;     // pairs per chunk of the pipelined host path, 0 = off
+    int pipe_lanes = 3;      // lanes (workspaces + streams) the chunks rotate over
+    int pipe_trace = 0;      // per-chunk timeline on stderr
+};
+
 struct b2orb_handle {
     b2orb_config cfg{};
+    B2Tuning tune{};
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -138,7 +147,6 @@ struct b2orb_handle {
     uint8_t* d_dflag = nullptr;                          // [npair_cap][cap] depth-gate flags
     double *d_tri_in = nullptr, *d_tri_out = nullptr;    // b2orb_triangulate scratch (grow-only)
     int tri_cap = 0;
-    int pipe_chunk = 64, pipe_lanes = 3;                 // B2ORB_PIPE_CHUNK / B2ORB_PIPE_LANES (chunk 0 = off)
 };
 
 namespace {
@@ -154,6 +162,11 @@ bool cuda_ok(b2orb_handle* h, cudaError_t e, const char* what) {
     do {                                                         \
         if (!cuda_ok((h), (call), #call)) return B2ORB_ERR_CUDA; \
     } while (0)
+
+inline bool pdl_for(const b2orb_handle* h, int nimg) {
+    const int forced = h->root->tune.pdl;
+    return forced >= 0 ? forced != 0 : nimg <= B2_PDL_MAX_IMAGES;
+}
 
 int fail(b2orb_handle* h, int code, const char* msg) {
     if (h) h->err = msg;
@@ -456,30 +469,21 @@ int bind_problems(b2orb_handle* h, int np) {
 int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     const B2Geom& g = h->geom;
     cudaStream_t s = h->stream;
-    b2_pdl_on = pdl_for(nimg);
+    const B2Tuning& tn = h->root->tune;
+    b2_pdl_on = pdl_for(h, nimg);
     // counters first: nothing between the resize chain and the FAST kernel breaks the programmatic launch chain
     B2_CUDA(h, cudaMemsetAsync(h->d_raw_cnt, 0, h->raw_state_bytes, s));
-    // B2ORB_CHAIN=<max images>: the whole resize chain in one cluster launch (pyramid.cu).  Off by default: measured
-    // 38 us for a KITTI pair against ~45 us for the seven programmatically chained launches it replaces, and the
-    // single-pair latency did not move (per-task table loads + cp.async prologue are the floor of every level).  A third
-    // variant (one CTA per row band of the image across all levels, thread per output word, 7 __syncthreads instead of
-    // 7 launches) measured 35 us and was dropped: with programmatic dependent launch the 7 launches cost ~18 us.
-    const int chain_max = [] { const char* e = getenv("B2ORB_CHAIN"); return e ? atoi(e) : 0; }();
-    bool chained = false;
-    if (nimg <= chain_max && g.nlevels > 1) {
-        prof_mark(h, B2ORB_K_RESIZE);
-        chained = b2_launch_pyramid_chain(g, im, h->d_xofs.data(), h->d_xw.data(), h->d_yofs.data(), h->d_yw.data(), nimg, s);
-        if (chained) ++h->launches; else cudaGetLastError();
-    }
-    for (int l = 1; l < g.nlevels && !chained; ++l) {
+    // (Two single-launch versions of the resize chain were measured and removed: one thread-block cluster per image with
+    // barrier.cluster between levels took 38 us for a KITTI pair, a band-per-CTA version 35 us, against ~18 us for the
+    // seven programmatically chained launches below.)
+    for (int l = 1; l < g.nlevels; ++l) {
         prof_mark(h, B2ORB_K_RESIZE);
         b2_launch_resize(g, im, l, h->d_xofs[l], h->d_xw[l], h->d_yofs[l], h->d_yw[l], nimg, s);
         ++h->launches;
     }
     prof_mark(h, -1);
-    // B2ORB_FORK=<max images>: blur on the side stream for latency-sized calls (not while profiling per kernel)
-    const int fork_max = [] { const char* e = getenv("B2ORB_FORK"); return e ? atoi(e) : 8; }();
-    const bool fork = nimg <= fork_max && !h->profiling && h->s_aux;
+    // blur on the side stream for latency-sized calls (not while profiling per kernel)
+    const bool fork = nimg <= tn.fork_max && !h->profiling && h->s_aux;
     if (fork) {
         B2_CUDA(h, cudaEventRecord(h->ev_fork, s));
         B2_CUDA(h, cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
@@ -489,13 +493,13 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     }
     prof_mark(h, B2ORB_K_FAST);
     if (g.total_cells > 0) {
-        b2_launch_fast_score(g, im, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, nimg, s);
+        b2_launch_fast_score(g, im, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, nimg, tn.fast_band, s);
         prof_mark(h, B2ORB_K_FAST_CELLS);
         b2_launch_fast_vote(g, h->d_raw_cand, h->d_raw_cnt, h->d_cell_ini, h->d_cand, h->d_cand_cnt, nimg, s);
         h->launches += 2;
     }
     prof_mark(h, B2ORB_K_OCTREE);
-    b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, nullptr, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, s);
+    b2_launch_octree(g, h->d_cand, h->d_cand_cnt, h->d_pnode, h->d_ot_scratch, h->d_sel, h->d_sel_cnt, nimg, tn.octree_points, s);
     ++h->launches;
     if (fork) {
         B2_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));
@@ -567,7 +571,7 @@ int upload_repack(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt
     const UploadPath path = upload_path(h, w, hgt, step, image_stride, on_device);
     const bool rect = rectifying(h, w, hgt, eye);
     if (!rect && path != UP_DEVICE && path != UP_TIGHT) return B2ORB_OK;
-    b2_pdl_on = pdl_for(2 * count);
+    b2_pdl_on = pdl_for(h, 2 * count);
     uint8_t* dst = h->d_stage + (size_t)slot0 * h->stage_img_bytes;
     const uint8_t* from = path == UP_DEVICE ? src : h->d_raw + (size_t)slot0 * w * hgt;
     const int fstep = path == UP_DEVICE ? step : w;
@@ -727,8 +731,7 @@ bool export_plan(b2orb_handle* h, int np, const b2orb_stereo_out* o, B2ExportPla
 // Results of `np` pairs to the caller and wait: direct export for latency-sized calls with pinned outputs, else the
 // copy path (b2orb_stereo_download).
 int finish_outputs(b2orb_handle* h, int np, const b2orb_stereo_out* o) {
-    const int export_max = [] { const char* e = getenv("B2ORB_EXPORT"); return e ? atoi(e) : 4; }();
-    if (o && np <= export_max && o->cap >= h->geom.kp_cap) {
+    if (o && np <= h->root->tune.export_max && o->cap >= h->geom.kp_cap) {
         static_assert(sizeof(B2ExportPlan) < 3500, "plan must fit the kernel parameter space");
         // The pointer attributes are queried on every call (a few hundred ns each): a cached verdict would go stale when
         // the caller frees a pinned array and a pageable one lands on the same address, or toggles b2orb_set_projection.
@@ -789,8 +792,6 @@ int b2orb_create(b2orb_handle** out, int device, const b2orb_config* cfg) {
     cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming);
     h->root = h;
-    if (const char* e = getenv("B2ORB_PIPE_CHUNK")) h->pipe_chunk = std::max(0, atoi(e));
-    if (const char* e = getenv("B2ORB_PIPE_LANES")) h->pipe_lanes = std::min(std::max(2, atoi(e)), 8);
     build_ctor_tables(h);
     return configure(h, cfg->max_width, cfg->max_height);
 }
@@ -1001,8 +1002,8 @@ int b2orb_stereo_download(b2orb_handle* h, int npairs, const b2orb_stereo_out* o
 static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs,
                                      int width, int height, int step, size_t image_stride, int temporal,
                                      const b2orb_stereo_out* out) {
-    const int chunk = h->pipe_chunk;
-    while ((int)h->lanes.size() < h->pipe_lanes) {
+    const int chunk = h->tune.pipe_chunk;
+    while ((int)h->lanes.size() < h->tune.pipe_lanes) {
         b2orb_config c = h->cfg;
         c.max_images = 2 * chunk;
         b2orb_handle* l = nullptr;
@@ -1012,7 +1013,6 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
             return rc;
         }
         l->root = h;
-        l->pipe_chunk = 0;
         h->lanes.push_back(l);
     }
     if (!h->s_in) {
@@ -1024,7 +1024,7 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
     B2_CUDA(h, cudaStreamWaitEvent(h->s_in, h->ev0, 0));   // ordered after earlier work on this handle
     const size_t cap = out->cap;
     int k = 0, rc = B2ORB_OK;
-    const bool trace = getenv("B2ORB_PIPE_TRACE") != nullptr;   // debugging aid: per-chunk timeline on stderr
+    const bool trace = h->tune.pipe_trace != 0;   // debugging aid: per-chunk timeline on stderr
     struct Tr { cudaEvent_t e[4]; double h0, h1; };
     std::vector<Tr> tr;
     const auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
@@ -1098,7 +1098,7 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
     if (npairs == 1) image_stride = (size_t)step * height;   // unused for one pair: keep the one-copy upload paths
     B2_CUDA(h, cudaSetDevice(h->device));
-    if (h->pipe_chunk > 0 && npairs > h->pipe_chunk && h->root == h)
+    if (h->tune.pipe_chunk > 0 && npairs > h->tune.pipe_chunk && h->root == h)
         return stereo_frontend_pipelined(h, images_l, images_r, npairs, width, height, step, image_stride, temporal, out);
     int rc = configure(h, width, height);
     if (rc) return rc;
@@ -1422,6 +1422,25 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
         B2_CUDA(h, cudaMemcpyAsync(circ_hist, d_ch, (size_t)out[0] * 4, cudaMemcpyDeviceToHost, s));
         B2_CUDA(h, cudaStreamSynchronize(s));
     }
+    return B2ORB_OK;
+}
+
+// ---- per-handle launch-time options (tests, A/B runs) ---------------------------------------------
+int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
+    if (!h || !key || h->root != h) return B2ORB_ERR_INVALID;
+    B2Tuning& t = h->tune;
+    const std::string k(key);
+    if (k == "pdl") t.pdl = value < 0 ? -1 : (value ? 1 : 0);
+    else if (k == "fork_max") t.fork_max = value;
+    else if (k == "export_max") t.export_max = value;
+    else if (k == "fast_band") t.fast_band = value;
+    else if (k == "octree_points") t.octree_points = value ? 1 : 0;
+    else if (k == "pipe_trace") t.pipe_trace = value;
+    else if (k == "pipe_chunk" || k == "pipe_lanes") {
+        if (!h->lanes.empty()) return fail(h, B2ORB_ERR_INVALID, "pipeline options must be set before the first pipelined call");
+        if (k == "pipe_chunk") t.pipe_chunk = std::max(0, value);
+        else t.pipe_lanes = std::min(std::max(2, value), 8);
+    } else return fail(h, B2ORB_ERR_INVALID, "unknown option");
     return B2ORB_OK;
 }
 

@@ -32,7 +32,6 @@
 //   (warp-aggregated atomics).  Candidate order is irrelevant downstream: the quadtree breaks response ties with
 //   a key that reproduces the reference's cell-row-major order.
 #include <cuda_fp16.h>
-#include <cstdlib>
 #include "b2orb_internal.cuh"
 
 namespace {
@@ -117,191 +116,11 @@ __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
     return b & (one * 255u);
 }
 
-template <int NQ, int NE>
-__global__ void __launch_bounds__(FS_WARPS * 32, 4)
-fast_score_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2* __restrict__ raw_list,
-                  int* __restrict__ raw_cnt, uint8_t* __restrict__ cell_ini, int variant) {
-    b2_pdl_wait();
-    __shared__ uint2 s_queue[FS_WARPS][FS_QUEUE];
-    __shared__ unsigned s_ring[FS_WARPS][7][32];
-    const int lane = threadIdx.x & 31;
-    const int task = blockIdx.x * FS_WARPS + (threadIdx.x >> 5);
-    if (task >= g.total_fast_tasks[variant]) return;
-    const int band_rows = B2_FAST_BAND << variant;
-    const int b = blockIdx.y;
-    int level = 0;
-    while (level + 1 < g.nlevels && task >= g.lv[level + 1].fast_task_base[variant]) ++level;
-    const B2Level& L = g.lv[level];
-    const int t = task - L.fast_task_base[variant];
-    const int band = t / L.fast_strips, strip = t - band * L.fast_strips;
-    int pitch;
-    const uint8_t* img = b2_level_ptr(g, im, b, level, pitch);
-    uint2* queue = s_queue[threadIdx.x >> 5];
-    int qn = 0;                                                // queue fill, warp-uniform
-    uint2* out = raw_list + (size_t)b * g.cand_total + L.cand_off;
-    int* out_cnt = raw_cnt + b * g.nlevels + level;
-    uint8_t* flags = cell_ini + (size_t)b * g.total_cells + L.cell_base;
-    const int w = L.w, h = L.h;
-    const int x = B2_BORDER - 4 + strip * 120 + lane * 4;      // lanes 1..30 own columns x .. x+3
-    const int ya = B2_EDGE + band * band_rows;                 // M rows [ya, yb)
-    const int yb = min(ya + band_rows, h - B2_EDGE);
-    const int nsteps = yb - ya + 8;                            // pixel rows ya-4 .. yb+3
-    const int xo = min(x, pitch - 4);
-    const uint8_t* col = img + xo;
-
-    // column masks of this lane's pixels (x, x+2 | x+1, x+3): inside [19, w-19), left / right neighbour in the same cell
-    unsigned inE = 0, inO = 0, mlE = 0, mlO = 0, mrE = 0, mrO = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int X = x + j;
-        const bool in = X >= B2_EDGE && X < w - B2_EDGE;
-        const int cx = (X - B2_EDGE) % L.w_cell;
-        const bool left = in && cx != 0;
-        const bool right = in && cx != L.w_cell - 1 && X + 1 < w - B2_EDGE;
-        const unsigned lanebits = (j & 2) ? 0xFFFF0000u : 0x0000FFFFu;
-        if (j & 1) { if (in) inO |= lanebits; if (left) mlO |= lanebits; if (right) mrO |= lanebits; }
-        else       { if (in) inE |= lanebits; if (left) mlE |= lanebits; if (right) mrE |= lanebits; }
-    }
-    // cell column of pixel 0 and which of the 4 pixels share it (a lane spans at most two cells: w_cell >= 30)
-    const int cjA = max(x - B2_EDGE, 0) / L.w_cell;
-    unsigned sameA = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-        if (max(x + j - B2_EDGE, 0) / L.w_cell == cjA) sameA |= 1u << j;
-    const unsigned kini = 0x00FF00FFu - (unsigned)g.ini_th * 0x00010001u;   // (o + kini) bit 8 per lane: o > ini
-    const unsigned lt_mask = (1u << lane) - 1;
-    unsigned accE = 0, accO = 0;
-    const unsigned thr2 = (unsigned)g.min_th * 0x00010001u;
-    const bool store_lane = lane >= 1 && lane <= 30 && x < w - B2_BORDER;   // b valid on lanes 1..30 + the facing pixels of 0 and 31
-
-    unsigned P[7][8];            // pairs (p[a], p[a+2]) for a = x-3 .. x+4, last 7 rows
-    // Rows are addressed by a 32-bit offset that is clamped to the last row of the band, so the prefetch needs no
-    // branch; pixel row r of the band sits at col0 + r * pitch.  Each lane stages its own word of the next FS_PF
-    // rows with 4-byte cp.async into a private shared-memory slot: async-copy groups complete in order, so waiting
-    // for row r never waits for the rows issued after it (plain loads share scoreboards and did, see blur.cu).
-    const uint8_t* col0 = col + (size_t)(ya - 4) * pitch;
-    const unsigned offmax = (unsigned)(nsteps - 1) * (unsigned)pitch;
-    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(&s_ring[threadIdx.x >> 5][0][lane]);
-    unsigned off = 0;
-#pragma unroll
-    for (int i = 0; i < FS_PF; ++i) {
-        fs_cp_async4(ring_s + i * 128, col0 + min(off, offmax));
-        off += pitch;
-    }
-#define B2_FAST_PAIRS(p)                                                                                        \
-    {                                                                                                           \
-        fs_cp_async4(ring_s + (((p) + FS_PF) % 7) * 128, col0 + min(off, offmax));                              \
-        off += pitch;                                                                                           \
-        const unsigned R1 = fs_wait_lds(ring_s + (p) * 128);                                                    \
-        const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);                      \
-        const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);    \
-        const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                      \
-        const unsigned Ep = __shfl_up_sync(0xFFFFFFFFu, E1, 1), Op = __shfl_up_sync(0xFFFFFFFFu, O1, 1);        \
-        P[p][0] = Op;                                           /* (x-3, x-1) */                                \
-        P[p][1] = __byte_perm(Ep, E1, 0x5432);                  /* (x-2, x): high half is this lane's own pixel */ \
-        P[p][2] = __byte_perm(Op, O1, 0x5432);                  /* (x-1, x+1) */                                \
-        P[p][3] = E1; P[p][4] = O1; P[p][5] = c2; P[p][6] = c3; P[p][7] = E2;                                   \
-    }
-    // prologue: pixel rows 0..5 only fill the window
-#pragma unroll
-    for (int p = 0; p < 6; ++p) B2_FAST_PAIRS(p)
-
-    // NMS state: rows s-2 (rm only), s-1 (pending centre), s (newest)
-    unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
-    int y = ya;
-    int ci = (band * band_rows) / L.h_cell;                    // cell row of y, and row of y inside its cell
-    int cy = band * band_rows - ci * L.h_cell;
-    // queue entry position word: x - 16 | (y - 16) << 12 | cell row << 24, advanced incrementally
-    unsigned meta = (unsigned)(x - B2_BORDER) | ((unsigned)(ya - B2_BORDER) << 12) | ((unsigned)ci << 24);
-    const int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
-
-    // "b > ini seen" bits of this lane's 4 pixels -> the (at most two) cells they belong to
-#define B2_FAST_FLAGS()                                                                                        \
-    {                                                                                                           \
-        const unsigned hit = ((accE >> 8) & 1u) | ((accO >> 7) & 2u) | ((accE >> 22) & 4u) | ((accO >> 21) & 8u); \
-        if (store_lane && (hit & sameA)) flags[ci * L.n_cols + cjA] = 1;                                       \
-        if (store_lane && (hit & ~sameA)) flags[ci * L.n_cols + cjA + 1] = 1;                                  \
-        accE = accO = 0;                                                                                        \
-    }
-    /* queue -> raw list: one global atomic per flush, coalesced 8-byte copies */
-#define B2_FAST_FLUSH()                                                                                        \
-    {                                                                                                           \
-        __syncwarp();                                                                                           \
-        if (qn) {                                                                                               \
-            int base = 0;                                                                                       \
-            if (lane == 0) base = atomicAdd(out_cnt, qn);                                                       \
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);                                                           \
-            for (int i = lane; i < qn; i += 32)                                                                 \
-                if (base + i < L.cand_cap) out[base + i] = queue[i];                                            \
-            __syncwarp();                                                                                       \
-            qn = 0;                                                                                             \
-        }                                                                                                       \
-    }
-#define B2_FAST_STEP(p, OUT)                                                                                   \
-    {                                                                                                           \
-        B2_FAST_PAIRS(p)                                                                                     \
-        const int s3 = p, s2 = (p + 6) % 7, s1 = (p + 5) % 7, s0 = (p + 4) % 7, t1 = (p + 3) % 7,            \
-                  t2 = (p + 2) % 7, t3 = (p + 1) % 7;                                                        \
-        unsigned bE, bO;                                                                                     \
-        {                                                                                                    \
-            const unsigned v[16] = {P[s3][3], P[s3][4], P[s2][5], P[s1][6], P[s0][6], P[t1][6], P[t2][5], P[t3][4], \
-                                    P[t3][3], P[t3][2], P[t2][1], P[t1][0], P[s0][0], P[s1][0], P[s2][1], P[s3][2]}; \
-            bE = fast_b_pair<NQ, NE>(v, P[s0][3]);                                                                   \
-        }                                                                                                    \
-        {                                                                                                    \
-            const unsigned v[16] = {P[s3][4], P[s3][5], P[s2][6], P[s1][7], P[s0][7], P[t1][7], P[t2][6], P[t3][5], \
-                                    P[t3][4], P[t3][3], P[t2][2], P[t1][1], P[s0][1], P[s1][1], P[s2][2], P[s3][3]}; \
-            bO = fast_b_pair<NQ, NE>(v, P[s0][4]);                                                                   \
-        }                                                                                                    \
-        const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1); \
-        const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;                                              \
-        const unsigned rE = bO & mrE;                                                                        \
-        const unsigned lO = bE & mlO;                                                                        \
-        const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;                                              \
-        const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);                                     \
-        if (OUT) {                                                                                           \
-            const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;                                                  \
-            const unsigned dn = (cy != hcell1 && y != ylast) ? 0xFFFFFFFFu : 0u;                             \
-            const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2));                            \
-            const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2));                            \
-            const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;     \
-            const unsigned m4 = __byte_perm(oE, oO, 0x6240);                                                 \
-            accE |= oE + kini; accO |= oO + kini;                                                            \
-            const bool has = store_lane && m4 != 0;                                                          \
-            const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);                                            \
-            if (has) queue[qn + __popc(bal & lt_mask)] = make_uint2(m4, meta);                               \
-            qn += __popc(bal);                                                                               \
-            ++y;                                                                                             \
-            meta += 0x1000u;                                                                                 \
-            if (cy == hcell1) { B2_FAST_FLAGS() cy = 0; ++ci; meta += 0x1000000u; } else ++cy;               \
-        }                                                                                                    \
-        rmE_a = rmE_b; rmO_a = rmO_b;                                                                        \
-        rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;                                                      \
-        sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);                                                        \
-    }
-    // score rows ya-1 and ya only prime the NMS window (pixel rows r = 6, 7); outputs start at r = 8
-    if (6 < nsteps) B2_FAST_STEP(6, false)
-    if (7 < nsteps) B2_FAST_STEP(0, false)
-    for (int base = 8; base < nsteps; base += 7) {
-#pragma unroll
-        for (int q = 0; q < 7; ++q) {
-            if (base + q < nsteps) B2_FAST_STEP((1 + q) % 7, true)
-        }
-        B2_FAST_FLUSH()
-    }
-    B2_FAST_FLAGS()
-#undef B2_FAST_STEP
-#undef B2_FAST_PAIRS
-#undef B2_FAST_FLAGS
-#undef B2_FAST_FLUSH
-}
-
 // ---------------------------------------------------------------------------------------------------
-// fast_score_win_kernel — same strip / lane ownership, arithmetic, NMS, queue and flag logic as above, but the 7-row
-// window of pixel pairs lives in SHARED memory instead of registers.  Why: the register window forces a 7-phase
-// unrolled loop (static register indices), 36-40 KB of SASS for the loop alone — more than the 32 KB instruction
-// cache level, and ncu showed "no instruction" as the top stall once the min/max work was spread over both math
-// pipes.  Here the loop body exists once (~5 KB): each lane keeps its 8 pairs of the six older rows in a private
+// fast_score_win_kernel — the 7-row window of pixel pairs lives in SHARED memory, not registers.  Why: a register
+// window forces a 7-phase unrolled loop (static register indices), 36-40 KB of SASS for the loop alone — more than
+// the 32 KB instruction cache level, and ncu showed "no instruction" as the top stall of that first version (removed;
+// git history).  Here the loop body exists once (~5 KB): each lane keeps its 8 pairs of the six older rows in a private
 // 6-slot ring (two 16-byte units per row: Q = pairs 2,5,3,4, W = pairs 1,6,0,7; lane stride 16 B, conflict-free
 // LDS.128 / STS.128), re-reads the 9 units the ring pixels of this step need, and overwrites the oldest slot with the
 // new row.  Slot addresses rotate through six registers (moves on the FMA pipe).  Only the lane itself reads what it
@@ -594,29 +413,17 @@ fast_vote_kernel(const __grid_constant__ B2Geom g, const uint2* __restrict__ raw
 }  // namespace
 
 void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* raw_cnt, uint8_t* cell_ini, int nimg,
-                          cudaStream_t s) {
+                          int forced_band, cudaStream_t s) {
     if (g.total_fast_tasks[0] <= 0) return;
-    const int forced = [] { const char* e = getenv("B2ORB_FAST_BAND"); return e ? atoi(e) : -1; }();   // A/B runs
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
     // and short ones while a 32-row launch would not even give every SM two CTAs (per-CTA latency is what counts then)
     int variant = (long long)g.total_fast_tasks[2] * nimg >= 148LL * 16 * 4 ? 2
                   : (long long)g.total_fast_tasks[1] * nimg >= 148LL * 2 * 4 ? 1 : 0;
-    if (forced >= 0 && forced < B2_FAST_VARIANTS) variant = forced;
+    if (forced_band >= 0 && forced_band < B2_FAST_VARIANTS) variant = forced_band;   // b2orb_debug_set("fast_band")
     dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);
-    // Default: shared-memory window kernel, first-layer (min, max) pairs on the FMA pipe.  A/B switches:
-    // B2ORB_FAST=regs -> the register-window kernel (all min/max on the ALU pipe); B2ORB_FAST_FMA=<NQ><NE> -> how many
-    // first-layer / arc-end pairs of the window kernel use the FMA pipe (0, 80, 88).
-    const int mix = [] { const char* e = getenv("B2ORB_FAST_FMA"); return e ? atoi(e) : 80; }();
-    const bool regs = [] { const char* e = getenv("B2ORB_FAST"); return e && e[0] == 'r'; }();
-    const dim3 block(FS_WARPS * 32);
-    if (regs)
-        b2_launch_pdl(fast_score_kernel<0, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
-    else if (mix == 0)
-        b2_launch_pdl(fast_score_win_kernel<0, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
-    else if (mix == 88)
-        b2_launch_pdl(fast_score_win_kernel<8, 8>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
-    else
-        b2_launch_pdl(fast_score_win_kernel<8, 0>, dim3(grid), block, 0, s, g, im, raw, raw_cnt, cell_ini, variant);
+    // the 8 first-layer (min, max) pairs on the FMA pipe, everything else on the ALU pipe: every other mix that was
+    // measured (0 / 8 / 16 pairs) landed within 1 %, the kernel runs at the mixed-issue limit
+    b2_launch_pdl(fast_score_win_kernel<8, 0>, dim3(grid), dim3(FS_WARPS * 32), 0, s, g, im, raw, raw_cnt, cell_ini, variant);
 }
 
 void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, const uint8_t* cell_ini, uint32_t* cand,

@@ -1,144 +1,18 @@
 // Brute-force Hamming matching and the FeatureTracker filters.
-//   * match_kernel — cv::BFMatcher(cv::NORM_HAMMING).match(query, train), src/feature-tracker.cpp:161-163,
+//   * match_tc_kernel — cv::BFMatcher(cv::NORM_HAMMING).match(query, train), src/feature-tracker.cpp:161-163,
 //     :258, :303 (K9): for every query row the nearest train row by popcount(q xor t) over 32-byte
-//     descriptors; train rows are scanned in ascending order with a strict '<' update, so the lowest
-//     train index wins ties exactly like OpenCV's batch-distance loop.  q.t on the tensor pipe (u8 IMMA).
+//     descriptors; the lowest train index wins ties exactly like OpenCV's batch-distance loop (strict '<' in
+//     ascending train order).  The distance is a dense contraction and runs on tcgen05 (see below).  Two earlier
+//     versions were measured and removed (git history): POPC + carry-save tree on the XU pipe 5.0 us per
+//     KITTI pair, warp-level mma.sync.m16n8k32.u8 2.5 us; this one 1.3 us.
 //   * stereo_filter_kernel — internalMatch, :164 and :208-218 (K10): global minDist, keep
 //     dist < max(matchRatio*minDist, minMatchDist) && |yL - yR| < maxVerticalPixelDist (fp32), ordered
 //     compaction in query order, gather of the kept descriptor rows (_curDescriptorsL/R).
 //   * circular_kernel — externalTrack, :258-259, 293-296, 303-321 (useRANSAC=false): distance filter on both
 //     sides and the circular test mapCurHist[queryIdx] == trainIdx.
-#include <cstdlib>
-
 #include "b2orb_internal.cuh"
 
 namespace {
-
-constexpr int MT_WARPS = 4;
-constexpr int MT_THREADS = MT_WARPS * 32;
-constexpr int MT_QPW = 32;                    // query rows per warp: two m16 tiles
-constexpr int MT_QPC = MT_WARPS * MT_QPW;     // query rows per CTA
-constexpr int MT_TILE = 1024;                 // train rows staged in shared memory per pass
-
-// The distance is a dense contraction: popcount(q xor t) = |q| + |t| - 2 q.t with q, t in {0,1}^256.  POPC
-// issues on the quarter-rate XU pipe (the plain loop was 92 % XU-bound, 5 us per stereo pair even with a
-// carry-save tree), so q.t runs on the tensor pipe as a u8 x u8 -> s32 warp-level MMA (mma.sync m16n8k32,
-// IMMA.16832.U8.U8 in SASS; measured 0.47 IMMA/clk/SM on B200, tools/ubench/imma.cu).  Bits are expanded to
-// bytes in registers with ONE LOP3 per fragment register by giving a set bit j the weight 2^j on the train side
-// and 2^(7-j) on the query side, so every matching bit pair contributes exactly 128 to the accumulator (the k
-// order of an MMA is free as long as both operands use the same one: fragment byte i of thread t in k-step s is
-// descriptor bit 8i + t (+4 for the upper half) of 32-bit word s).
-__device__ __forceinline__ void imma_16832(int (&d)[4], const unsigned (&a)[4], unsigned b0, unsigned b1, const int (&c)[4]) {
-    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
-                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]));
-}
-
-// query side: bit j of every byte of w -> value 2^(7-j) in that byte
-__device__ __forceinline__ unsigned expand_q(unsigned w, int j) {
-    const unsigned x = w & (0x01010101u << j);
-    return j <= 3 ? x << (7 - 2 * j) : x >> (2 * j - 7);
-}
-
-__global__ void __launch_bounds__(MT_THREADS, 4)
-match_kernel(const B2MatchProblem* __restrict__ probs) {
-    b2_pdl_wait();
-    __shared__ __align__(16) unsigned s_bits[MT_TILE * 8];   // train descriptors of the current pass
-    __shared__ __align__(8) int s_cn[MT_TILE];                // (|t| << 22) + global train index, INT_MAX beyond nt
-    const B2MatchProblem P = probs[blockIdx.y];
-    const int nq = *P.nq, nt = *P.nt;
-    const int q0 = blockIdx.x * MT_QPC;
-    if (q0 >= nq) return;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const int qw0 = q0 + wid * MT_QPW;                          // first query row of this warp
-
-    // ---- query fragments, resident for the whole kernel: rows qw0 + 16*m + g and + 8 ----
-    unsigned A[2][8][4];
-    int qpop[2][2];
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-#pragma unroll
-        for (int hrow = 0; hrow < 2; ++hrow) {
-            const int row = qw0 + 16 * m + 8 * hrow + g;
-            uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
-            if (row < nq) {
-                const uint4* qp = reinterpret_cast<const uint4*>(P.q + (size_t)row * 32);
-                lo = qp[0];
-                hi = qp[1];
-            }
-            const unsigned w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-            int pc = 0;
-#pragma unroll
-            for (int s = 0; s < 8; ++s) {
-                A[m][s][hrow] = expand_q(w[s], t);
-                A[m][s][2 + hrow] = expand_q(w[s], 4 + t);
-                pc += __popc(w[s]);
-            }
-            qpop[m][hrow] = pc;
-        }
-    }
-    const unsigned mask0 = 0x01010101u << t, mask1 = 0x01010101u << (4 + t);
-    const int zero[4] = {0, 0, 0, 0};
-    // best[m][hrow] = min over train columns of ((|t| - 2 q.t) << 22) + train index  (signed; ascending scan with
-    // strict '<' of BFMatcher == lexicographic min over (distance, index))
-    int best[2][2] = {{0x7FFFFFFF, 0x7FFFFFFF}, {0x7FFFFFFF, 0x7FFFFFFF}};
-
-    for (int t0 = 0; t0 < nt; t0 += MT_TILE) {
-        const int n = min(MT_TILE, nt - t0);
-        const int ntile8 = (n + 7) >> 3;
-        __syncthreads();
-        {   // stage: 8 words per train row (zeros beyond nt), then the per-row constant
-            const uint4* tp = reinterpret_cast<const uint4*>(P.t + (size_t)t0 * 32);
-            uint4* sb = reinterpret_cast<uint4*>(s_bits);
-            for (int i = threadIdx.x; i < ntile8 * 16; i += MT_THREADS) sb[i] = i < 2 * n ? tp[i] : make_uint4(0, 0, 0, 0);
-        }
-        __syncthreads();
-        for (int i = threadIdx.x; i < ntile8 * 8; i += MT_THREADS) {
-            int pc = 0;
-#pragma unroll
-            for (int s = 0; s < 8; ++s) pc += __popc(s_bits[i * 8 + s]);
-            s_cn[i] = i < n ? (pc << 22) + (t0 + i) : 0x7FFFFFFF;
-        }
-        __syncthreads();
-#pragma unroll 2
-        for (int j = 0; j < ntile8; ++j) {
-            // train row 8j + g: the four threads of a group read the same 32 bytes (broadcast)
-            const uint4* tr = reinterpret_cast<const uint4*>(s_bits + (size_t)(8 * j + g) * 8);
-            const uint4 lo = tr[0], hi = tr[1];
-            const unsigned w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-            int acc0[4], acc1[4];
-            imma_16832(acc0, A[0][0], w[0] & mask0, w[0] & mask1, zero);
-            imma_16832(acc1, A[1][0], w[0] & mask0, w[0] & mask1, zero);
-#pragma unroll
-            for (int s = 1; s < 8; ++s) {
-                const unsigned b0 = w[s] & mask0, b1 = w[s] & mask1;
-                imma_16832(acc0, A[0][s], b0, b1, acc0);
-                imma_16832(acc1, A[1][s], b0, b1, acc1);
-            }
-            // accumulator = 128 q.t ; key = cn - (q.t << 23) = cn - acc * 65536   (columns 2t, 2t+1 of this tile)
-            const int2 cn = *reinterpret_cast<const int2*>(s_cn + 8 * j + 2 * t);
-            best[0][0] = min(best[0][0], min(cn.x - acc0[0] * 65536, cn.y - acc0[1] * 65536));
-            best[0][1] = min(best[0][1], min(cn.x - acc0[2] * 65536, cn.y - acc0[3] * 65536));
-            best[1][0] = min(best[1][0], min(cn.x - acc1[0] * 65536, cn.y - acc1[1] * 65536));
-            best[1][1] = min(best[1][1], min(cn.x - acc1[2] * 65536, cn.y - acc1[3] * 65536));
-        }
-    }
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-#pragma unroll
-        for (int hrow = 0; hrow < 2; ++hrow) {
-            int v = best[m][hrow];
-            v = min(v, __shfl_xor_sync(0xFFFFFFFFu, v, 1));
-            v = min(v, __shfl_xor_sync(0xFFFFFFFFu, v, 2));
-            const int row = qw0 + 16 * m + 8 * hrow + g;
-            if (t == 0 && row < nq) {
-                P.train_idx[row] = nt > 0 ? (v & 0x3FFFFF) : -1;
-                P.dist[row] = nt > 0 ? (v >> 22) + qpop[m][hrow] : 0x7fffffff;
-            }
-        }
-    }
-}
 
 constexpr int SF_THREADS = 1024;   // one CTA per pair: the passes over ~2000 matches are latency chains, so use the widest CTA
 
@@ -478,12 +352,6 @@ void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStr
 
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s) {
     if (nprob <= 0 || max_nq <= 0) return;
-    static const bool use_imma = [] { const char* e = getenv("B2ORB_MATCH"); return e && e[0] == 'i'; }();
-    if (use_imma) {   // warp-level IMMA version, kept for A/B measurements (B2ORB_MATCH=imma)
-        dim3 grid((max_nq + MT_QPC - 1) / MT_QPC, nprob);
-        b2_launch_pdl(match_kernel, dim3(grid), dim3(MT_THREADS), 0, s, probs);
-        return;
-    }
     const int smem = 3 * TC_TILE;
     cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device; cheap
     dim3 grid((max_nq + TC_ROWS - 1) / TC_ROWS, nprob);

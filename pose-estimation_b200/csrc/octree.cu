@@ -27,8 +27,6 @@
 //  * POINT PASSES (fallback, the first version): every round moves every point to its new node and counts it into
 //    that node's children.  Used when the level has few points, and when a node at depth D still has to be split
 //    (sparse, clustered points), in which case the level is simply redone this way.
-#include <cstdlib>
-#include <cstring>
 #include "b2orb_internal.cuh"
 
 namespace {
@@ -609,15 +607,12 @@ int b2_octree_scratch_words(const B2Geom& g) {
 }
 
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
-                      B2Node* nodes, unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, cudaStream_t s) {
-    (void)nodes;
+                      unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, int force_legacy, cudaStream_t s) {
     const size_t smem = (size_t)b2_octree_scratch_words(g) * sizeof(unsigned);
     const int use_global = scratch != nullptr;
     if (!use_global && smem > 24 * 1024)   // static (tables) + dynamic above 48 KB needs the opt-in; per-device
                                            // attribute, cheap enough to set on every launch
         cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    const char* mode = getenv("B2ORB_OCTREE");   // "points" = point passes only (A/B runs, tests of the fallback path)
-    const int force_legacy = mode && !strcmp(mode, "points") ? 1 : 0;
     dim3 grid(g.nlevels, nimg);
     b2_launch_pdl(octree_kernel, dim3(grid), dim3(OT_THREADS), use_global ? 0 : smem, s, g, cand, cand_cnt, pnode, scratch, use_global, sel,
                                                               sel_cnt, force_legacy);

@@ -226,44 +226,6 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
                 s_ring[threadIdx.x >> 5]);
 }
 
-// Latency path (a few images per call): the seven per-level launches above are a chain of tiny dependent kernels, ~8 us
-// each for one stereo pair.  Here ONE thread-block cluster per image walks the whole chain: the cluster's warps share
-// the (band, strip) tasks of level l, then meet at a cluster barrier (arrive.release / wait.acquire orders the global
-// stores of level l before the cp.async.cg reads of level l+1, which bypass L1) and go on to level l+1.
-constexpr int PC_WARPS = 8;
-struct B2ResizeTables {
-    const int* xofs[B2_MAX_LEVELS];
-    const short* xw[B2_MAX_LEVELS];
-    const int* yofs[B2_MAX_LEVELS];
-    const short* yw[B2_MAX_LEVELS];
-};
-
-__global__ void __launch_bounds__(PC_WARPS * 32)
-pyramid_chain_kernel(const __grid_constant__ B2Geom g, const B2Images im, const __grid_constant__ B2ResizeTables tb) {
-    b2_pdl_wait();
-    __shared__ __align__(16) uint8_t s_ring[PC_WARPS][RS_SLOTS * RS_ROWB];
-    unsigned crank, csize;
-    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
-    asm("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
-    const int wid = threadIdx.x >> 5;
-    const int cw = (int)crank * PC_WARPS + wid, ncw = (int)csize * PC_WARPS;
-    const int b = blockIdx.y;
-    for (int level = 1; level < g.nlevels; ++level) {
-        const B2Level& L = g.lv[level];
-        const int strips = (L.w + 127) >> 7;
-        const int nb = max(ncw / strips, 1);
-        const int band = max((L.h + nb - 1) / nb, 4);
-        const int tasks = strips * ((L.h + band - 1) / band);
-        for (int task = cw; task < tasks; task += ncw) {
-            resize_task(g, im, b, level, band, task, tb.xofs[level], tb.xw[level], tb.yofs[level], tb.yw[level], s_ring[wid]);
-            rs_wait<0>();
-            __syncwarp();
-        }
-        if (level + 1 < g.nlevels)
-            asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-    }
-}
-
 // cv::resize(INTER_LINEAR) to 2*half_w x dh -> cvtColor(BGR2GRAY) -> left / right halves, fused: one thread per output
 // word of one eye; four 32-bit pixel loads per output pixel, the Q11 resize arithmetic of resize_kernel per channel
 // (H = S0*wx0 + S1*wx1;  v = ((wy0*(H0>>4))>>16) + ((wy1*(H1>>4))>>16) + 2) >> 2), then OpenCV 4.x's 15-bit grey
@@ -338,45 +300,6 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
     const int tasks = strips * ((L.h + band - 1) / band);
     dim3 grid((tasks + RS_WARPS - 1) / RS_WARPS, nimg);
     b2_launch_pdl(resize_kernel, dim3(grid), dim3(RS_WARPS * 32), 0, s, g, im, level, band, xofs, xw, yofs, yw);
-}
-
-// Whole resize chain in one launch (latency path).  Returns false when the cluster launch is not available, and the
-// caller falls back to the per-level launches.
-bool b2_launch_pyramid_chain(const B2Geom& g, const B2Images& im, int* const* xofs, short* const* xw, int* const* yofs,
-                             short* const* yw, int nimg, cudaStream_t s) {
-    static int cluster = -1;    // largest usable cluster size (16, 8) or 0
-    if (cluster < 0) {
-        cluster = 0;
-        if (cudaFuncSetAttribute(pyramid_chain_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
-            cudaGetLastError();
-        for (int c : {16, 8}) {
-            cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3(c, 1);
-            cfg.blockDim = dim3(PC_WARPS * 32);
-            cudaLaunchAttribute a[1];
-            a[0].id = cudaLaunchAttributeClusterDimension;
-            a[0].val.clusterDim.x = c; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
-            cfg.attrs = a; cfg.numAttrs = 1;
-            int n = 0;
-            if (cudaOccupancyMaxActiveClusters(&n, pyramid_chain_kernel, &cfg) == cudaSuccess && n > 0) { cluster = c; break; }
-            cudaGetLastError();
-        }
-    }
-    if (cluster == 0) return false;
-    B2ResizeTables tb = {};
-    for (int l = 1; l < g.nlevels; ++l) { tb.xofs[l] = xofs[l]; tb.xw[l] = xw[l]; tb.yofs[l] = yofs[l]; tb.yw[l] = yw[l]; }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(cluster, nimg);
-    cfg.blockDim = dim3(PC_WARPS * 32);
-    cfg.stream = s;
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[1].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = b2_pdl_on ? 2 : 1;
-    return cudaLaunchKernelEx(&cfg, pyramid_chain_kernel, g, im, tb) == cudaSuccess;
 }
 
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,

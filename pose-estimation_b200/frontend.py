@@ -106,6 +106,8 @@ def lib():
         L.b2orb_debug_get_level.argtypes = [vp, i32, i32, i32, vp]
         L.b2orb_debug_get_candidates.restype = i32
         L.b2orb_debug_get_candidates.argtypes = [vp, i32, i32, vp, i32, C.POINTER(i32)]
+        L.b2orb_debug_set.restype = i32
+        L.b2orb_debug_set.argtypes = [vp, C.c_char_p, i32]
         L.b2orb_debug_octree_fallbacks.restype = C.c_uint64
         L.b2orb_debug_octree_fallbacks.argtypes = [vp]
         L.b2orb_stream.restype = vp
@@ -365,6 +367,11 @@ class Handle:
         self.L.b2orb_reset_history(self.h)
 
     # ---- debug
+    def debug_set(self, key, value):
+        """Pin a launch-time choice on this handle (include/b2orb.h: b2orb_debug_set)."""
+        self.check(self.L.b2orb_debug_set(self.h, key.encode(), int(value)))
+        return self
+
     def debug_level(self, slot, level, blurred=False):
         w, hh = C.c_int(), C.c_int()
         self.check(self.L.b2orb_debug_level_size(self.h, level, C.byref(w), C.byref(hh)))

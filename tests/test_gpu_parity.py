@@ -64,19 +64,18 @@ def test_extract_stages_match_oracle(case, fe, oracle, synth):
 
 
 @pytest.mark.parametrize("mode", ["", "points"])
-def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth, monkeypatch):
-    """The quadtree has two sources of child counts (octree.cu): the count pyramid and the point passes (B2ORB_OCTREE=
-    points forces the latter).  Both must reproduce DistributeOctTree; the second image packs all texture into two
-    small patches, so nodes below the pyramid's depth have to be split and the kernel redoes those levels with point
-    passes on its own."""
-    monkeypatch.setenv("B2ORB_OCTREE", mode)
+def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth):
+    """The quadtree has two sources of child counts (octree.cu): the count pyramid and the point passes
+    (debug_set("octree_points", 1) forces the latter).  Both must reproduce DistributeOctTree; the second image packs
+    all texture into a few small patches, so nodes below the pyramid's depth have to be split and the kernel redoes
+    those levels with point passes on its own."""
     w, h, nf, ini, mn = 1241, 376, 2000, 12, 7
     dense = synth.canvas(w, h, 17, 3)[:h, :w].copy()
     clustered = np.full((h, w), 96, np.uint8)
     for (y, x) in ((30, 60), (150, 420), (250, 800), (60, 1100)):
         clustered[y:y + 90, x:x + 90] = dense[y:y + 90, x:x + 90]
     ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
-    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2).debug_set("octree_points", mode == "points")
     for tag, img in (("dense", dense), ("clustered", clustered)):
         ref = ex(img)
         assert len(ref[0]) > 500
@@ -87,19 +86,15 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth, monkeypatch):
     hd.close()
 
 
-@pytest.mark.parametrize("env", [{"B2ORB_FAST_BAND": "0"}, {"B2ORB_FAST_BAND": "1"}, {"B2ORB_FAST_BAND": "2"},
-                                 {"B2ORB_FAST": "regs"}, {"B2ORB_FAST_FMA": "0"}, {"B2ORB_FAST_FMA": "88"},
-                                 {"B2ORB_CHAIN": "8"}, {"B2ORB_FORK": "0"}, {"B2ORB_PDL": "0"}],
-                         ids=lambda e: ",".join(f"{k[6:]}={v}" for k, v in e.items()))
-def test_kernel_variants_agree_with_oracle(env, fe, oracle, synth, monkeypatch):
+@pytest.mark.parametrize("opt", [("fast_band", 0), ("fast_band", 1), ("fast_band", 2), ("fork_max", 0), ("pdl", 0),
+                                 ("pdl", 1), ("export_max", 0)], ids=lambda o: f"{o[0]}={o[1]}")
+def test_launch_time_choices_agree_with_oracle(opt, fe, oracle, synth):
     """Every launch-time choice the library makes by batch size (FAST band length, side-stream blur, programmatic
-    launch chain) and every A/B kernel kept in the tree (register-window FAST, FMA-pipe mixes, cluster resize chain)
-    must give the oracle's bits: forced one at a time on a low-texture image (both FAST thresholds in play)."""
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
+    launch chain, direct export) must give the oracle's bits: pinned one at a time with b2orb_debug_set on a
+    low-texture image (both FAST thresholds in play)."""
     w, h = 400, 300
     ls, rs = synth.sequence((w, h), 2, seed=21, passes=8)
-    hd = fe.Handle(500, 1.2, 8, 20, 7, w, h, max_images=4)
+    hd = fe.Handle(500, 1.2, 8, 20, 7, w, h, max_images=4).debug_set(*opt)
     ex = oracle.OracleExtractor(500, 1.2, 8, 20, 7)
     out = hd.stereo_frontend(ls, rs, temporal=True)
     for p in range(2):
@@ -255,16 +250,13 @@ def _stereo_equal(a, b, npairs):
 
 
 @pytest.mark.parametrize("chunk,lanes", [(2, 3), (3, 2)])
-def test_pipelined_host_path_equals_single_call(chunk, lanes, fe, synth, monkeypatch):
+def test_pipelined_host_path_equals_single_call(chunk, lanes, fe, synth):
     """A long host batch is cut into chunks that rotate over internal lanes (streams): same results as one call,
     including the temporal chain across chunk, lane and call boundaries."""
     w, h, nf, ini, mn = synth.SHAPES["cfsd"]
     ls, rs = synth.sequence("cfsd", 7, seed=33)
-    monkeypatch.setenv("B2ORB_PIPE_CHUNK", "0")
-    ref = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14)
-    monkeypatch.setenv("B2ORB_PIPE_CHUNK", str(chunk))
-    monkeypatch.setenv("B2ORB_PIPE_LANES", str(lanes))
-    pip = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14)
+    ref = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14).debug_set("pipe_chunk", 0)
+    pip = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=14).debug_set("pipe_chunk", chunk).debug_set("pipe_lanes", lanes)
     a, b = ref.stereo_frontend(ls, rs, temporal=True), pip.stereo_frontend(ls, rs, temporal=True)
     assert a["n_circ"][1:].min() > 5
     _stereo_equal(a, b, 7)

@@ -71,7 +71,7 @@ def test_cuda_remap_reproduces_cv2_known_answers(name, synth):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,npairs,chunk", [("cfsd", 3, 0), ("kitti", 5, 2), ("odd", 2, 0)])
-def test_fused_rectification_equals_prerectified_frames(shape, npairs, chunk, oracle, synth, monkeypatch):
+def test_fused_rectification_equals_prerectified_frames(shape, npairs, chunk, oracle, synth):
     """processImage = remap x2 + internalMatch: raw frames through the fused device path == oracle-rectified frames
     through the plain path (keypoints, descriptors, matches, temporal circular matches), also when the batch is
     pipelined in chunks over the lanes."""
@@ -84,9 +84,8 @@ def test_fused_rectification_equals_prerectified_frames(shape, npairs, chunk, or
         ls, rs = synth.sequence(shape, npairs, seed=9)
     maps = [synth.rectification_maps(w, h, e) for e in (0, 1)]
     rl = np.stack([oracle.remap(im, *maps[0]) for im in ls]); rr = np.stack([oracle.remap(im, *maps[1]) for im in rs])
-    monkeypatch.setenv("B2ORB_PIPE_CHUNK", str(chunk))
-    plain = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
-    fused = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    plain = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs).debug_set("pipe_chunk", chunk)
+    fused = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs).debug_set("pipe_chunk", chunk)
     fused.set_rectification(maps[0][0], maps[0][1], maps[1][0], maps[1][1])
     a = plain.stereo_frontend(rl, rr, temporal=True)
     b = fused.stereo_frontend(ls, rs, temporal=True)

@@ -111,7 +111,7 @@ def _expected_fused(o, p, P1, P2, max_depth, oracle):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,npairs,chunk", [("euroc", 2, 0), ("cfsd", 7, 3)])
-def test_fused_triangulation_behind_the_stereo_filter(shape, npairs, chunk, fe, synth, oracle, monkeypatch):
+def test_fused_triangulation_behind_the_stereo_filter(shape, npairs, chunk, fe, synth, oracle):
     """b2orb_set_projection: the kept matches of every pair are triangulated in the same device pass; also through the
     pipelined host path (chunks over lanes) and with the caller's cap larger than the handle's."""
     w, h, nf, ini, mn = synth.SHAPES[shape]
@@ -119,8 +119,7 @@ def test_fused_triangulation_behind_the_stereo_filter(shape, npairs, chunk, fe, 
     P2 = P2.copy(); P2[0, 3] = -P2[0, 3]     # synth.stereo_pair displaces the right eye's content towards +x
     max_depth = 4.0
     ls, rs = synth.sequence(shape, npairs, seed=21)
-    monkeypatch.setenv("B2ORB_PIPE_CHUNK", str(chunk))
-    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2 * npairs).debug_set("pipe_chunk", chunk)
     plain = hd.stereo_frontend(ls, rs, temporal=True)
     assert "points4d" not in plain
     hd.reset_history()
