@@ -223,6 +223,24 @@ int b2orb_debug_set(b2orb_handle* h, const char* key, int value);
  * count-pyramid path had to be redone with point passes (csrc/octree.cu).  Test / tuning aid. */
 uint64_t b2orb_debug_octree_fallbacks(b2orb_handle* h);
 
+/* NO COUNTERPART IN THE REFERENCE.  An allocation-free form of the
+ * quadtree keypoint culling (DistributeOctTree, csrc/octree.cu) for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it): the call itself invokes no cudaMalloc / cudaFree / allocating
+ * library routine; its workspace is a fixed file-scope device array (0.95 MB, held by every GPU that loads the library
+ * until exit) instead of the handle's workspace.  Pyramid level `level` of the handle's CURRENT image size (the size of
+ * its last call, or max_width x max_height) supplies the geometry: quota, quadtree roots, FAST cell grid.
+ *   d_cand   DEVICE pointer: n_cand candidates x | y << 12 | response << 24 (x, y relative to the 16-px border, the
+ *            format of b2orb_debug_get_candidates), any order
+ *   d_sel    DEVICE pointer, room for quota(level) + 4 entries: the selected keypoints in the same packing, in
+ *            DistributeOctTree's list order;  d_n_sel  DEVICE pointer to one int32: their count
+ * Limits: quota(level) <= B2ORB_STATIC_MAX_FEATURES and n_cand <= B2ORB_STATIC_MAX_CANDIDATES (and the level's own
+ * candidate capacity), else B2ORB_ERR_CAPACITY.  Asynchronous on the handle's stream (b2orb_sync waits).  ALL calls, on
+ * every handle of a device, share the one workspace, which keeps the previous call's contents (the kernel initialises
+ * what it reads): calls that overlap on the GPU race — serialise them. */
+#define B2ORB_STATIC_MAX_FEATURES 4096
+#define B2ORB_STATIC_MAX_CANDIDATES 262144
+int b2orb_distribute_static(b2orb_handle* h, int level, const uint32_t* d_cand, int n_cand, uint32_t* d_sel, int32_t* d_n_sel);
+
 /* The handle's CUDA stream (a cudaStream_t) so callers can record their own events on it. */
 void* b2orb_stream(const b2orb_handle* h);
 

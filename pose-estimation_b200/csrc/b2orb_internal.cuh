@@ -175,5 +175,9 @@ void b2_launch_triangulate_matches(const B2Projection& pr, const void* kps, cons
                                    const int* n_match, int cap, int npairs, double* points4d, double* point_cam,
                                    uint8_t* flags, cudaStream_t s);
 #define B2_OT_WORDS 26   // quadtree workspace words per node slot (octree.cu)
+// allocation-free quadtree (b2orb_distribute_static): limits of the file-scope device workspace in octree.cu
+#define B2_STATIC_MAX_NODES (B2ORB_STATIC_MAX_FEATURES + 4)
+#define B2_STATIC_MAX_CANDIDATES B2ORB_STATIC_MAX_CANDIDATES
+int b2_launch_octree_static(const B2Geom& g1, const uint32_t* d_cand, int n_cand, uint32_t* d_sel, int* d_sel_cnt, cudaStream_t s);
 int b2_octree_scratch_words(const B2Geom& g);
 unsigned long long b2_octree_fallbacks();   // per device, since the library was loaded

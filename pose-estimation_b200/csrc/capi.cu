@@ -1425,6 +1425,31 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
     return B2ORB_OK;
 }
 
+// ---- allocation-free quadtree (no counterpart in the reference) ------
+int b2orb_distribute_static(b2orb_handle* h, int level, const uint32_t* d_cand, int n_cand, uint32_t* d_sel, int32_t* d_n_sel) {
+    if (!h) return B2ORB_ERR_INVALID;
+    if (level < 0 || level >= h->geom.nlevels || !d_cand || !d_sel || !d_n_sel || n_cand < 0)
+        return fail(h, B2ORB_ERR_INVALID, "bad b2orb_distribute_static arguments");
+    const B2Level& L = h->geom.lv[level];
+    if (L.quota > B2ORB_STATIC_MAX_FEATURES || L.node_cap > B2_STATIC_MAX_NODES)
+        return fail(h, B2ORB_ERR_CAPACITY, "b2orb_distribute_static: level quota exceeds B2ORB_STATIC_MAX_FEATURES (4096)");
+    if (n_cand > B2ORB_STATIC_MAX_CANDIDATES)
+        return fail(h, B2ORB_ERR_CAPACITY, "b2orb_distribute_static: n_cand exceeds B2ORB_STATIC_MAX_CANDIDATES (262144)");
+    if (n_cand > L.cand_cap) return fail(h, B2ORB_ERR_CAPACITY, "b2orb_distribute_static: more candidates than the level can hold");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2Geom g1 = h->geom;                    // one-level geometry: the level's slots start at 0
+    g1.nlevels = 1;
+    g1.lv[0] = L;
+    g1.lv[0].cand_off = 0; g1.lv[0].node_off = 0; g1.lv[0].sel_base = 0;
+    g1.cand_total = (unsigned)L.cand_cap;
+    g1.node_total = (unsigned)L.node_cap;
+    g1.sel_total = L.sel_cap;
+    const int e = b2_launch_octree_static(g1, d_cand, n_cand, d_sel, d_n_sel, h->stream);
+    h->launches += 2;
+    if (e) { cuda_ok(h, (cudaError_t)e, "b2orb_distribute_static"); return B2ORB_ERR_CUDA; }
+    return B2ORB_OK;
+}
+
 // ---- per-handle launch-time options (tests, A/B runs) ---------------------------------------------
 int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
     if (!h || !key || h->root != h) return B2ORB_ERR_INVALID;

@@ -617,3 +617,48 @@ void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt
     b2_launch_pdl(octree_kernel, dim3(grid), dim3(OT_THREADS), use_global ? 0 : smem, s, g, cand, cand_cnt, pnode, scratch, use_global, sel,
                                                               sel_cnt, force_legacy);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (b2orb_distribute_static, include/b2orb.h).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The quadtree's workspace — node lists, child counts / count pyramid, per-point node ids,
+// and the candidate count the kernel reads — lives in ONE file-scope device array of fixed size instead of the
+// handle's cudaMalloc'ed (or dynamic shared) workspace.  Every GPU that loads the library holds the array until exit.
+// All calls share it and it keeps the last call's contents: the kernel initialises every word it reads (it has to,
+// its normal workspace is uninitialised shared memory) and the count word is rewritten by every call; two calls that
+// overlap on the GPU (different streams / handles) race on it.
+constexpr int OT_STATIC_WS_WORDS = B2_OT_WORDS * B2_STATIC_MAX_NODES;                 // 26 words per node slot
+constexpr int OT_STATIC_PNODE_WORDS = B2_STATIC_MAX_CANDIDATES / 2;                   // one u16 per candidate
+constexpr int OT_STATIC_HDR_WORDS = 64;                                               // [0] = candidate count
+constexpr int OT_STATIC_WORDS = OT_STATIC_HDR_WORDS + OT_STATIC_WS_WORDS + OT_STATIC_PNODE_WORDS;
+static __device__ __align__(256) unsigned g_ot_static[OT_STATIC_WORDS];              // 0.95 MB per GPU
+
+namespace {
+// device code may name the array directly; host code needs cudaGetSymbolAddress (below)
+__global__ void octree_static_prep_kernel(int n_cand) { g_ot_static[0] = (unsigned)n_cand; }
+}  // namespace
+
+// One level of one image: candidates (x | y << 12 | response << 24, relative to the 16-px border) -> selected keypoints
+// in DistributeOctTree's list order.  g1 = one-level geometry.  Returns a cudaError_t (0 = ok).  Allocates nothing.
+int b2_launch_octree_static(const B2Geom& g1, const uint32_t* d_cand, int n_cand, uint32_t* d_sel, int* d_sel_cnt, cudaStream_t s) {
+    // In host code `g_ot_static` is a host-side stand-in, not a device address: resolve it once per device, with that
+    // device current (the caller has made the handle's device current).
+    static unsigned* s_base[64] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    if (!s_base[dev]) {
+        unsigned* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_ot_static);
+        if (e != cudaSuccess) return (int)e;
+        s_base[dev] = ptr;
+    }
+    unsigned* base = s_base[dev];
+    octree_static_prep_kernel<<<1, 1, 0, s>>>(n_cand);
+    b2_pdl_on = false;
+    b2_launch_pdl(octree_kernel, dim3(1, 1), dim3(OT_THREADS), 0, s, g1, d_cand, reinterpret_cast<const int*>(base),
+                  reinterpret_cast<unsigned short*>(base + OT_STATIC_HDR_WORDS + OT_STATIC_WS_WORDS),
+                  base + OT_STATIC_HDR_WORDS, 1, d_sel, d_sel_cnt, 0);
+    return (int)cudaGetLastError();
+}
