@@ -74,6 +74,15 @@ def lib():
         L.orc_threshold_filter.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp]
         L.orc_triangulate.argtypes = [vp, vp, vp, vp, C.c_int, vp]
         L.orc_depth_gate.argtypes = [vp, C.c_int, C.c_double, vp, vp]
+        L.orc_pool_create.restype = vp
+        L.orc_pool_create.argtypes = [C.c_float, C.c_float, C.c_int]
+        L.orc_pool_destroy.argtypes = [vp]
+        L.orc_pool_track.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp]
+        L.orc_pool_update.restype = C.c_int
+        L.orc_pool_update.argtypes = [vp, C.c_int, vp, i32p]
+        L.orc_pool_size.restype = C.c_int
+        L.orc_pool_size.argtypes = [vp]
+        L.orc_pool_get.argtypes = [vp, vp, vp, vp, vp]
         L.orc_stereo_pair.restype = C.c_int
         L.orc_stereo_pair.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_int, vp, vp, vp, vp, C.c_int, i32p, i32p, vp, vp, vp, vp]
@@ -324,6 +333,46 @@ def threshold_filter(train_idx, dist, nt, ratio, min_match_dist):
     ti = np.ascontiguousarray(train_idx, np.int32); di = np.ascontiguousarray(dist, np.int32)
     m = lib().orc_threshold_filter(_p(ti), _p(di), nq, nt, ratio, min_match_dist, _p(o_q), _p(o_t))
     return o_q[:m].copy(), o_t[:m].copy()
+
+
+class OracleFeaturePool:
+    """The feature pool of cfsd::FeatureTracker (src/feature-tracker.cpp:231-328 matching parts with useRANSAC=false,
+    :330-412 pool bookkeeping), restated on the same std::unordered_map so the pool ORDER follows libstdc++'s."""
+
+    def __init__(self, ratio=2.0, min_match_dist=30.0, max_feature_age=8):
+        self.L = lib()
+        self.h = self.L.orc_pool_create(ratio, min_match_dist, max_feature_age)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_pool_destroy(self.h)
+            self.h = None
+
+    def track(self, cur_l, cur_r):
+        """externalTrack: returns dict(circ_cur, circ_hist, mask, matched_ids, n_left, n_right, n_hist)."""
+        cl = np.ascontiguousarray(cur_l, np.uint8).reshape(-1, 32); cr = np.ascontiguousarray(cur_r, np.uint8).reshape(-1, 32)
+        n = len(cl)
+        cc = np.zeros(max(n, 1), np.int32); ch = np.zeros(max(n, 1), np.int32)
+        mask = np.zeros(max(n, 1), np.uint8); ids = np.zeros(max(n, 1), np.uint64); cnt = np.zeros(4, np.int32)
+        self.L.orc_pool_track(self.h, _p(cl), _p(cr), n, _p(cc), _p(ch), _p(mask), _p(ids), _p(cnt))
+        k = int(cnt[0])
+        return {"circ_cur": cc[:k].copy(), "circ_hist": ch[:k].copy(), "mask": mask[:n].copy(), "matched_ids": ids[:k].copy(),
+                "n_left": int(cnt[1]), "n_right": int(cnt[2]), "n_hist": int(cnt[3])}
+
+    def update(self, is_keyframe, accept=None):
+        """featurePoolUpdate: returns (inserted, erased)."""
+        er = C.c_int(0)
+        acc = np.ascontiguousarray(accept, np.uint8) if accept is not None else None
+        ins = self.L.orc_pool_update(self.h, 1 if is_keyframe else 0, _p(acc) if acc is not None else None, C.byref(er))
+        return ins, er.value
+
+    def state(self):
+        """(_histFeatureIDs, ages, _histDescriptorsL, _histDescriptorsR) in pool order."""
+        n = self.L.orc_pool_size(self.h)
+        ids = np.zeros(max(n, 1), np.uint64); ages = np.zeros(max(n, 1), np.int32)
+        hl = np.zeros((max(n, 1), 32), np.uint8); hr = np.zeros((max(n, 1), 32), np.uint8)
+        self.L.orc_pool_get(self.h, _p(ids), _p(ages), _p(hl), _p(hr))
+        return ids[:n].copy(), ages[:n].copy(), hl[:n].copy(), hr[:n].copy()
 
 
 def triangulate(P1, P2, pix_l, pix_r):

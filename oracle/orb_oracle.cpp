@@ -769,6 +769,109 @@ static int threshold_filter(const int* trainIdx, const int* dist, int nq, int nt
     return m;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Next row f3: the feature pool of cfsd::FeatureTracker — the matching parts of externalTrack
+// (src/feature-tracker.cpp:231-328, useRANSAC == false branch :293-296) against _histDescriptorsL/R, the
+// _curFeatureMask / _matchedFeatureIDs bookkeeping (:311-321) and the pool rebuild of featurePoolUpdate
+// (:330-412: age -= 1 for matched, += 2 for all, erase above maxFeatureAge, _hist* rebuilt by iterating _features,
+// un-masked new features appended).  Triangulated positions are not kept (f4 computes them); the depth gate of :374 is
+// an input (`accept`).
+// _features is a std::unordered_map<size_t, Ptr<Feature>> (include/cfsd/feature-tracker.hpp:129), and the ORDER of
+// _histFeatureIDs / _histDescriptors after a keyframe is that container's iteration order (:351-363) — it decides
+// trainIdx and BFMatcher's lowest-index tie-break.  The restatement therefore uses the same container with the same
+// key type, hash and sequence of operator[] / erase calls, so it follows libstdc++'s bucket order like the reference.
+// ------------------------------------------------------------------------------------------
+}  // namespace orc
+#include <unordered_map>
+namespace orc {
+
+struct PoolFeature {
+    uint8_t descL[32], descR[32];
+    int age = 0;
+};
+
+struct FeaturePool {
+    std::unordered_map<size_t, PoolFeature> features;          // _features
+    std::vector<size_t> histIDs;                               // _histFeatureIDs
+    std::vector<uint8_t> histL, histR;                         // _histDescriptorsL/R rows
+    std::vector<size_t> matchedIDs;                            // _matchedFeatureIDs
+    std::vector<uint8_t> curMask;                              // _curFeatureMask
+    std::vector<uint8_t> curL, curR;                           // _curDescriptorsL/R of the last track call
+    std::vector<int> circCur, circHist;                        // (queryIdx, trainIdx) of the circular matches
+    size_t featureID = 0;                                      // _featureID
+    int nLeft = 0, nRight = 0;                                 // verbose counters :297, :325
+    float ratio = 2.f, minMatchDist = 30.f;
+    int maxFeatureAge = 8;
+
+    // processImage :102-103 then externalTrack(false) :231-328
+    void track(const uint8_t* cl, const uint8_t* cr, int n) {
+        curL.assign(cl, cl + (size_t)n * 32);
+        curR.assign(cr, cr + (size_t)n * 32);
+        curMask.assign(n, 1);
+        circCur.clear(); circHist.clear();
+        nLeft = nRight = 0;
+        if (features.empty()) return;                          // :237-240 (matchedIDs keeps its old content)
+        const int nh = (int)histIDs.size();
+        std::vector<int> tl(n), dl(n), tr(n), dr(n), ql(n), hl(n), qr(n), hr(n);
+        std::vector<int> mapCurHist(n, -1);
+        if (n && nh) {
+            bf_match(cl, n, histL.data(), nh, tl.data(), dl.data());
+            nLeft = threshold_filter(tl.data(), dl.data(), n, nh, ratio, minMatchDist, ql.data(), hl.data());
+            for (int i = 0; i < nLeft; ++i) mapCurHist[ql[i]] = hl[i];
+        }
+        matchedIDs.clear();                                    // :300
+        if (n && nh) {
+            bf_match(cr, n, histR.data(), nh, tr.data(), dr.data());
+            nRight = threshold_filter(tr.data(), dr.data(), n, nh, ratio, minMatchDist, qr.data(), hr.data());
+            for (int i = 0; i < nRight; ++i) {
+                if (mapCurHist[qr[i]] == hr[i]) {              // :311-312
+                    matchedIDs.push_back(histIDs[hr[i]]);
+                    curMask[qr[i]] = 0;                        // :319
+                    circCur.push_back(qr[i]);
+                    circHist.push_back(hr[i]);
+                }
+            }
+        }
+    }
+
+    // featurePoolUpdate :330-412.  accept[i] != 0 <=> !(depth > maxDepth) for cur feature i (:374); NULL = all.
+    // Returns the number of inserted features; *erased = features dropped for age.
+    int update(bool isKeyframe, const uint8_t* accept, int* erased) {
+        int eraseCount = 0, insertCount = 0;
+        if (features.empty() || isKeyframe) {
+            for (size_t i = 0; i < matchedIDs.size(); ++i) features[matchedIDs[i]].age -= 1;   // :341-343
+            histIDs.clear(); histL.clear(); histR.clear();
+            auto f = features.begin();
+            while (f != features.end()) {                      // :349-363
+                f->second.age += 2;
+                if (f->second.age > maxFeatureAge) { f = features.erase(f); ++eraseCount; }
+                else {
+                    histIDs.push_back(f->first);
+                    histL.insert(histL.end(), f->second.descL, f->second.descL + 32);
+                    histR.insert(histR.end(), f->second.descR, f->second.descR + 32);
+                    ++f;
+                }
+            }
+            for (size_t i = 0; i < curMask.size(); ++i) {      // :369-406
+                if (!curMask[i] || (accept && !accept[i])) continue;
+                PoolFeature pf;
+                std::memcpy(pf.descL, &curL[i * 32], 32);
+                std::memcpy(pf.descR, &curR[i * 32], 32);
+                pf.age = 0;
+                features[featureID] = pf;
+                histIDs.push_back(featureID);
+                histL.insert(histL.end(), pf.descL, pf.descL + 32);
+                histR.insert(histR.end(), pf.descR, pf.descR + 32);
+                ++featureID;
+                ++insertCount;
+            }
+        }
+        if (erased) *erased = eraseCount;
+        return insertCount;
+    }
+};
+
 }  // namespace orc
 
 // ------------------------------------------------------------------------------------------
@@ -1188,6 +1291,40 @@ long orc_run_pairs(int nf, float sf, int nl, int ini, int mn, const uint8_t* img
     long sum = 0;
     for (long v : tot) sum += v;
     return sum;
+}
+
+// ---- f3: feature pool -------------------------------------------------------------------------
+void* orc_pool_create(float ratio, float minMatchDist, int maxFeatureAge) {
+    FeaturePool* p = new FeaturePool();
+    p->ratio = ratio; p->minMatchDist = minMatchDist; p->maxFeatureAge = maxFeatureAge;
+    return p;
+}
+void orc_pool_destroy(void* h) { delete (FeaturePool*)h; }
+// externalTrack on n current (kept stereo) descriptor pairs.  Outputs: circ_cur / circ_hist [n], mask [n],
+// matched_ids [n] (as uint64), counts[4] = {n_circ, n_left, n_right, n_hist}.
+void orc_pool_track(void* h, const uint8_t* curL, const uint8_t* curR, int n, int* circ_cur, int* circ_hist,
+                    uint8_t* mask, uint64_t* matched_ids, int* counts) {
+    FeaturePool* p = (FeaturePool*)h;
+    p->track(curL, curR, n);
+    const int nc = (int)p->circCur.size();
+    for (int i = 0; i < nc; ++i) { circ_cur[i] = p->circCur[i]; circ_hist[i] = p->circHist[i]; matched_ids[i] = p->matchedIDs[i]; }
+    for (int i = 0; i < n; ++i) mask[i] = p->curMask[i];
+    counts[0] = nc; counts[1] = p->nLeft; counts[2] = p->nRight; counts[3] = (int)p->histIDs.size();
+}
+int orc_pool_update(void* h, int isKeyframe, const uint8_t* accept, int* erased) {
+    return ((FeaturePool*)h)->update(isKeyframe != 0, accept, erased);
+}
+int orc_pool_size(void* h) { return (int)((FeaturePool*)h)->histIDs.size(); }
+// _histFeatureIDs, ages and descriptor rows in pool order
+void orc_pool_get(void* h, uint64_t* ids, int* ages, uint8_t* histL, uint8_t* histR) {
+    FeaturePool* p = (FeaturePool*)h;
+    const size_t n = p->histIDs.size();
+    for (size_t i = 0; i < n; ++i) {
+        if (ids) ids[i] = p->histIDs[i];
+        if (ages) ages[i] = p->features[p->histIDs[i]].age;
+    }
+    if (histL && n) std::memcpy(histL, p->histL.data(), n * 32);
+    if (histR && n) std::memcpy(histR, p->histR.data(), n * 32);
 }
 
 }  // extern "C"
