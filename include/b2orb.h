@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B2ORB_ABI_VERSION 1
+#define B2ORB_ABI_VERSION 2
 
 enum {
     B2ORB_OK = 0,
@@ -149,14 +149,25 @@ typedef struct b2orb_stereo_out {
     double* points4d;         /* [npairs][4][cap]: pair p is a 4 x cap row-major matrix = cv::Mat(4, n, CV_64F, ptr, cap*8) */
     double* point_cam;        /* [npairs*cap][3]: (X/W, Y/W, Z/W), the reference's point_wrt_cam */
     uint8_t* depth_flags;     /* [npairs*cap]: bit 0 = !(depth > max_depth), bit 1 = !(depth < 0.1 || depth > max_depth) */
+    /* What the reference itself keeps of a frame (src/feature-tracker.cpp:210-218), kept match i of pair p — a caller
+     * that sets ONLY these (and the counts / match_* / circ_* lists) gets back a few KB per pair instead of every
+     * keypoint and descriptor of both eyes; with pinned arrays the valid prefixes are written straight into them for
+     * any batch size. */
+    double* pix_l;            /* [npairs*cap][2]: _curPixelsL as cv::Point2d */
+    double* pix_r;            /* [npairs*cap][2]: _curPixelsR */
+    uint8_t* cur_desc_l;      /* [npairs*cap*32]: rows of _curDescriptorsL */
+    uint8_t* cur_desc_r;      /* [npairs*cap*32]: rows of _curDescriptorsR */
+    uint8_t* cur_mask;        /* [npairs*cap]: _curFeatureMask after externalTrack (temporal != 0): 0 = circularly matched */
 } b2orb_stereo_out;
 
 /* FeatureTracker::internalMatch (useRANSAC=false, src/feature-tracker.cpp:140-164,208-218) for `npairs`
  * independent stereo pairs: extract L and R, BF match L->R, keep matches with
  * dist < max(match_ratio*minDist, min_match_dist) and |yL - yR| < max_vertical_pixel_dist.
- * With temporal != 0 it also runs the matching parts of externalTrack (:258-259,293-296,303-321) between
+ * With temporal == 1 it also runs the matching parts of externalTrack (:258-259,293-296,303-321) between
  * consecutive pairs: cur = kept descriptors of pair p, hist = those of pair p-1 (the last pair of the
- * previous call for p == 0).  2*npairs <= max_images.  Images are host buffers (pinned memory, see
+ * previous call for p == 0) — a previous-frame stand-in for the pool, NOT the reference's multi-frame feature pool;
+ * temporal == 2 matches every pair against the device-resident feature pool instead (b2orb_pool_*, below), which is
+ * what externalTrack computes.  2*npairs <= max_images.  Images are host buffers (pinned memory, see
  * b2orb_host_alloc, lets the copies run asynchronously).  Batches longer than 64 pairs are processed as a pipeline
  * of chunks on internal streams so that the H2D copy, the kernels and the D2H copy of different chunks overlap;
  * results do not depend on the chunking (b2orb_debug_set: "pipe_chunk" pairs per chunk, 0 = off; "pipe_lanes" 2..8
@@ -202,6 +213,38 @@ int b2orb_set_projection(b2orb_handle* h, const double* P1, const double* P2, do
 int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* cur_r, int ncur, const uint8_t* hist_l,
                          const uint8_t* hist_r, int nhist, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ,
                          int32_t* n_left, int32_t* n_right);
+
+/* ---- next row f3: the feature pool of FeatureTracker, resident on the device ------------------------------------
+ * Reference: externalTrack matches _curDescriptorsL/R against _histDescriptorsL/R (src/feature-tracker.cpp:258, :303),
+ * two cv::Mats that featurePoolUpdate (:330-412) rebuilds on every keyframe from the pool `_features`.  Here the pooled
+ * descriptor rows never leave the GPU: per frame only the circular-match lists, a byte mask and counts come back, and a
+ * keyframe update sends one small index list.  The host side mirrors the reference's bookkeeping (ages, feature ids,
+ * std::unordered_map iteration order of :349-363, which decides trainIdx and tie-breaks), so ids, ages, pool order,
+ * circular matches and mask equal the reference's (useRANSAC = false path; a caller that runs RANSAC between the two
+ * matches takes the filtered lists of b2orb_temporal_track instead).  "cur" is always the kept stereo matches of pair
+ * `pair` of the LAST b2orb_stereo_frontend* call on this handle (its _curDescriptorsL/R rows are still on the device).
+ *
+ *   b2orb_pool_reset        empty pool (`_features.clear()`, _featureID = 0), sets maxFeatureAge
+ *   b2orb_pool_track        externalTrack(false): match + distance filter + circular test against the pool;
+ *                           circ_cur / circ_hist = (queryIdx, trainIdx) in query order, cur_mask = _curFeatureMask,
+ *                           matched_ids = _matchedFeatureIDs; arrays sized b2orb_keypoint_capacity(); any may be NULL
+ *   b2orb_stereo_frontend(..., temporal = 2)  runs the same track fused behind the stereo filter (one launch chain,
+ *                           every pair of the call against the same pool); b2orb_pool_last_track returns pair 0's lists
+ *   b2orb_pool_update       featurePoolUpdate: on a keyframe (or while the pool is empty) ages -1 for matched, +2 for
+ *                           all, erase above maxFeatureAge, rebuild in container order, append the un-masked current
+ *                           features whose accept[i] != 0 (`!(depth > maxDepth)`, :374; NULL = bit 0 of the device depth
+ *                           flags when b2orb_set_projection is active, else all).  new_ids = ids given to the appended
+ *                           features in order
+ *   b2orb_pool_get          _histFeatureIDs, ages and the descriptor rows in pool order (test / debug: copies rows back) */
+int b2orb_pool_reset(b2orb_handle* h, int max_feature_age);
+int b2orb_pool_size(b2orb_handle* h);
+int b2orb_pool_track(b2orb_handle* h, int pair, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ, uint8_t* cur_mask,
+                     uint64_t* matched_ids, int32_t* n_cur, int32_t* n_left, int32_t* n_right);
+int b2orb_pool_last_track(b2orb_handle* h, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ, uint8_t* cur_mask,
+                          uint64_t* matched_ids, int32_t* n_cur, int32_t* n_left, int32_t* n_right);
+int b2orb_pool_update(b2orb_handle* h, int is_keyframe, const uint8_t* accept, uint64_t* new_ids, int32_t* n_inserted,
+                      int32_t* n_erased);
+int b2orb_pool_get(b2orb_handle* h, uint64_t* ids, int32_t* ages, uint8_t* hist_l, uint8_t* hist_r, int cap, int* n);
 
 /* Test/debug access to intermediates of the LAST extract call for image slot `slot`:
  * which = 0 pyramid level, 1 blurred level (dst = w*h bytes, tightly packed). */

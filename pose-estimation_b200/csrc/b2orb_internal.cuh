@@ -155,15 +155,33 @@ struct B2BindBases {
     uint8_t *desc, *cur_l, *cur_r;
     int *nkp, *train, *dist, *nmatch, *tti_l, *tdi_l, *tti_r, *tdi_r;
     int cap;
+    const uint8_t *pool_l, *pool_r;   // non-null: temporal problems match against the feature pool (pool.cu)
+    const int* pool_n;
 };
 void b2_launch_bind(B2MatchProblem* probs, int np, const B2BindBases& b, cudaStream_t s);
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
                              const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,
-                             int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, int npairs,
-                             cudaStream_t s);   // left image slot = p, right image slot = npairs + p
+                             int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, double* pix_l, double* pix_r,
+                             int npairs, cudaStream_t s);   // left image slot = p, right image slot = npairs + p;
+                                                            // pix_* (optional) = kept pixels as cv::Point2d
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
-                        const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
-                        int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s);
+                        const int* n_hist, int hist_stride, int cap, float ratio, float min_match, int* circ_cur,
+                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s);
+// ---- f3: device-resident feature pool (pool.cu) ---------------------------------------------------------------
+struct B2Pool;
+B2Pool* b2_pool_create();
+void b2_pool_destroy(B2Pool* p);
+void b2_pool_reset(B2Pool* p);
+int b2_pool_size(const B2Pool* p);                      // rows of _histDescriptorsL/R
+bool b2_pool_empty(const B2Pool* p);                    // _features.empty()
+const uint8_t* b2_pool_rows(const B2Pool* p, int eye);  // device rows in pool order (may change after an update)
+const int* b2_pool_dcount(const B2Pool* p);             // device copy of the row count
+const unsigned long long* b2_pool_ids(const B2Pool* p); // host: _histFeatureIDs
+int b2_pool_age(const B2Pool* p, unsigned long long id);
+// featurePoolUpdate bookkeeping; descriptors move device-to-device only.  Returns 0 or a cudaError_t.
+int b2_pool_update(B2Pool* p, cudaStream_t s, bool keyframe, int max_age, const unsigned long long* matched_ids, int n_matched,
+                   const uint8_t* mask, const uint8_t* accept, int n_cur, const uint8_t* d_cur_l, const uint8_t* d_cur_r,
+                   unsigned long long* new_ids, int* n_inserted, int* n_erased);
 // cv::triangulatePoints operands (triangulate.cu): 3x4 row-major projection matrices, passed by value
 struct B2Projection {
     double P1[12], P2[12];

@@ -40,7 +40,7 @@ struct B2ExportSeg {
     long long src_pair, dst_pair;   // bytes between consecutive pairs
     int elem, fixed, count_off, count_max;
 };
-constexpr int B2_EXPORT_MAX_SEG = 24;
+constexpr int B2_EXPORT_MAX_SEG = 30;
 struct B2ExportPlan {
     B2ExportSeg seg[B2_EXPORT_MAX_SEG];
     int nseg;
@@ -145,6 +145,21 @@ struct b2orb_handle {
     bool proj_on = false;
     double *d_pts4 = nullptr, *d_ptcam = nullptr;        // [npair_cap][4][cap] homogeneous points, [npair_cap][cap][3]
     uint8_t* d_dflag = nullptr;                          // [npair_cap][cap] depth-gate flags
+    double *d_pix_l = nullptr, *d_pix_r = nullptr;       // [npair_cap][cap][2] kept pixels (_curPixelsL/R as cv::Point2d)
+    uint8_t* d_mask = nullptr;                           // [npair_cap][cap] _curFeatureMask
+    // next row f3: device-resident feature pool (root handle) + host copies of the last pool track
+    B2Pool* pool = nullptr;
+    int pool_max_age = 8;
+    std::vector<int> trk_circ_hist;                      // trainIdx of the circular matches of the last pool track
+    std::vector<unsigned long long> trk_ids;             // ... and the feature ids behind them (_matchedFeatureIDs)
+    std::vector<uint8_t> trk_mask, trk_flags;            // _curFeatureMask / depth flags of the last pool track
+    int trk_ncur = -1, trk_pair = 0;                     // -1 = lists of the last track not fetched yet
+    b2orb_handle* trk_owner = nullptr;                   // handle (lane) whose workspace holds the tracked pair
+    int bound_pool = 0;                                  // problem table bound for pool mode (and to which buffers)
+    const uint8_t* bound_pool_rows = nullptr;
+    // b2orb_extract_async: pinned count the device writes, state of the call in flight
+    int32_t* h_async_n = nullptr;
+    int async_count = 0;
     double *d_tri_in = nullptr, *d_tri_out = nullptr;    // b2orb_triangulate scratch (grow-only)
     int tri_cap = 0;
 };
@@ -431,7 +446,8 @@ int configure(b2orb_handle* h, int w, int hgt) {
               dev_alloc(h, &h->d_nleft, (size_t)np) && dev_alloc(h, &h->d_nright, (size_t)np) &&
               dev_alloc(h, &h->d_probs, (size_t)3 * np + 4) && dev_alloc(h, &h->d_gcnt, (size_t)8) &&
               dev_alloc(h, &h->d_pts4, (size_t)np * cap * 4) && dev_alloc(h, &h->d_ptcam, (size_t)np * cap * 3) &&
-              dev_alloc(h, &h->d_dflag, (size_t)np * cap);
+              dev_alloc(h, &h->d_dflag, (size_t)np * cap) && dev_alloc(h, &h->d_pix_l, (size_t)np * cap * 2) &&
+              dev_alloc(h, &h->d_pix_r, (size_t)np * cap * 2) && dev_alloc(h, &h->d_mask, (size_t)np * cap);
     if (!ok) return B2ORB_ERR_NOMEM;
     {   // raw candidate counters and per-cell flags share one allocation: one memset per batch clears both
         const size_t cnt_bytes = (size_t)nimg * nl * sizeof(int);
@@ -453,12 +469,27 @@ int configure(b2orb_handle* h, int w, int hgt) {
     return B2ORB_OK;
 }
 
+B2Pool* pool_of(b2orb_handle* h) {   // the feature pool lives on the root handle, created on first use
+    b2orb_handle* r = h->root;
+    if (!r->pool) r->pool = b2_pool_create();
+    return r->pool;
+}
+
 // Stereo problems [0,np): desc(left p) vs desc(right np+p).  Temporal problems [np, 3np): cur slot p+1 vs
-// hist slot p, left then right.
-int bind_problems(b2orb_handle* h, int np) {
-    if (h->bound_np == np) return B2ORB_OK;
+// hist slot p (or vs the feature pool), left then right.
+int bind_problems(b2orb_handle* h, int np, int pool_mode = 0) {
+    B2Pool* pool = pool_mode ? pool_of(h) : nullptr;
+    if (pool_mode && !pool) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    const uint8_t* rows = pool ? b2_pool_rows(pool, 0) : nullptr;
+    if (h->bound_np == np && h->bound_pool == pool_mode && h->bound_pool_rows == rows) return B2ORB_OK;
     B2BindBases b{h->d_desc, h->d_cur_l, h->d_cur_r, h->d_nkp, h->d_train, h->d_dist, h->d_nmatch,
-                  h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->geom.kp_cap};
+                  h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->geom.kp_cap,
+                  rows, pool ? b2_pool_rows(pool, 1) : nullptr, pool ? b2_pool_dcount(pool) : nullptr};
+    if (pool && !rows) {   // empty pool, nothing allocated yet: any valid pointer will do, the count is 0
+        b.pool_l = h->d_cur_l; b.pool_r = h->d_cur_r;
+    }
+    h->bound_pool = pool_mode;
+    h->bound_pool_rows = rows;
     b2_launch_bind(h->d_probs, np, b, h->stream);       // stream-ordered: no host synchronisation
     ++h->launches;
     h->bound_np = np;
@@ -598,7 +629,7 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
     cudaStream_t s = h->stream;
     int rc = launch_extract(h, im, 2 * np);
     if (rc) return rc;
-    rc = bind_problems(h, np);   // small H2D; table depends on np only
+    rc = bind_problems(h, np, temporal == 2);   // stream-ordered kernel; the table depends on np and the history source
     if (rc) return rc;
     prof_mark(h, B2ORB_K_MATCH_STEREO);
     b2_launch_match(h->d_probs, np, g.kp_cap, s);
@@ -606,8 +637,8 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
     prof_mark(h, B2ORB_K_STEREO_FILTER);
     b2_launch_stereo_filter(h->d_kps, h->d_desc, h->d_nkp, h->d_train, h->d_dist, g.kp_cap, h->cfg.match_ratio,
                             h->cfg.min_match_dist, h->cfg.max_vertical_pixel_dist, h->d_match_l, h->d_match_r,
-                            h->d_nmatch + 1, h->d_cur_l + (size_t)g.kp_cap * 32, h->d_cur_r + (size_t)g.kp_cap * 32, np,
-                            s);
+                            h->d_nmatch + 1, h->d_cur_l + (size_t)g.kp_cap * 32, h->d_cur_r + (size_t)g.kp_cap * 32,
+                            h->d_pix_l, h->d_pix_r, np, s);
     ++h->launches;
     if (h->root->proj_on) {   // f4: triangulate the kept matches where they lie (src/feature-tracker.cpp:365-379)
         prof_mark(h, B2ORB_K_TRIANGULATE);
@@ -616,7 +647,21 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
         ++h->launches;
     }
     prof_mark(h, -1);
-    if (temporal) {
+    if (temporal == 2) {   // f3: every pair against the device-resident feature pool (externalTrack :258, :303)
+        B2Pool* pool = h->root->pool;
+        h->root->trk_ncur = -1;          // the lists of this call are fetched on demand (b2orb_pool_last_track / _update)
+        h->root->trk_owner = h;
+        h->root->trk_pair = 0;
+        prof_mark(h, B2ORB_K_MATCH_TEMPORAL);
+        b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
+        ++h->launches;
+        prof_mark(h, B2ORB_K_CIRCULAR);
+        b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, b2_pool_dcount(pool), 0, g.kp_cap,
+                           h->cfg.match_ratio, h->cfg.min_match_dist, h->d_circ_cur, h->d_circ_hist, h->d_ncirc,
+                           h->d_nleft, h->d_nright, h->d_mask, np, s);
+        ++h->launches;
+        prof_mark(h, -1);
+    } else if (temporal) {
         const size_t row = (size_t)g.kp_cap * 32;
         b2orb_handle* src = h->root->hist_owner;
         if (src && src != h) {   // the previous pair of the sequence was processed on another lane: fetch its slot 0
@@ -629,9 +674,9 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
         b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
         ++h->launches;
         prof_mark(h, B2ORB_K_CIRCULAR);
-        b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, h->d_nmatch, g.kp_cap,
+        b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, h->d_nmatch, 1, g.kp_cap,
                            h->cfg.match_ratio, h->cfg.min_match_dist, h->d_circ_cur, h->d_circ_hist, h->d_ncirc,
-                           h->d_nleft, h->d_nright, np, s);
+                           h->d_nleft, h->d_nright, h->d_mask, np, s);
         ++h->launches;
         prof_mark(h, -1);
         // the last pair of this call becomes the history of the next call (slot 0)
@@ -721,6 +766,11 @@ bool export_plan(b2orb_handle* h, int np, const b2orb_stereo_out* o, B2ExportPla
         add(o->point_cam, h->d_ptcam, 24, kcap, cap, nm, 0, 0);
         add(o->depth_flags, h->d_dflag, 1, kcap, cap, nm, 0, 0);
     }
+    add(o->pix_l, h->d_pix_l, 16, kcap, cap, nm, 0, 0);
+    add(o->pix_r, h->d_pix_r, 16, kcap, cap, nm, 0, 0);
+    add(o->cur_desc_l, h->d_cur_l + (size_t)kcap * 32, 32, kcap, cap, nm, 0, 0);
+    add(o->cur_desc_r, h->d_cur_r + (size_t)kcap * 32, 32, kcap, cap, nm, 0, 0);
+    add(o->cur_mask, h->d_mask, 1, kcap, cap, nm, 0, 0);
     add(o->n_l, h->d_nkp, 4, 0, 0, nullptr, 0, np);
     add(o->n_r, h->d_nkp + np, 4, 0, 0, nullptr, 0, np);
     add(o->n_match, h->d_nmatch + 1, 4, 0, 0, nullptr, 0, np);
@@ -730,8 +780,15 @@ bool export_plan(b2orb_handle* h, int np, const b2orb_stereo_out* o, B2ExportPla
 
 // Results of `np` pairs to the caller and wait: direct export for latency-sized calls with pinned outputs, else the
 // copy path (b2orb_stereo_download).
+// A caller that asks only for what the reference keeps of a frame (kept pixels / descriptor rows / lists / counts,
+// src/feature-tracker.cpp:210-218) gets a few KB per pair: valid prefixes by export_kernel beat whole-slab copies at
+// any batch size then.
+bool kept_only(const b2orb_stereo_out* o) {
+    return !o->kp_l && !o->kp_r && !o->desc_l && !o->desc_r && !o->train_idx && !o->dist;
+}
+
 int finish_outputs(b2orb_handle* h, int np, const b2orb_stereo_out* o) {
-    if (o && np <= h->root->tune.export_max && o->cap >= h->geom.kp_cap) {
+    if (o && (np <= h->root->tune.export_max || (kept_only(o) && h->root->tune.export_max > 0)) && o->cap >= h->geom.kp_cap) {
         static_assert(sizeof(B2ExportPlan) < 3500, "plan must fit the kernel parameter space");
         // The pointer attributes are queried on every call (a few hundred ns each): a cached verdict would go stale when
         // the caller frees a pinned array and a pageable one lands on the same address, or toggles b2orb_set_projection.
@@ -807,6 +864,8 @@ void b2orb_destroy(b2orb_handle* h) {
         if (h->d_map1[e]) cudaFree(h->d_map1[e]);
         if (h->d_map2[e]) cudaFree(h->d_map2[e]);
     }
+    if (h->pool) b2_pool_destroy(h->pool);
+    if (h->h_async_n) cudaFreeHost(h->h_async_n);
     if (h->d_packed) cudaFree(h->d_packed);
     if (h->d_tri_in) cudaFree(h->d_tri_in);
     if (h->d_tri_out) cudaFree(h->d_tri_out);
@@ -977,6 +1036,11 @@ static int enqueue_download(b2orb_handle* h, int npairs, const b2orb_stereo_out*
         B2_CUDA(h, copy2d(o->point_cam, h->d_ptcam, 24, np));
         B2_CUDA(h, copy2d(o->depth_flags, h->d_dflag, 1, np));
     }
+    B2_CUDA(h, copy2d(o->pix_l, h->d_pix_l, 16, np));
+    B2_CUDA(h, copy2d(o->pix_r, h->d_pix_r, 16, np));
+    B2_CUDA(h, copy2d(o->cur_desc_l, h->d_cur_l + (size_t)kcap * 32, 32, np));
+    B2_CUDA(h, copy2d(o->cur_desc_r, h->d_cur_r + (size_t)kcap * 32, 32, np));
+    B2_CUDA(h, copy2d(o->cur_mask, h->d_mask, 1, np));
     if (o->n_l) B2_CUDA(h, cudaMemcpyAsync(o->n_l, h->d_nkp, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_r) B2_CUDA(h, cudaMemcpyAsync(o->n_r, h->d_nkp + np, np * 4, cudaMemcpyDeviceToHost, s));
     if (o->n_match) B2_CUDA(h, cudaMemcpyAsync(o->n_match, h->d_nmatch + 1, np * 4, cudaMemcpyDeviceToHost, s));
@@ -1068,7 +1132,16 @@ static int stereo_frontend_pipelined(b2orb_handle* h, const uint8_t* images_l, c
         shift(o.circ_cur, cap); shift(o.circ_hist, cap);
         shift(o.points4d, cap * 4); shift(o.point_cam, cap * 3); shift(o.depth_flags, cap);
         shift(o.n_l, 1); shift(o.n_r, 1); shift(o.n_match, 1); shift(o.n_circ, 1);
-        if ((rc = enqueue_download(l, n, &o, h->s_out))) break;
+        shift(o.pix_l, cap * 2); shift(o.pix_r, cap * 2); shift(o.cur_desc_l, cap * 32); shift(o.cur_desc_r, cap * 32);
+        shift(o.cur_mask, cap);
+        if (kept_only(&o) && h->tune.export_max > 0 && o.cap >= l->geom.kp_cap && export_plan(l, n, &o, l->exp_plan)) {
+            // kept-only outputs in pinned memory: the lane writes the valid prefixes itself, nothing for the copy-out stream
+            b2_pdl_on = false;
+            b2_launch_pdl(export_kernel, dim3(l->exp_plan.nseg, n, 4), dim3(256), 0, l->stream, l->exp_plan);
+            ++l->launches;
+            cudaEventRecord(l->ev_done, l->stream);
+            cudaStreamWaitEvent(h->s_out, l->ev_done, 0);
+        } else if ((rc = enqueue_download(l, n, &o, h->s_out))) break;
         cudaEventRecord(l->ev_out, h->s_out);
         if (trace) { cudaEventRecord(tr.back().e[3], h->s_out); tr.back().h1 = now() - t_start; }
     }
@@ -1405,8 +1478,8 @@ int b2orb_temporal_track(b2orb_handle* h, const uint8_t* cur_l, const uint8_t* c
     // only after the kernel has read them, so use separate regions: the q buffers are free after matching.
     int* d_cc = reinterpret_cast<int*>(h->d_gq);
     int* d_ch = reinterpret_cast<int*>(h->d_gq2);
-    b2_launch_circular(h->d_gidx, h->d_gdist, h->d_gidx2, h->d_gdist2, h->d_gcnt, h->d_gcnt + 1, 0, h->cfg.match_ratio,
-                       h->cfg.min_match_dist, d_cc, d_ch, d_out, d_out + 1, d_out + 2, 1, s);
+    b2_launch_circular(h->d_gidx, h->d_gdist, h->d_gidx2, h->d_gdist2, h->d_gcnt, h->d_gcnt + 1, 1, 0, h->cfg.match_ratio,
+                       h->cfg.min_match_dist, d_cc, d_ch, d_out, d_out + 1, d_out + 2, nullptr, 1, s);
     ++h->launches;
     B2_CUDA(h, cudaGetLastError());
     int out[3] = {0, 0, 0};
@@ -1447,6 +1520,170 @@ int b2orb_distribute_static(b2orb_handle* h, int level, const uint32_t* d_cand, 
     const int e = b2_launch_octree_static(g1, d_cand, n_cand, d_sel, d_n_sel, h->stream);
     h->launches += 2;
     if (e) { cuda_ok(h, (cudaError_t)e, "b2orb_distribute_static"); return B2ORB_ERR_CUDA; }
+    return B2ORB_OK;
+}
+
+// ---- next row f3: device-resident feature pool ------------------------------------------------------
+// featurePoolUpdate / externalTrack bookkeeping (src/feature-tracker.cpp:231-328, 330-412): descriptors of pooled
+// features stay on the device (pool.cu); per frame only index lists, a byte mask and counts cross the bus.
+int b2orb_pool_reset(b2orb_handle* h, int max_feature_age) {
+    if (!h || h->root != h || max_feature_age < 0) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    B2Pool* p = pool_of(h);
+    if (!p) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    b2_pool_reset(p);
+    h->pool_max_age = max_feature_age;
+    h->trk_ncur = -1;
+    h->trk_owner = nullptr;
+    h->trk_circ_hist.clear(); h->trk_mask.clear(); h->trk_flags.clear(); h->trk_ids.clear();
+    return B2ORB_OK;
+}
+
+int b2orb_pool_size(b2orb_handle* h) { return h && h->root->pool ? b2_pool_size(h->root->pool) : 0; }
+
+int b2orb_pool_get(b2orb_handle* h, uint64_t* ids, int32_t* ages, uint8_t* hist_l, uint8_t* hist_r, int cap, int* n) {
+    if (!h || !n) return B2ORB_ERR_INVALID;
+    B2Pool* p = pool_of(h);
+    if (!p) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    const int m = b2_pool_size(p);
+    *n = m;
+    if (m > cap) return (ids || ages || hist_l || hist_r) ? fail(h, B2ORB_ERR_CAPACITY, "pool larger than the caller's arrays") : B2ORB_OK;
+    const unsigned long long* pid = b2_pool_ids(p);
+    for (int i = 0; i < m; ++i) {
+        if (ids) ids[i] = pid[i];
+        if (ages) ages[i] = b2_pool_age(p, pid[i]);
+    }
+    B2_CUDA(h, cudaSetDevice(h->device));
+    if (m && hist_l) B2_CUDA(h, cudaMemcpyAsync(hist_l, b2_pool_rows(p, 0), (size_t)m * 32, cudaMemcpyDeviceToHost, h->stream));
+    if (m && hist_r) B2_CUDA(h, cudaMemcpyAsync(hist_r, b2_pool_rows(p, 1), (size_t)m * 32, cudaMemcpyDeviceToHost, h->stream));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    return B2ORB_OK;
+}
+
+// Host copies of what featurePoolUpdate needs from the tracked pair (a few KB): circular trainIdx list, mask, depth
+// flags.  `o` = the handle (root or lane) whose workspace holds the pair.
+static int pool_fetch_track(b2orb_handle* o, int pair) {
+    b2orb_handle* r = o->root;
+    const int kcap = o->geom.kp_cap;
+    int cnt[2] = {0, 0};
+    B2_CUDA(o, cudaMemcpyAsync(&cnt[0], o->d_nmatch + 1 + pair, 4, cudaMemcpyDeviceToHost, o->stream));
+    B2_CUDA(o, cudaMemcpyAsync(&cnt[1], o->d_ncirc + pair, 4, cudaMemcpyDeviceToHost, o->stream));
+    B2_CUDA(o, cudaStreamSynchronize(o->stream));
+    const int n = std::min(std::max(cnt[0], 0), kcap), nc = std::min(std::max(cnt[1], 0), kcap);
+    r->trk_circ_hist.resize(nc);
+    r->trk_mask.resize(n);
+    r->trk_flags.assign(n, 1);
+    if (nc) B2_CUDA(o, cudaMemcpyAsync(r->trk_circ_hist.data(), o->d_circ_hist + (size_t)pair * kcap, (size_t)nc * 4, cudaMemcpyDeviceToHost, o->stream));
+    if (n) B2_CUDA(o, cudaMemcpyAsync(r->trk_mask.data(), o->d_mask + (size_t)pair * kcap, n, cudaMemcpyDeviceToHost, o->stream));
+    if (n && r->proj_on) B2_CUDA(o, cudaMemcpyAsync(r->trk_flags.data(), o->d_dflag + (size_t)pair * kcap, n, cudaMemcpyDeviceToHost, o->stream));
+    B2_CUDA(o, cudaStreamSynchronize(o->stream));
+    r->trk_ids.resize(nc);                 // _matchedFeatureIDs.push_back(_histFeatureIDs[m.trainIdx]), :315-317
+    const unsigned long long* pid = b2_pool_ids(pool_of(o));
+    const int psz = b2_pool_size(pool_of(o));
+    for (int i = 0; i < nc; ++i) r->trk_ids[i] = r->trk_circ_hist[i] >= 0 && r->trk_circ_hist[i] < psz ? pid[r->trk_circ_hist[i]] : ~0ull;
+    r->trk_ncur = n;
+    r->trk_pair = pair;
+    r->trk_owner = o;
+    return B2ORB_OK;
+}
+
+// Results of the last pool track (b2orb_pool_track, or b2orb_stereo_frontend with temporal = 2).
+int b2orb_pool_last_track(b2orb_handle* h, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ, uint8_t* cur_mask,
+                          uint64_t* matched_ids, int32_t* n_cur, int32_t* n_left, int32_t* n_right) {
+    if (!h || h->root != h || !n_circ) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    b2orb_handle* o = h->trk_owner ? h->trk_owner : h;
+    if (h->trk_ncur < 0) {   // a fused call (temporal = 2) left the lists on the device: fetch pair 0
+        const int rc = pool_fetch_track(o, 0);
+        if (rc) { h->err = o->err; return rc; }
+    }
+    B2Pool* p = pool_of(h);
+    if (!p) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    const int kcap = o->geom.kp_cap, pair = h->trk_pair;
+    const int nc = (int)h->trk_circ_hist.size(), n = h->trk_ncur;
+    *n_circ = nc;
+    if (n_cur) *n_cur = n;
+    for (int i = 0; i < nc; ++i) {
+        if (circ_hist) circ_hist[i] = h->trk_circ_hist[i];
+        if (matched_ids) matched_ids[i] = h->trk_ids[i];
+    }
+    if (cur_mask && n) memcpy(cur_mask, h->trk_mask.data(), n);
+    int lr[2] = {0, 0};
+    if (nc && circ_cur) B2_CUDA(h, cudaMemcpyAsync(circ_cur, o->d_circ_cur + (size_t)pair * kcap, (size_t)nc * 4, cudaMemcpyDeviceToHost, o->stream));
+    if (n_left) B2_CUDA(h, cudaMemcpyAsync(&lr[0], o->d_nleft + pair, 4, cudaMemcpyDeviceToHost, o->stream));
+    if (n_right) B2_CUDA(h, cudaMemcpyAsync(&lr[1], o->d_nright + pair, 4, cudaMemcpyDeviceToHost, o->stream));
+    B2_CUDA(h, cudaStreamSynchronize(o->stream));
+    if (n_left) *n_left = lr[0];
+    if (n_right) *n_right = lr[1];
+    return B2ORB_OK;
+}
+
+int b2orb_pool_track(b2orb_handle* h, int pair, int32_t* circ_cur, int32_t* circ_hist, int32_t* n_circ, uint8_t* cur_mask,
+                     uint64_t* matched_ids, int32_t* n_cur, int32_t* n_left, int32_t* n_right) {
+    if (!h || h->root != h || pair < 0 || pair >= h->npair_cap || !n_circ) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2Pool* p = pool_of(h);
+    if (!p) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    const int kcap = h->geom.kp_cap;
+    const size_t row = (size_t)kcap * 32;
+    cudaStream_t s = h->stream;
+    // two problems in the generic slots: cur (kept rows of `pair`) against the pool, left and right
+    const uint8_t* pl = b2_pool_rows(p, 0);
+    const uint8_t* pr_ = b2_pool_rows(p, 1);
+    B2MatchProblem pr[2] = {
+        {h->d_cur_l + (pair + 1) * row, pl ? pl : h->d_cur_l, h->d_nmatch + 1 + pair, b2_pool_dcount(p), h->d_tti_l + (size_t)pair * kcap, h->d_tdi_l + (size_t)pair * kcap},
+        {h->d_cur_r + (pair + 1) * row, pr_ ? pr_ : h->d_cur_r, h->d_nmatch + 1 + pair, b2_pool_dcount(p), h->d_tti_r + (size_t)pair * kcap, h->d_tdi_r + (size_t)pair * kcap}};
+    B2MatchProblem* slot = h->d_probs + (size_t)3 * h->npair_cap + 1;
+    b2_pdl_on = false;
+    cudaEventRecord(h->ev0, s);
+    B2_CUDA(h, cudaMemcpyAsync(slot, pr, sizeof pr, cudaMemcpyHostToDevice, s));
+    prof_mark(h, B2ORB_K_MATCH_TEMPORAL);
+    b2_launch_match(slot, 2, kcap, s);
+    prof_mark(h, B2ORB_K_CIRCULAR);
+    b2_launch_circular(h->d_tti_l + (size_t)pair * kcap, h->d_tdi_l + (size_t)pair * kcap, h->d_tti_r + (size_t)pair * kcap,
+                       h->d_tdi_r + (size_t)pair * kcap, h->d_nmatch + 1 + pair, b2_pool_dcount(p), 0, 0, h->cfg.match_ratio,
+                       h->cfg.min_match_dist, h->d_circ_cur + (size_t)pair * kcap, h->d_circ_hist + (size_t)pair * kcap,
+                       h->d_ncirc + pair, h->d_nleft + pair, h->d_nright + pair, h->d_mask + (size_t)pair * kcap, 1, s);
+    h->launches += 2;
+    prof_mark(h, -1);
+    cudaEventRecord(h->ev1, s);
+    B2_CUDA(h, cudaGetLastError());
+    B2_CUDA(h, cudaStreamSynchronize(s));   // `pr` is a stack array: its copy must have left the host
+    const int rc = pool_fetch_track(h, pair);
+    if (rc) return rc;
+    return b2orb_pool_last_track(h, circ_cur, circ_hist, n_circ, cur_mask, matched_ids, n_cur, n_left, n_right);
+}
+
+int b2orb_pool_update(b2orb_handle* h, int is_keyframe, const uint8_t* accept, uint64_t* new_ids, int32_t* n_inserted,
+                      int32_t* n_erased) {
+    if (!h || h->root != h) return B2ORB_ERR_INVALID;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2Pool* p = pool_of(h);
+    if (!p) return fail(h, B2ORB_ERR_NOMEM, "feature pool");
+    b2orb_handle* o = h->trk_owner ? h->trk_owner : h;
+    if (h->trk_ncur < 0) {
+        const int rc = pool_fetch_track(o, 0);
+        if (rc) { h->err = o->err; return rc; }
+    }
+    const size_t row = (size_t)o->geom.kp_cap * 32;
+    const int n = h->trk_ncur;
+    // :374 `depth > _maxDepth` -> skip: the caller's flags, else bit 0 of the device depth flags when a projection is set
+    std::vector<uint8_t> acc;
+    if (!accept && h->proj_on) {
+        acc.resize(n);
+        for (int i = 0; i < n; ++i) acc[i] = h->trk_flags[i] & 1;
+        accept = acc.data();
+    }
+    int ins = 0, er = 0;
+    static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "id type");
+    const int e = b2_pool_update(p, o->stream, is_keyframe != 0, h->pool_max_age, h->trk_ids.data(), (int)h->trk_ids.size(),
+                                 h->trk_mask.data(), accept, n, o->d_cur_l + (h->trk_pair + 1) * row, o->d_cur_r + (h->trk_pair + 1) * row,
+                                 reinterpret_cast<unsigned long long*>(new_ids), &ins, &er);
+    if (e) { cuda_ok(h, (cudaError_t)e, "feature pool update"); return B2ORB_ERR_CUDA; }
+    if (n_inserted) *n_inserted = ins;
+    if (n_erased) *n_erased = er;
+    if (b2_pool_size(p) > 0 && (ins || er || is_keyframe)) ++h->launches;
     return B2ORB_OK;
 }
 

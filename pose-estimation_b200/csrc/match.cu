@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(SF_THREADS)
 stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restrict__ desc, const int* __restrict__ n_kp,
                      const int* __restrict__ train_idx, const int* __restrict__ dist, int cap, float ratio,
                      float min_match, float max_dy, int* __restrict__ match_l, int* __restrict__ match_r,
-                     int* __restrict__ n_match, uint8_t* __restrict__ cur_l, uint8_t* __restrict__ cur_r) {
+                     int* __restrict__ n_match, uint8_t* __restrict__ cur_l, uint8_t* __restrict__ cur_r,
+                     double2* __restrict__ pix_l, double2* __restrict__ pix_r) {
     b2_pdl_wait();
     __shared__ int s_red[SF_THREADS / 32];
     const int p = blockIdx.x;
@@ -93,6 +94,10 @@ stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restri
             uint4* dr = reinterpret_cast<uint4*>(cur_r + ((size_t)p * cap + m) * 32);
             dl[0] = sl[0]; dl[1] = sl[1];
             dr[0] = sr[0]; dr[1] = sr[1];
+            if (pix_l) {   // _curPixelsL/R.push_back(keypoint.pt): Point2f widened to Point2d (:214-215)
+                pix_l[(size_t)p * cap + m] = make_double2((double)kl[i].x, (double)kl[i].y);
+                pix_r[(size_t)p * cap + m] = make_double2((double)kr[t].x, (double)kr[t].y);
+            }
         }
         base += tot;
     }
@@ -102,15 +107,17 @@ stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restri
 // One CTA per temporal problem: left and right match lists of the same cur set against the same hist set.
 __global__ void __launch_bounds__(SF_THREADS)
 circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, const int* __restrict__ ti_r,
-                const int* __restrict__ di_r, const int* __restrict__ n_cur, const int* __restrict__ n_hist, int cap,
-                float ratio, float min_match, int* __restrict__ circ_cur, int* __restrict__ circ_hist,
-                int* __restrict__ n_circ, int* __restrict__ n_left, int* __restrict__ n_right) {
+                const int* __restrict__ di_r, const int* __restrict__ n_cur, const int* __restrict__ n_hist,
+                int hist_stride, int cap, float ratio, float min_match, int* __restrict__ circ_cur,
+                int* __restrict__ circ_hist, int* __restrict__ n_circ, int* __restrict__ n_left, int* __restrict__ n_right,
+                uint8_t* __restrict__ mask) {
     b2_pdl_wait();
     __shared__ int s_red[SF_THREADS / 32];
     const int p = blockIdx.x;
-    const int nc = n_cur[p], nh = n_hist[p];
+    const int nc = n_cur[p], nh = n_hist[p * hist_stride];   // hist_stride 0: every problem against the same set (the pool)
     if (nc == 0 || nh == 0) {   // :237-240 early-out on an empty pool; empty cur set -> nothing to match
         if (threadIdx.x == 0) { n_circ[p] = 0; if (n_left) n_left[p] = 0; if (n_right) n_right[p] = 0; }
+        if (mask) for (int i = threadIdx.x; i < nc; i += SF_THREADS) mask[(size_t)p * cap + i] = 1;   // _curFeatureMask all true
         return;
     }
     const int* tl = ti_l + (size_t)p * cap; const int* dl = di_l + (size_t)p * cap;
@@ -130,6 +137,7 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
         int tot, t2;
         const int off = block_scan_flag(keep, s_red, &tot);
         if (keep) { circ_cur[(size_t)p * cap + base + off] = i; circ_hist[(size_t)p * cap + base + off] = tl[i]; }
+        if (mask && i < nc) mask[(size_t)p * cap + i] = keep ? 0 : 1;   // _curFeatureMask[m.queryIdx] = false (:319)
         base += tot;
         block_scan_flag(okl, s_red, &t2); cl += t2;
         block_scan_flag(okr, s_red, &t2); cr += t2;
@@ -342,6 +350,11 @@ __global__ void bind_kernel(B2MatchProblem* pr, int np, B2BindBases b) {
     if (p >= np) return;
     const size_t cap = b.cap, row = cap * 32;
     pr[p] = {b.desc + p * row, b.desc + (np + p) * row, b.nkp + p, b.nkp + np + p, b.train + p * cap, b.dist + p * cap};
+    if (b.pool_l) {   // temporal problems against the device-resident feature pool (f3): the same train set for every pair
+        pr[np + p] = {b.cur_l + (p + 1) * row, b.pool_l, b.nmatch + p + 1, b.pool_n, b.tti_l + p * cap, b.tdi_l + p * cap};
+        pr[2 * np + p] = {b.cur_r + (p + 1) * row, b.pool_r, b.nmatch + p + 1, b.pool_n, b.tti_r + p * cap, b.tdi_r + p * cap};
+        return;
+    }
     pr[np + p] = {b.cur_l + (p + 1) * row, b.cur_l + p * row, b.nmatch + p + 1, b.nmatch + p, b.tti_l + p * cap, b.tdi_l + p * cap};
     pr[2 * np + p] = {b.cur_r + (p + 1) * row, b.cur_r + p * row, b.nmatch + p + 1, b.nmatch + p, b.tti_r + p * cap, b.tdi_r + p * cap};
 }
@@ -360,16 +373,16 @@ void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStr
 
 void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_kp, const int* train_idx,
                              const int* dist, int kp_cap, float ratio, float min_match, float max_dy, int* match_l,
-                             int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, int npairs,
-                             cudaStream_t s) {
+                             int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, double* pix_l, double* pix_r,
+                             int npairs, cudaStream_t s) {
     b2_launch_pdl(stereo_filter_kernel, dim3(npairs), dim3(SF_THREADS), 0, s, static_cast<const KeyPointIn*>(kps), desc, n_kp, train_idx, dist,
-                                                       kp_cap, ratio, min_match, max_dy, match_l, match_r, n_match,
-                                                       cur_l, cur_r);
+                  kp_cap, ratio, min_match, max_dy, match_l, match_r, n_match, cur_l, cur_r,
+                  reinterpret_cast<double2*>(pix_l), reinterpret_cast<double2*>(pix_r));
 }
 
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
-                        const int* n_hist, int cap, float ratio, float min_match, int* circ_cur, int* circ_hist,
-                        int* n_circ, int* n_left, int* n_right, int nprob, cudaStream_t s) {
-    b2_launch_pdl(circular_kernel, dim3(nprob), dim3(SF_THREADS), 0, s, ti_l, di_l, ti_r, di_r, n_cur, n_hist, cap, ratio, min_match,
-                                                 circ_cur, circ_hist, n_circ, n_left, n_right);
+                        const int* n_hist, int hist_stride, int cap, float ratio, float min_match, int* circ_cur,
+                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s) {
+    b2_launch_pdl(circular_kernel, dim3(nprob), dim3(SF_THREADS), 0, s, ti_l, di_l, ti_r, di_r, n_cur, n_hist, hist_stride, cap, ratio,
+                  min_match, circ_cur, circ_hist, n_circ, n_left, n_right, mask);
 }

@@ -36,7 +36,8 @@ class B2Config(C.Structure):
 class B2StereoOut(C.Structure):
     _fields_ = [("cap", C.c_int32)] + [(n, C.c_void_p) for n in (
         "kp_l", "kp_r", "desc_l", "desc_r", "n_l", "n_r", "train_idx", "dist", "match_l", "match_r", "n_match",
-        "circ_cur", "circ_hist", "n_circ", "points4d", "point_cam", "depth_flags")]
+        "circ_cur", "circ_hist", "n_circ", "points4d", "point_cam", "depth_flags", "pix_l", "pix_r", "cur_desc_l",
+        "cur_desc_r", "cur_mask")]
 
 
 class B2Error(RuntimeError):
@@ -106,6 +107,19 @@ def lib():
         L.b2orb_debug_get_level.argtypes = [vp, i32, i32, i32, vp]
         L.b2orb_debug_get_candidates.restype = i32
         L.b2orb_debug_get_candidates.argtypes = [vp, i32, i32, vp, i32, C.POINTER(i32)]
+        u8p = vp
+        L.b2orb_pool_reset.restype = i32
+        L.b2orb_pool_reset.argtypes = [vp, i32]
+        L.b2orb_pool_size.restype = i32
+        L.b2orb_pool_size.argtypes = [vp]
+        for fn in (L.b2orb_pool_track, L.b2orb_pool_last_track):
+            fn.restype = i32
+        L.b2orb_pool_track.argtypes = [vp, i32, vp, vp, C.POINTER(i32), u8p, vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+        L.b2orb_pool_last_track.argtypes = [vp, vp, vp, C.POINTER(i32), u8p, vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+        L.b2orb_pool_update.restype = i32
+        L.b2orb_pool_update.argtypes = [vp, i32, vp, vp, C.POINTER(i32), C.POINTER(i32)]
+        L.b2orb_pool_get.restype = i32
+        L.b2orb_pool_get.argtypes = [vp, vp, vp, vp, vp, i32, C.POINTER(i32)]
         L.b2orb_debug_set.restype = i32
         L.b2orb_debug_set.argtypes = [vp, C.c_char_p, i32]
         L.b2orb_debug_octree_fallbacks.restype = C.c_uint64
@@ -280,12 +294,20 @@ class Handle:
         self._proj = True
 
     # ---- fused stereo front-end
-    def alloc_stereo_out(self, npairs, pinned=False, full=True):
+    def alloc_stereo_out(self, npairs, pinned=False, full=True, kept=False):
+        """full: every keypoint / descriptor / match of both eyes; kept: what the reference keeps of a frame
+        (_curPixelsL/R, _curDescriptorsL/R, _curFeatureMask — src/feature-tracker.cpp:210-218); kept without full is
+        the small result set (a few KB per pair)."""
         cap = self.keypoint_capacity
         mk = (lambda shape, dt: pinned_empty(shape, dt)) if pinned else (lambda shape, dt: np.zeros(shape, dt))
         a = {"n_l": mk((npairs,), np.int32), "n_r": mk((npairs,), np.int32), "n_match": mk((npairs,), np.int32),
              "n_circ": mk((npairs,), np.int32),
              "match_l": mk((npairs, cap), np.int32), "match_r": mk((npairs, cap), np.int32)}
+        if kept:
+            a.update({"pix_l": mk((npairs, cap, 2), np.float64), "pix_r": mk((npairs, cap, 2), np.float64),
+                      "cur_desc_l": mk((npairs, cap, 32), np.uint8), "cur_desc_r": mk((npairs, cap, 32), np.uint8),
+                      "cur_mask": mk((npairs, cap), np.uint8),
+                      "circ_cur": mk((npairs, cap), np.int32), "circ_hist": mk((npairs, cap), np.int32)})
         if full:
             a.update({"kp_l": mk((npairs, cap), KP_DTYPE), "kp_r": mk((npairs, cap), KP_DTYPE),
                       "desc_l": mk((npairs, cap, 32), np.uint8), "desc_r": mk((npairs, cap, 32), np.uint8),
@@ -307,12 +329,12 @@ class Handle:
         npairs, hgt, w = images_l.shape
         arrays, s = out if out is not None else self.alloc_stereo_out(npairs)
         self.check(self.L.b2orb_stereo_frontend(self.h, _p(images_l), _p(images_r), npairs, w, hgt, w, w * hgt,
-                                                1 if temporal else 0, C.byref(s)))
+                                                int(temporal), C.byref(s)))   # temporal: 0 / 1 (previous pair) / 2 (pool)
         return arrays
 
     def stereo_frontend_device(self, d_ptr_l, d_ptr_r, npairs, w, hgt, step, image_stride, temporal=False):
         self.check(self.L.b2orb_stereo_frontend_device(self.h, d_ptr_l, d_ptr_r, npairs, w, hgt, step, image_stride,
-                                                       1 if temporal else 0))
+                                                       int(temporal)))
 
     def stereo_download(self, npairs, out):
         self.check(self.L.b2orb_stereo_download(self.h, npairs, C.byref(out[1])))
@@ -359,6 +381,49 @@ class Handle:
         self.check(self.L.b2orb_stereo_frontend_packed(self.h, frames.ctypes.data, n, sw, sh, sw * 4, sw * sh * 4, width,
                                                        height, 1 if temporal else 0, C.byref(s)))
         return arrays
+
+    # ---- device-resident feature pool (next row f3)
+    def pool_reset(self, max_feature_age=8):
+        self.check(self.L.b2orb_pool_reset(self.h, max_feature_age))
+
+    @property
+    def pool_size(self):
+        return self.L.b2orb_pool_size(self.h)
+
+    def _pool_lists(self, fn, *lead):
+        cap = self.keypoint_capacity
+        cc = np.zeros(cap, np.int32); ch = np.zeros(cap, np.int32); mask = np.zeros(cap, np.uint8); ids = np.zeros(cap, np.uint64)
+        n, ncur, nl, nr = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+        self.check(fn(self.h, *lead, _p(cc), _p(ch), C.byref(n), _p(mask), _p(ids), C.byref(ncur), C.byref(nl), C.byref(nr)))
+        k = n.value
+        return {"circ_cur": cc[:k].copy(), "circ_hist": ch[:k].copy(), "mask": mask[:ncur.value].copy(),
+                "matched_ids": ids[:k].copy(), "n_left": nl.value, "n_right": nr.value}
+
+    def pool_track(self, pair=0):
+        """externalTrack(false) of the kept matches of `pair` of the last stereo_frontend call against the pool."""
+        return self._pool_lists(self.L.b2orb_pool_track, pair)
+
+    def pool_last_track(self):
+        """Lists of the last track (after stereo_frontend(..., temporal=2): pair 0)."""
+        return self._pool_lists(self.L.b2orb_pool_last_track)
+
+    def pool_update(self, is_keyframe, accept=None):
+        """featurePoolUpdate; returns (new feature ids, erased count)."""
+        cap = self.keypoint_capacity
+        ids = np.zeros(cap, np.uint64)
+        ins, er = C.c_int(0), C.c_int(0)
+        acc = np.ascontiguousarray(accept, np.uint8) if accept is not None else None
+        self.check(self.L.b2orb_pool_update(self.h, 1 if is_keyframe else 0, _p(acc), _p(ids), C.byref(ins), C.byref(er)))
+        return ids[:ins.value].copy(), er.value
+
+    def pool_state(self):
+        """(_histFeatureIDs, ages, _histDescriptorsL, _histDescriptorsR) in pool order (copies the rows back: tests)."""
+        n = C.c_int(0)
+        self.check(self.L.b2orb_pool_get(self.h, None, None, None, None, 0, C.byref(n)))
+        m = max(n.value, 1)
+        ids = np.zeros(m, np.uint64); ages = np.zeros(m, np.int32); hl = np.zeros((m, 32), np.uint8); hr = np.zeros((m, 32), np.uint8)
+        self.check(self.L.b2orb_pool_get(self.h, _p(ids), _p(ages), _p(hl), _p(hr), m, C.byref(n)))
+        return ids[:n.value].copy(), ages[:n.value].copy(), hl[:n.value].copy(), hr[:n.value].copy()
 
     def sync(self):
         self.check(self.L.b2orb_sync(self.h))

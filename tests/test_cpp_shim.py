@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 20
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/b2orb.h but not exported"
-    assert L.b2orb_abi_version() == 1
+    assert L.b2orb_abi_version() == 2
     # no CUDA device here (CPU suite): creation must fail loudly, never fall back
     import torch
     if not torch.cuda.is_available():
