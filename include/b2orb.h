@@ -246,6 +246,22 @@ int b2orb_pool_update(b2orb_handle* h, int is_keyframe, const uint8_t* accept, u
                       int32_t* n_erased);
 int b2orb_pool_get(b2orb_handle* h, uint64_t* ids, int32_t* ages, uint8_t* hist_l, uint8_t* hist_r, int cap, int* n);
 
+/* The host loops of internalMatch on their own (src/feature-tracker.cpp:164, 208-218, useRANSAC = false): global minDist,
+ * keep match i iff dist < max(match_ratio*minDist, min_match_dist) and |yL - yR| < max_vertical_pixel_dist; outputs the
+ * kept (queryIdx, trainIdx) in query order and, when asked for, _curPixelsL/R (cv::Point2d) and the gathered rows of
+ * _curDescriptorsL/R (needs desc_l / desc_r).  Host arrays; nq, nt <= b2orb_keypoint_capacity(); max_images >= 2. */
+int b2orb_stereo_filter(b2orb_handle* h, const int32_t* train_idx, const int32_t* dist, int nq, const b2orb_keypoint* kp_l,
+                        const uint8_t* desc_l, const b2orb_keypoint* kp_r, const uint8_t* desc_r, int nt, int32_t* match_l,
+                        int32_t* match_r, int32_t* n_match, double* pix_l, double* pix_r, uint8_t* cur_desc_l,
+                        uint8_t* cur_desc_r);
+
+/* Asynchronous form of b2orb_extract for the reference's two-instances pattern (src/feature-tracker.cpp:153-156): the
+ * call enqueues upload + kernels on the handle's stream and returns; b2orb_extract_wait blocks and copies the results.
+ * Two handles driven from ONE thread overlap exactly like the reference's two std::threads.  The image must stay valid
+ * until the wait returns. */
+int b2orb_extract_async(b2orb_handle* h, const uint8_t* image, int width, int height, int step);
+int b2orb_extract_wait(b2orb_handle* h, b2orb_keypoint* kps, uint8_t* desc, int cap, int* n);
+
 /* Test/debug access to intermediates of the LAST extract call for image slot `slot`:
  * which = 0 pyramid level, 1 blurred level (dst = w*h bytes, tightly packed). */
 int b2orb_debug_level_size(const b2orb_handle* h, int level, int* w, int* hgt);

@@ -1687,6 +1687,98 @@ int b2orb_pool_update(b2orb_handle* h, int is_keyframe, const uint8_t* accept, u
     return B2ORB_OK;
 }
 
+// ---- stand-alone stereo filter (src/feature-tracker.cpp:164, 208-218 on host arrays) -----------------
+int b2orb_stereo_filter(b2orb_handle* h, const int32_t* train_idx, const int32_t* dist, int nq, const b2orb_keypoint* kp_l,
+                        const uint8_t* desc_l, const b2orb_keypoint* kp_r, const uint8_t* desc_r, int nt, int32_t* match_l,
+                        int32_t* match_r, int32_t* n_match, double* pix_l, double* pix_r, uint8_t* cur_desc_l,
+                        uint8_t* cur_desc_r) {
+    if (!h || !n_match || nq < 0 || nt < 0) return B2ORB_ERR_INVALID;
+    *n_match = 0;
+    if (nq == 0 || nt == 0) return B2ORB_OK;   // min_element on an empty vector (:164): defined as "no matches"
+    if (!train_idx || !dist || !kp_l || !kp_r || !match_l || !match_r || ((cur_desc_l || cur_desc_r) && (!desc_l || !desc_r)))
+        return fail(h, B2ORB_ERR_INVALID, "bad stereo filter arguments");
+    const int kcap = h->geom.kp_cap;
+    if (nq > kcap || nt > kcap) return fail(h, B2ORB_ERR_CAPACITY, "more rows than b2orb_keypoint_capacity()");
+    if (h->nimg_cap < 2) return fail(h, B2ORB_ERR_CAPACITY, "handle needs max_images >= 2");
+    for (int i = 0; i < nq; ++i)
+        if (train_idx[i] < 0 || train_idx[i] >= nt) return fail(h, B2ORB_ERR_INVALID, "train_idx out of range");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    const int cnt[2] = {nq, nt};
+    // image slots 0 (left) and 1 (right) of a one-pair batch
+    B2_CUDA(h, cudaMemcpyAsync(h->d_kps, kp_l, (size_t)nq * sizeof(b2orb_keypoint), cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_kps + kcap, kp_r, (size_t)nt * sizeof(b2orb_keypoint), cudaMemcpyHostToDevice, s));
+    if (desc_l) B2_CUDA(h, cudaMemcpyAsync(h->d_desc, desc_l, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    if (desc_r) B2_CUDA(h, cudaMemcpyAsync(h->d_desc + (size_t)kcap * 32, desc_r, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_train, train_idx, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_dist, dist, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+    B2_CUDA(h, cudaMemcpyAsync(h->d_nkp, cnt, sizeof cnt, cudaMemcpyHostToDevice, s));
+    b2_pdl_on = false;
+    prof_mark(h, B2ORB_K_STEREO_FILTER);
+    b2_launch_stereo_filter(h->d_kps, h->d_desc, h->d_nkp, h->d_train, h->d_dist, kcap, h->cfg.match_ratio, h->cfg.min_match_dist,
+                            h->cfg.max_vertical_pixel_dist, h->d_match_l, h->d_match_r, h->d_nmatch + 1,
+                            h->d_cur_l + (size_t)kcap * 32, h->d_cur_r + (size_t)kcap * 32, h->d_pix_l, h->d_pix_r, 1, s);
+    ++h->launches;
+    prof_mark(h, -1);
+    B2_CUDA(h, cudaGetLastError());
+    int m = 0;
+    B2_CUDA(h, cudaMemcpyAsync(&m, h->d_nmatch + 1, 4, cudaMemcpyDeviceToHost, s));
+    B2_CUDA(h, cudaStreamSynchronize(s));
+    *n_match = m;
+    if (m > 0) {
+        B2_CUDA(h, cudaMemcpyAsync(match_l, h->d_match_l, (size_t)m * 4, cudaMemcpyDeviceToHost, s));
+        B2_CUDA(h, cudaMemcpyAsync(match_r, h->d_match_r, (size_t)m * 4, cudaMemcpyDeviceToHost, s));
+        if (pix_l) B2_CUDA(h, cudaMemcpyAsync(pix_l, h->d_pix_l, (size_t)m * 16, cudaMemcpyDeviceToHost, s));
+        if (pix_r) B2_CUDA(h, cudaMemcpyAsync(pix_r, h->d_pix_r, (size_t)m * 16, cudaMemcpyDeviceToHost, s));
+        if (cur_desc_l) B2_CUDA(h, cudaMemcpyAsync(cur_desc_l, h->d_cur_l + (size_t)kcap * 32, (size_t)m * 32, cudaMemcpyDeviceToHost, s));
+        if (cur_desc_r) B2_CUDA(h, cudaMemcpyAsync(cur_desc_r, h->d_cur_r + (size_t)kcap * 32, (size_t)m * 32, cudaMemcpyDeviceToHost, s));
+        B2_CUDA(h, cudaStreamSynchronize(s));
+    }
+    return B2ORB_OK;
+}
+
+// ---- asynchronous extraction (two instances driven from one or two threads, src/feature-tracker.cpp:153-156) -----
+int b2orb_extract_async(b2orb_handle* h, const uint8_t* image, int width, int height, int step) {
+    if (!h) return B2ORB_ERR_INVALID;
+    h->async_count = 0;
+    if (width == 0 || height == 0) { h->async_count = -1; return B2ORB_OK; }   // empty image: wait reports 0 keypoints
+    if (!image || width < 0 || height < 0 || step < width) return fail(h, B2ORB_ERR_INVALID, "bad image arguments");
+    if (width > h->cfg.max_width || height > h->cfg.max_height) return fail(h, B2ORB_ERR_INVALID, "image larger than configured maximum");
+    B2_CUDA(h, cudaSetDevice(h->device));
+    int rc = configure(h, width, height);
+    if (rc) return rc;
+    if (!h->h_async_n) B2_CUDA(h, cudaHostAlloc(&h->h_async_n, sizeof(int32_t), cudaHostAllocDefault));
+    cudaEventRecord(h->ev0, h->stream);
+    if ((rc = upload(h, image, 1, width, height, step, (size_t)step * height, 0))) return rc;
+    B2Images im = make_images(h, h->d_stage, h->d_stage, 1, h->stage_img_bytes, h->stage_pitch);
+    if ((rc = launch_extract(h, im, 1))) return rc;
+    B2_CUDA(h, cudaMemcpyAsync(h->h_async_n, h->d_nkp, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    cudaEventRecord(h->ev1, h->stream);
+    h->async_count = 1;
+    return B2ORB_OK;
+}
+
+int b2orb_extract_wait(b2orb_handle* h, b2orb_keypoint* kps, uint8_t* desc, int cap, int* n) {
+    if (!h || !n) return B2ORB_ERR_INVALID;
+    *n = 0;
+    if (h->async_count == -1) { h->async_count = 0; return B2ORB_OK; }
+    if (h->async_count != 1) return fail(h, B2ORB_ERR_INVALID, "b2orb_extract_wait without b2orb_extract_async");
+    h->async_count = 0;
+    B2_CUDA(h, cudaSetDevice(h->device));
+    B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    const int m = *h->h_async_n;
+    if (m > cap) return fail(h, B2ORB_ERR_CAPACITY, "keypoint buffer too small");
+    if (m > 0) {
+        if (!kps || !desc) return fail(h, B2ORB_ERR_INVALID, "bad output arguments");
+        B2_CUDA(h, cudaMemcpyAsync(kps, h->d_kps, (size_t)m * sizeof(b2orb_keypoint), cudaMemcpyDeviceToHost, h->stream));
+        B2_CUDA(h, cudaMemcpyAsync(desc, h->d_desc, (size_t)m * 32, cudaMemcpyDeviceToHost, h->stream));
+        B2_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    *n = m;
+    return B2ORB_OK;
+}
+
 // ---- per-handle launch-time options (tests, A/B runs) ---------------------------------------------
 int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
     if (!h || !key || h->root != h) return B2ORB_ERR_INVALID;

@@ -120,6 +120,12 @@ def lib():
         L.b2orb_pool_update.argtypes = [vp, i32, vp, vp, C.POINTER(i32), C.POINTER(i32)]
         L.b2orb_pool_get.restype = i32
         L.b2orb_pool_get.argtypes = [vp, vp, vp, vp, vp, i32, C.POINTER(i32)]
+        L.b2orb_stereo_filter.restype = i32
+        L.b2orb_stereo_filter.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp, C.POINTER(i32), vp, vp, vp, vp]
+        L.b2orb_extract_async.restype = i32
+        L.b2orb_extract_async.argtypes = [vp, vp, i32, i32, i32]
+        L.b2orb_extract_wait.restype = i32
+        L.b2orb_extract_wait.argtypes = [vp, vp, vp, i32, C.POINTER(i32)]
         L.b2orb_debug_set.restype = i32
         L.b2orb_debug_set.argtypes = [vp, C.c_char_p, i32]
         L.b2orb_debug_octree_fallbacks.restype = C.c_uint64
@@ -241,6 +247,38 @@ class Handle:
         self.check(self.L.b2orb_extract(self.h, _p(image) if hgt else None, w, hgt, step, _p(kps), _p(desc), cap,
                                         C.byref(n)))
         return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_async(self, image):
+        """b2orb_extract_async: enqueue and return; extract_wait() collects.  Keeps `image` alive until then."""
+        image = np.ascontiguousarray(image, np.uint8) if image.strides[-1] != 1 else image
+        hgt, w = image.shape if image.ndim == 2 else (0, 0)
+        self._async_img = image
+        self.check(self.L.b2orb_extract_async(self.h, _p(image) if hgt else None, w, hgt, image.strides[0] if hgt else 0))
+
+    def extract_wait(self):
+        cap = self.keypoint_capacity
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        self.check(self.L.b2orb_extract_wait(self.h, _p(kps), _p(desc), cap, C.byref(n)))
+        self._async_img = None
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def stereo_filter(self, train_idx, dist, kp_l, desc_l, kp_r, desc_r):
+        """Host loops of internalMatch (src/feature-tracker.cpp:164, 208-218): returns dict(match_l, match_r, pix_l,
+        pix_r, cur_desc_l, cur_desc_r)."""
+        ti = np.ascontiguousarray(train_idx, np.int32); di = np.ascontiguousarray(dist, np.int32)
+        kl = np.ascontiguousarray(kp_l); kr = np.ascontiguousarray(kp_r)
+        dl = np.ascontiguousarray(desc_l, np.uint8).reshape(-1, 32); dr = np.ascontiguousarray(desc_r, np.uint8).reshape(-1, 32)
+        nq, nt = len(kl), len(kr)
+        ml = np.zeros(max(nq, 1), np.int32); mr = np.zeros(max(nq, 1), np.int32)
+        pl = np.zeros((max(nq, 1), 2), np.float64); pr = np.zeros((max(nq, 1), 2), np.float64)
+        cl = np.zeros((max(nq, 1), 32), np.uint8); cr = np.zeros((max(nq, 1), 32), np.uint8)
+        m = C.c_int(0)
+        self.check(self.L.b2orb_stereo_filter(self.h, _p(ti), _p(di), nq, _p(kl), _p(dl), _p(kr), _p(dr), nt, _p(ml), _p(mr),
+                                              C.byref(m), _p(pl), _p(pr), _p(cl), _p(cr)))
+        k = m.value
+        return {"match_l": ml[:k].copy(), "match_r": mr[:k].copy(), "pix_l": pl[:k].copy(), "pix_r": pr[:k].copy(),
+                "cur_desc_l": cl[:k].copy(), "cur_desc_r": cr[:k].copy()}
 
     def extract_batch(self, images):
         images = np.ascontiguousarray(images, np.uint8)

@@ -203,3 +203,39 @@ def test_sequence_sharded_over_two_handles_equals_sequential_full_slabs(fe, synt
     assert a["n_circ"][1:].min() > 5
     for hd in (seq, h0, h1):
         hd.close()
+
+
+def test_unchanged_caller_path_async_extract_match_and_stereo_filter(fe, oracle, synth):
+    """The reference's own call sequence with nothing fused (src/feature-tracker.cpp:153-164, 208-218): two extractor
+    instances run concurrently (b2orb_extract_async on two handles from one thread = the two std::threads), then
+    BFMatcher.match, then the host filter loops as b2orb_stereo_filter.  Must equal the fused b2orb_stereo_frontend and
+    the oracle."""
+    w, h, nf, ini, mn = synth.SHAPES["euroc"]
+    ls, rs = synth.sequence("euroc", 2, seed=71)
+    left = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    right = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    fused = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    ex = oracle.OracleExtractor(nf, 1.2, 8, ini, mn)
+    for t in range(2):
+        left.extract_async(ls[t]); right.extract_async(rs[t])
+        kl, dl = left.extract_wait(); kr, dr = right.extract_wait()
+        ko, do = ex(ls[t])
+        assert same(kl, dl, ko, do)
+        ti, di = left.match(dl, dr)
+        f = left.stereo_filter(ti, di, kl, dl, kr, dr)
+        o = fused.stereo_frontend(ls[t], rs[t], out=fused.alloc_stereo_out(1, kept=True))
+        m = int(o["n_match"][0])
+        assert m == len(f["match_l"]) > 20
+        for k in ("match_l", "match_r", "pix_l", "pix_r", "cur_desc_l", "cur_desc_r"):
+            assert np.array_equal(f[k], o[k][0, :m]), k
+        ml, mr = oracle.stereo_filter(ti, di, kl, kr, 2.0, 30.0, 0.1)
+        assert np.array_equal(f["match_l"], ml) and np.array_equal(f["match_r"], mr)
+        assert np.array_equal(f["pix_l"], np.stack([kl["x"][ml], kl["y"][ml]], 1).astype(np.float64))
+    # empty image / wait without async / empty sets
+    left.extract_async(np.zeros((0, 0), np.uint8))
+    assert len(left.extract_wait()[0]) == 0
+    with pytest.raises(fe.B2Error):
+        left.extract_wait()
+    assert len(left.stereo_filter(np.zeros(0, np.int32), np.zeros(0, np.int32), kl[:0], dl[:0], kr, dr)["match_l"]) == 0
+    for hd in (left, right, fused):
+        hd.close()
