@@ -273,8 +273,8 @@ int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* d
 /* Launch-time choices the library normally makes by batch size, pinned per handle for tests and A/B runs (nothing is
  * read from the environment; two handles on two threads may differ).  Keys: "pdl" (-1 auto / 0 / 1 programmatic
  * dependent launch), "fork_max" (blur on a side stream for calls of at most this many images), "export_max" (direct
- * export into pinned outputs for calls of at most this many pairs), "fast_band" (-1 auto, 0 / 1 / 2 = 16 / 32 / 64-row
- * FAST bands), "octree_points" (1 = quadtree by point passes only), "pipe_chunk" / "pipe_lanes" (pipelined host path,
+ * export into pinned outputs for calls of at most this many pairs), "fast_band" (-1 auto, 0 / 1 / 2 / 3 = 16 / 32 / 64 / 128-row
+ * FAST bands), "blur_band" (-1 auto, 0 / 1 = 32 / 128-row blur bands), "octree_points" (1 = quadtree by point passes only), "pipe_chunk" / "pipe_lanes" (pipelined host path,
  * before its first use), "pipe_trace". */
 int b2orb_debug_set(b2orb_handle* h, const char* key, int value);
 

@@ -86,6 +86,7 @@ def lib():
         L.orc_stereo_pair.restype = C.c_int
         L.orc_stereo_pair.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
                                       C.c_int, vp, vp, vp, vp, C.c_int, i32p, i32p, vp, vp, vp, vp]
+        L.orc_last_stage_seconds.argtypes = [vp]
         L.orc_run_pairs.restype = C.c_long
         L.orc_run_pairs.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int,
                                     C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int]
@@ -195,6 +196,9 @@ def ref_lib(arena=1):
         L.ref_level_size.argtypes = [vp, C.c_int, i32p, i32p]
         L.ref_get_level.argtypes = [vp, C.c_int, vp]
         L.ref_get_level_bordered.argtypes = [vp, C.c_int, vp]
+        L.ref_run_pairs.restype = C.c_long
+        L.ref_run_pairs.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
+                                    C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int]
         assert L.ref_arena_mode() == arena
         _ref_libs[arena] = L
     return _ref_libs[arena]
@@ -249,6 +253,16 @@ class RefExtractor:
             out = np.zeros((h.value, w.value), np.uint8)
             self.L.ref_get_level(self.h, level, _p(out))
         return out
+
+
+def ref_run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads, temporal=False):
+    """run_pairs with the reference's own ORBextractor doing the extraction (oracle/_ref, process-malloc build: the
+    arena builds exist for reproducible tie-breaks, not for speed)."""
+    L = ref_lib(0)
+    imgs_l = np.ascontiguousarray(imgs_l, np.uint8); imgs_r = np.ascontiguousarray(imgs_r, np.uint8)
+    p, h, w = imgs_l.shape
+    return L.ref_run_pairs(cfg[0], cfg[1], cfg[2], cfg[3], cfg[4], _p(imgs_l), _p(imgs_r), p, w, h, ratio, min_match_dist,
+                           max_dy, workers, per_pair_threads, 1 if temporal else 0)
 
 
 def resize(src, dw, dh):
@@ -399,6 +413,16 @@ def depth_gate(points4d, max_depth):
     if n:
         lib().orc_depth_gate(_p(p4), n, float(max_depth), _p(pc), _p(fl))
     return pc, fl
+
+
+STAGES = ("pyramid", "fast_cells", "quadtree", "orientation", "blur", "describe", "match_stereo", "match_temporal")
+
+
+def last_stage_seconds():
+    """Per-stage CPU seconds of the last run_pairs, summed over workers (thread-seconds)."""
+    out = np.zeros(8, np.float64)
+    lib().orc_last_stage_seconds(_p(out))
+    return dict(zip(STAGES, out.tolist()))
 
 
 def run_pairs(cfg, imgs_l, imgs_r, ratio, min_match_dist, max_dy, workers, per_pair_threads, temporal=False):

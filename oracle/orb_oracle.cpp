@@ -29,6 +29,7 @@
 // mirrors the reference build, CMakeLists.txt:53 / Dockerfile.amd64:50).
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -517,6 +518,11 @@ struct Extractor {
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
     std::vector<int> mnFeaturesPerLevel, umax;
     int taps[7];
+    // per-stage wall-clock seconds accumulated over calls (bench.py's CPU legs print stage means like the reference's
+    // benchmark programs do, benchmark/bundleAdjustment/bundleAdjustment.cpp:174-318): pyramid, FAST cells, quadtree,
+    // orientation, blur, descriptors
+    double stage_s[6] = {0, 0, 0, 0, 0, 0};
+    static double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
     int tie_mode = 1;            // see distribute_octtree
     std::vector<int> ties;       // per level: equal-count comparisons that mattered in the last extract
     // intermediates kept for tests (the reference keeps mvImagePyramid as a public member too)
@@ -615,6 +621,7 @@ struct Extractor {
             if (nCols < 1 || nRows < 1) continue;  // the reference divides by zero here
             const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
             std::vector<KeyPoint> cell;
+            double t0 = now_s();
             for (int i = 0; i < nRows; ++i) {
                 const float iniY = (float)(minBorderY + i * hCell);
                 float maxY = iniY + hCell + 6;
@@ -635,6 +642,8 @@ struct Extractor {
                     }
                 }
             }
+            stage_s[1] += now_s() - t0;
+            t0 = now_s();
             std::vector<KeyPoint>& kps = all[level];
             kps = distribute_octtree(toDistribute, minBorderX, maxBorderX, minBorderY, maxBorderY,
                                      mnFeaturesPerLevel[level], tie_mode, &ties[level]);
@@ -645,9 +654,12 @@ struct Extractor {
                 kp.octave = level;
                 kp.size = (float)scaledPatchSize;
             }
+            stage_s[2] += now_s() - t0;
         }
+        const double t1 = now_s();
         for (int level = 0; level < nlevels; ++level)
             for (KeyPoint& kp : all[level]) kp.angle = ic_angle(pyramid[level], kp.x, kp.y);
+        stage_s[3] += now_s() - t1;
     }
 
     // computeOrbDescriptor, src/ORBextractor.cc:108-147.  fp32 products and sum are rounded
@@ -681,7 +693,9 @@ struct Extractor {
         descriptors.clear();
         blurred.assign(nlevels, Img());
         if (image.w == 0 || image.h == 0) return;
+        double t0 = now_s();
         compute_pyramid(image);
+        stage_s[0] += now_s() - t0;
         std::vector<std::vector<KeyPoint>> all;
         compute_keypoints(all);
         size_t n = 0;
@@ -692,9 +706,13 @@ struct Extractor {
         for (int level = 0; level < nlevels; ++level) {
             std::vector<KeyPoint>& kps = all[level];
             if (kps.empty()) continue;
+            t0 = now_s();
             gaussian_blur7(pyramid[level], blurred[level], taps);
+            stage_s[4] += now_s() - t0;
+            t0 = now_s();
             for (size_t i = 0; i < kps.size(); ++i)
                 orb_descriptor(kps[i], blurred[level], &descriptors[(offset + i) * 32]);
+            stage_s[5] += now_s() - t0;
             offset += kps.size();
             if (level != 0) {
                 float scale = mvScaleFactor[level];
@@ -1233,10 +1251,16 @@ int orc_stereo_pair(void* hL, void* hR, const uint8_t* imgL, const uint8_t* imgR
 // src/feature-tracker.cpp:153-156).  temporal != 0 adds the matching parts of externalTrack
 // (:258-259, 293-296, 303-321) between a worker's consecutive pairs.  Returns kept stereo matches +
 // circular matches summed (so the work cannot be optimised away).
+// stage seconds of the last orc_run_pairs, summed over workers: 6 extractor stages (both eyes), stereo match + filter,
+// temporal match + circular check
+static double g_stage_s[8];
+void orc_last_stage_seconds(double* out) { std::memcpy(out, g_stage_s, sizeof g_stage_s); }
+
 long orc_run_pairs(int nf, float sf, int nl, int ini, int mn, const uint8_t* imgsL, const uint8_t* imgsR,
                    int npairs, int w, int hh, float ratio, float minMatchDist, float maxDy, int workers,
                    int per_pair_threads, int temporal) {
     std::vector<long> tot(workers, 0);
+    std::vector<std::vector<double>> st(workers, std::vector<double>(8, 0.0));
     std::vector<std::thread> th;
     for (int t = 0; t < workers; ++t) {
         th.emplace_back([&, t] {
@@ -1258,12 +1282,15 @@ long orc_run_pairs(int nf, float sf, int nl, int ini, int mn, const uint8_t* img
                 const int a = (int)kL.size(), b = (int)kR.size();
                 std::vector<int> ti(a), di(a), oL(a), oR(a);
                 int m = 0;
+                double tm = Extractor::now_s();
                 if (a && b) {
                     bf_match(dL.data(), a, dR.data(), b, ti.data(), di.data());
                     m = stereo_filter(ti.data(), di.data(), a, b, kL.data(), kR.data(), ratio, minMatchDist, maxDy,
                                       oL.data(), oR.data());
                 }
+                st[t][6] += Extractor::now_s() - tm;
                 tot[t] += m;
+                tm = Extractor::now_s();
                 if (temporal) {
                     std::vector<uint8_t> curL((size_t)m * 32), curR((size_t)m * 32);
                     for (int i = 0; i < m; ++i) {
@@ -1284,12 +1311,18 @@ long orc_run_pairs(int nf, float sf, int nl, int ini, int mn, const uint8_t* img
                     histL.swap(curL);
                     histR.swap(curR);
                 }
+                st[t][7] += Extractor::now_s() - tm;
             }
+            for (int k = 0; k < 6; ++k) st[t][k] = eL.stage_s[k] + eR.stage_s[k];
         });
     }
     for (auto& x : th) x.join();
     long sum = 0;
     for (long v : tot) sum += v;
+    for (int k = 0; k < 8; ++k) {
+        g_stage_s[k] = 0;
+        for (int t = 0; t < workers; ++t) g_stage_s[k] += st[t][k];
+    }
     return sum;
 }
 

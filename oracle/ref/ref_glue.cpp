@@ -34,6 +34,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include <opencv2/core.hpp>
@@ -50,6 +51,11 @@ void orc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh
 void orc_blur(const uint8_t* src, int w, int hh, uint8_t* dst, const int* taps);
 int orc_fast(const uint8_t* img, int w, int hh, int x0, int y0, int x1, int y1, int thr, float* xyr, int cap);
 float orc_fast_atan2(float y, float x);
+void orc_bf_match(const uint8_t* q, int nq, const uint8_t* t, int nt, int* trainIdx, int* dist);
+int orc_stereo_filter(const int* trainIdx, const int* dist, int nq, int nt, const void* kpL, const void* kpR, float ratio,
+                      float minMatchDist, float maxDy, int* outL, int* outR);
+int orc_threshold_filter(const int* trainIdx, const int* dist, int nq, int nt, float ratio, float minMatchDist, int* outQ,
+                         int* outT);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -287,6 +293,76 @@ void ref_get_level_bordered(void* h, int level, uint8_t* out) {
     const int W = m.cols + 38, H = m.rows + 38;
     const uint8_t* origin = m.data - 19 * m.step - 19;
     for (int y = 0; y < H; ++y) std::memcpy(out + (size_t)y * W, origin + (size_t)y * m.step, (size_t)W);
+}
+
+// CPU reference arm of bench.py (--impl reference): `npairs` stereo pairs spread over `workers` host threads, each
+// worker owning two instances of the reference's ORBextractor (left / right, src/feature-tracker.cpp:26-27) and running
+// its pairs one after the other: operator() x2 (on two std::threads when per_pair_threads >= 2, :153-156), BFMatcher +
+// min-distance / row filter (:161-164, 208-218) and, with temporal != 0, the matching parts of externalTrack against the
+// worker's previous pair (:258-259, 293-296, 303-321).  Extraction is the reference's own code; the matcher calls are
+// OpenCV's in the reference and the cv2-pinned restatements here.  Returns kept + circular matches (keeps the work live).
+long ref_run_pairs(int nf, float sf, int nl, int ini, int mn, const uint8_t* imgsL, const uint8_t* imgsR, int npairs, int w,
+                   int hh, float ratio, float minMatchDist, float maxDy, int workers, int per_pair_threads, int temporal) {
+    std::vector<long> tot(workers, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < workers; ++t) {
+        th.emplace_back([&, t] {
+            Probe* eL = new Probe(nf, sf, nl, ini, mn);
+            Probe* eR = new Probe(nf, sf, nl, ini, mn);
+            std::vector<uint8_t> histL, histR;
+            const int cap = nf + 4 * nl + 64;
+            std::vector<cv::KeyPoint> kL(cap), kR(cap);
+            std::vector<uint8_t> dL((size_t)cap * 32), dR((size_t)cap * 32);
+            for (int p = t; p < npairs; p += workers) {
+                int a = 0, b = 0;
+                const uint8_t* iL = imgsL + (size_t)p * w * hh;
+                const uint8_t* iR = imgsR + (size_t)p * w * hh;
+                if (per_pair_threads >= 2) {
+                    std::thread tl([&] { a = ref_extract(eL, iL, w, hh, w, kL.data(), dL.data(), cap); });
+                    std::thread tr([&] { b = ref_extract(eR, iR, w, hh, w, kR.data(), dR.data(), cap); });
+                    tl.join();
+                    tr.join();
+                } else {
+                    a = ref_extract(eL, iL, w, hh, w, kL.data(), dL.data(), cap);
+                    b = ref_extract(eR, iR, w, hh, w, kR.data(), dR.data(), cap);
+                }
+                if (a < 0 || b < 0) continue;
+                std::vector<int> ti(a), di(a), oL(a), oR(a);
+                int m = 0;
+                if (a && b) {
+                    orc_bf_match(dL.data(), a, dR.data(), b, ti.data(), di.data());
+                    m = orc_stereo_filter(ti.data(), di.data(), a, b, kL.data(), kR.data(), ratio, minMatchDist, maxDy, oL.data(), oR.data());
+                }
+                tot[t] += m;
+                if (temporal) {
+                    std::vector<uint8_t> curL((size_t)m * 32), curR((size_t)m * 32);
+                    for (int i = 0; i < m; ++i) {
+                        std::memcpy(&curL[(size_t)i * 32], &dL[(size_t)oL[i] * 32], 32);
+                        std::memcpy(&curR[(size_t)i * 32], &dR[(size_t)oR[i] * 32], 32);
+                    }
+                    const int nh = (int)histL.size() / 32;
+                    if (m && nh) {
+                        std::vector<int> tl(m), dl(m), tr(m), dr(m), ql(m), hl(m), qr(m), hr(m);
+                        orc_bf_match(curL.data(), m, histL.data(), nh, tl.data(), dl.data());
+                        orc_bf_match(curR.data(), m, histR.data(), nh, tr.data(), dr.data());
+                        const int cl = orc_threshold_filter(tl.data(), dl.data(), m, nh, ratio, minMatchDist, ql.data(), hl.data());
+                        const int cr = orc_threshold_filter(tr.data(), dr.data(), m, nh, ratio, minMatchDist, qr.data(), hr.data());
+                        std::vector<int> map(m, -1);
+                        for (int i = 0; i < cl; ++i) map[ql[i]] = hl[i];
+                        for (int i = 0; i < cr; ++i) tot[t] += (map[qr[i]] == hr[i]);
+                    }
+                    histL.swap(curL);
+                    histR.swap(curR);
+                }
+            }
+            delete eL;
+            delete eR;
+        });
+    }
+    for (auto& x : th) x.join();
+    long sum = 0;
+    for (long v : tot) sum += v;
+    return sum;
 }
 
 }  // extern "C"

@@ -38,8 +38,9 @@ inline cudaError_t b2_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block
 #define B2_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:74
 #define B2_BORDER 16        // EDGE_THRESHOLD-3 = minBorderX/Y, src/ORBextractor.cc:773-776
 #define B2_FAST_BAND 16     // corner-map rows per FAST score task (fast.cu): variant v uses B2_FAST_BAND << v rows
-#define B2_FAST_VARIANTS 3  // 16 rows (latency-sized calls), 32, 64 (large batches: less halo work)
-#define B2_BLUR_BAND 32     // output rows per blur task (blur.cu)
+#define B2_FAST_VARIANTS 4  // 16 rows (latency-sized calls), 32, 64, 128 (large batches: less halo work)
+#define B2_BLUR_BAND 32     // output rows per blur task (blur.cu): variant v uses B2_BLUR_BAND << (2 * v) rows
+#define B2_BLUR_VARIANTS 2  // 32 rows, 128 rows (large batches: 6 halo rows per band are 19 % / 5 % extra work)
 #define B2_HALF_PATCH 15    // HALF_PATCH_SIZE, src/ORBextractor.cc:73
 
 // Per-level geometry, fixed for (config, image size).  Passed to kernels BY VALUE as one
@@ -52,7 +53,7 @@ struct B2Level {
     int cell_base;            // first flattened cell index of this level
     int fast_task_base[B2_FAST_VARIANTS];    // first flattened FAST score task (band, strip) of this level, per band variant
     int fast_strips;          // 120-px strips per row band (fast.cu)
-    int blur_task_base;       // first flattened blur task (band, strip) of this level
+    int blur_task_base[B2_BLUR_VARIANTS];    // first flattened blur task (band, strip) of this level, per band variant
     int blur_strips;          // 128-px strips per row band
     int quota;                // mnFeaturesPerLevel[level]
     int sel_base;             // first slot of this level in the per-image selected-keypoint array
@@ -72,7 +73,7 @@ struct B2Geom {
     int nlevels;
     int ini_th, min_th;
     int total_cells;          // over all levels
-    int total_blur_tasks;
+    int total_blur_tasks[B2_BLUR_VARIANTS];
     int total_fast_tasks[B2_FAST_VARIANTS];  // per band variant (short bands for small batches, long bands for less halo work)
     int sel_total;            // per-image selected-keypoint slots (sum of sel_cap)
     int kp_cap;               // per-image output capacity
@@ -136,7 +137,7 @@ void b2_launch_ingest_bgra(const uint8_t* frames, int sstep, size_t sstride, int
                            int half_w, int dh, int count, cudaStream_t s);
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s);
-void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s);
+void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, int forced_band, cudaStream_t s);
 // fast_score appends the non-zero words of the NMS'd corner map (4 px of b + position, uint2) to a raw list and raises
 // the per-cell "iniThFAST found something" flags; fast_vote applies the per-cell threshold vote and expands the words
 // into candidates x | y<<12 | (b-1)<<24

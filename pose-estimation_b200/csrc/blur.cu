@@ -149,24 +149,25 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
 }
 
 __global__ void __launch_bounds__(BL_WARPS * 32)
-blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
+blur_kernel(const __grid_constant__ B2Geom g, const B2Images im, int variant) {
     b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[BL_WARPS][BL_SLOTS * BL_ROWB];
     const int lane = threadIdx.x & 31;
     const int task = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
-    if (task >= g.total_blur_tasks) return;
+    if (task >= g.total_blur_tasks[variant]) return;
+    const int band_rows = B2_BLUR_BAND << (2 * variant);
     const int b = blockIdx.y;
     int level = 0;
-    while (level + 1 < g.nlevels && task >= g.lv[level + 1].blur_task_base) ++level;
+    while (level + 1 < g.nlevels && task >= g.lv[level + 1].blur_task_base[variant]) ++level;
     const B2Level& L = g.lv[level];
-    const int t = task - L.blur_task_base;
+    const int t = task - L.blur_task_base[variant];
     const int band = t / L.blur_strips, strip = t - band * L.blur_strips;
     int spitch;
     const uint8_t* src = b2_level_ptr(g, im, b, level, spitch);
     uint8_t* dst = im.blur + (size_t)b * g.slab + L.off;
     const int x = strip * 128 + lane * 4;
-    const int y0 = band * B2_BLUR_BAND;
-    const int rows = min(B2_BLUR_BAND, L.h - y0);
+    const int y0 = band * band_rows;
+    const int rows = min(band_rows, L.h - y0);
 
     // a strip needs the border code if it touches column 0 or its last lane's halo reaches beyond w-1
     const bool edge = strip == 0 || strip * 128 + 128 + 3 > L.w - 1;
@@ -182,7 +183,10 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im) {
 
 }  // namespace
 
-void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, cudaStream_t s) {
-    dim3 grid((g.total_blur_tasks + BL_WARPS - 1) / BL_WARPS, nimg);
-    b2_launch_pdl(blur_kernel, dim3(grid), dim3(BL_WARPS * 32), 0, s, g, im);
+void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, int forced_band, cudaStream_t s) {
+    // long bands once the batch alone fills the machine several times over (6 halo rows per band)
+    int variant = (long long)g.total_blur_tasks[1] * nimg >= 148LL * 16 * 4 ? 1 : 0;
+    if (forced_band >= 0 && forced_band < B2_BLUR_VARIANTS) variant = forced_band;   // b2orb_debug_set("blur_band")
+    dim3 grid((g.total_blur_tasks[variant] + BL_WARPS - 1) / BL_WARPS, nimg);
+    b2_launch_pdl(blur_kernel, dim3(grid), dim3(BL_WARPS * 32), 0, s, g, im, variant);
 }

@@ -52,7 +52,8 @@ struct B2Tuning {
     int pdl = -1;            // programmatic dependent launch: -1 = by batch size (<= 8 images), 0 / 1 = forced
     int fork_max = 8;        // blur on the side stream for calls of at most this many images
     int export_max = 4;      // direct export into pinned outputs for calls of at most this many pairs
-    int fast_band = -1;      // FAST band variant 0 / 1 / 2 (16 / 32 / 64 rows), -1 = by batch size
+    int fast_band = -1;      // FAST band variant 0 / 1 / 2 / 3 (16 / 32 / 64 / 128 rows), -1 = by batch size
+    int blur_band = -1;      // blur band variant 0 / 1 (32 / 128 rows), -1 = by batch size
     int octree_points = 0;   // 1 = quadtree by point passes only (the count-pyramid path's fallback)
     int pipe_chunk = 64;     // pairs per chunk of the pipelined host path, 0 = off
     int pipe_lanes = 3;      // lanes (workspaces + streams) the chunks rotate over
@@ -296,7 +297,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         memcpy(g.tapv, v, sizeof v);
     }
     unsigned off = 0, cand_off = 0, node_off = 0;
-    int cells = 0, tiles = 0, sel = 0, ftasks[B2_FAST_VARIANTS] = {};
+    int cells = 0, tiles[B2_BLUR_VARIANTS] = {}, sel = 0, ftasks[B2_FAST_VARIANTS] = {};
     for (int l = 0; l < c.nlevels; ++l) {
         B2Level& L = g.lv[l];
         // ComputePyramid :1111-1112: Size(cvRound((float)cols*scale), cvRound((float)rows*scale))
@@ -307,8 +308,11 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
         L.off = off;
         off += align_up((unsigned)L.pitch * (unsigned)L.h, 256);
         L.blur_strips = (L.w + 127) / 128;
-        L.blur_task_base = tiles;
-        tiles += L.blur_strips * ((L.h + B2_BLUR_BAND - 1) / B2_BLUR_BAND);
+        for (int v = 0; v < B2_BLUR_VARIANTS; ++v) {
+            const int band = B2_BLUR_BAND << (2 * v);
+            L.blur_task_base[v] = tiles[v];
+            tiles[v] += L.blur_strips * ((L.h + band - 1) / band);
+        }
         L.quota = h->quota[l];
         L.scale = h->scale[l];
         L.kp_size = (float)(int)(31 * h->scale[l]);     // :836 `const int scaledPatchSize = PATCH_SIZE*mvScaleFactor[level]`
@@ -360,7 +364,7 @@ const char* build_geometry(b2orb_handle* h, int w, int hgt, B2Geom& g) {
     }
     if (w > 4096 + B2_BORDER || hgt > 4096 + B2_BORDER) return "image larger than 4096 px";
     g.total_cells = cells;
-    g.total_blur_tasks = tiles;
+    for (int v = 0; v < B2_BLUR_VARIANTS; ++v) g.total_blur_tasks[v] = tiles[v];
     for (int v = 0; v < B2_FAST_VARIANTS; ++v) g.total_fast_tasks[v] = ftasks[v];
     g.sel_total = sel;
     g.kp_cap = sel;
@@ -518,7 +522,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
     if (fork) {
         B2_CUDA(h, cudaEventRecord(h->ev_fork, s));
         B2_CUDA(h, cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
-        b2_launch_blur(g, im, nimg, h->s_aux);
+        b2_launch_blur(g, im, nimg, tn.blur_band, h->s_aux);
         ++h->launches;
         B2_CUDA(h, cudaEventRecord(h->ev_join, h->s_aux));
     }
@@ -536,7 +540,7 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
         B2_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));
     } else {
         prof_mark(h, B2ORB_K_BLUR);
-        b2_launch_blur(g, im, nimg, s);
+        b2_launch_blur(g, im, nimg, tn.blur_band, s);
         ++h->launches;
     }
     prof_mark(h, B2ORB_K_DESCRIBE);
@@ -1788,6 +1792,7 @@ int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
     else if (k == "fork_max") t.fork_max = value;
     else if (k == "export_max") t.export_max = value;
     else if (k == "fast_band") t.fast_band = value;
+    else if (k == "blur_band") t.blur_band = value;
     else if (k == "octree_points") t.octree_points = value ? 1 : 0;
     else if (k == "pipe_trace") t.pipe_trace = value;
     else if (k == "pipe_chunk" || k == "pipe_lanes") {

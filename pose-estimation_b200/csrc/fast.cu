@@ -417,7 +417,8 @@ void b2_launch_fast_score(const B2Geom& g, const B2Images& im, uint2* raw, int* 
     if (g.total_fast_tasks[0] <= 0) return;
     // long bands (less halo work per output row) once the batch alone fills the machine several times over
     // and short ones while a 32-row launch would not even give every SM two CTAs (per-CTA latency is what counts then)
-    int variant = (long long)g.total_fast_tasks[2] * nimg >= 148LL * 16 * 4 ? 2
+    int variant = (long long)g.total_fast_tasks[3] * nimg >= 148LL * 16 * 4 ? 3
+                  : (long long)g.total_fast_tasks[2] * nimg >= 148LL * 16 * 4 ? 2
                   : (long long)g.total_fast_tasks[1] * nimg >= 148LL * 2 * 4 ? 1 : 0;
     if (forced_band >= 0 && forced_band < B2_FAST_VARIANTS) variant = forced_band;   // b2orb_debug_set("fast_band")
     dim3 grid((g.total_fast_tasks[variant] + FS_WARPS - 1) / FS_WARPS, nimg);

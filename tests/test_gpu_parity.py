@@ -86,7 +86,8 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth):
     hd.close()
 
 
-@pytest.mark.parametrize("opt", [("fast_band", 0), ("fast_band", 1), ("fast_band", 2), ("fork_max", 0), ("pdl", 0),
+@pytest.mark.parametrize("opt", [("fast_band", 0), ("fast_band", 1), ("fast_band", 2), ("fast_band", 3), ("blur_band", 0), ("blur_band", 1),
+                                 ("fork_max", 0), ("pdl", 0),
                                  ("pdl", 1), ("export_max", 0)], ids=lambda o: f"{o[0]}={o[1]}")
 def test_launch_time_choices_agree_with_oracle(opt, fe, oracle, synth):
     """Every launch-time choice the library makes by batch size (FAST band length, side-stream blur, programmatic
