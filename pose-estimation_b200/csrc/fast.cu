@@ -39,7 +39,7 @@ namespace {
 constexpr int FS_WARPS = 4;
 constexpr int FS_PF = 5;        // rows in flight per warp (ring of 7 slots, slot = row % 7 = unroll phase)
 constexpr int FS_FLUSH = 7;     // output rows between queue flushes (one pass of the 7-phase unrolled loop)
-constexpr int FS_QUEUE = 30 * FS_FLUSH;   // at most one non-zero word per storing lane and row
+constexpr int FS_QUEUE = 2 * 30 * FS_FLUSH;   // at most one non-zero word per storing lane and row; flushed when half full
 
 __device__ __forceinline__ unsigned vmin2(unsigned a, unsigned b) { return __vminu2(a, b); }
 __device__ __forceinline__ unsigned vmax2(unsigned a, unsigned b) { return __vmaxu2(a, b); }
@@ -114,6 +114,15 @@ __device__ __forceinline__ unsigned keep_if_greater(unsigned b, unsigned nb) {
     const unsigned d = b + 0x00FF00FFu - nb;                 // bit 8 of each lane: b > nb
     const unsigned one = __byte_perm(d, 0u, 0x4341);         // (d.b1, 0, d.b3, 0): 0 or 1 per lane
     return b & (one * 255u);
+}
+
+// out = (b > nb) ? (b & m) : 0 per u16 lane, all values < 256: bit 15 of (b - nb + 0x7FFF) is "b > nb"; PRMT replicates it
+// over the low byte of each lane (selector nibbles 9 / B = sign of byte 1 / 3, 4 = zero byte), one LOP3 applies both masks
+__device__ __forceinline__ unsigned keep_if_greater_and(unsigned b, unsigned nb, unsigned m) {
+    const unsigned d = b + 0x7FFF7FFFu - nb;
+    unsigned keep;                                           // (__byte_perm masks the selector's replicate bit: PTX it is)
+    asm("prmt.b32 %0, %1, %2, 0x4B49;" : "=r"(keep) : "r"(d), "r"(0u));
+    return b & keep & m;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -214,19 +223,18 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
     unsigned a2 = a1 + 1024, a3 = a1 + 2048, a4 = a1 + 3072, a5 = a1 + 4096, a6 = a1 + 5120;
 
     unsigned rmE_a = 0, rmO_a = 0, rmE_b = 0, rmO_b = 0, bE_b = 0, bO_b = 0, sdE_b = 0, sdO_b = 0;
-    int y = ya;
-    int ci = (band * band_rows) / L.h_cell;
-    int cy = band * band_rows - ci * L.h_cell;
+    int ci = (band * band_rows) / L.h_cell;                     // cell row of the output row
     unsigned meta = (unsigned)(x - B2_BORDER) | ((unsigned)(ya - B2_BORDER) << 12) | ((unsigned)ci << 24);
-    int hcell1 = L.h_cell - 1, ylast = h - B2_EDGE - 1;
-    int since_flush = 0;
+    const int hcell = L.h_cell, ylast = h - B2_EDGE - 1;
     // loop invariants the compiler would otherwise rebuild from the constant bank / special registers every row
-    unsigned thr2_r = thr2, kini_r = kini, queue_s = (unsigned)__cvta_generic_to_shared(queue);
-    asm volatile("" : "+r"(hcell1), "+r"(ylast), "+r"(thr2_r), "+r"(kini_r), "+r"(queue_s));
+    unsigned thr2_r = thr2, queue_s = (unsigned)__cvta_generic_to_shared(queue);
+    asm volatile("" : "+r"(thr2_r), "+r"(queue_s));
 
+    // "b > ini seen" per pixel: acc holds the running max of the emitted scores (one VIMNMX per row instead of add + or)
 #define B2_FW_FLAGS()                                                                                          \
     {                                                                                                           \
-        const unsigned hit = ((accE >> 8) & 1u) | ((accO >> 7) & 2u) | ((accE >> 22) & 4u) | ((accO >> 21) & 8u); \
+        const unsigned tE = accE + kini, tO = accO + kini;      /* bit 8 of each u16 lane: score > ini */       \
+        const unsigned hit = ((tE >> 8) & 1u) | ((tO >> 7) & 2u) | ((tE >> 22) & 4u) | ((tO >> 21) & 8u);       \
         if (store_lane && (hit & sameA)) flags[ci * L.n_cols + cjA] = 1;                                       \
         if (store_lane && (hit & ~sameA)) flags[ci * L.n_cols + cjA + 1] = 1;                                  \
         accE = accO = 0;                                                                                        \
@@ -244,78 +252,116 @@ fast_score_win_kernel(const __grid_constant__ B2Geom g, const B2Images im, uint2
             qn = 0;                                                                                             \
         }                                                                                                       \
     }
+    // ---- one row step.  MODE 0: rows 0..5 only fill the window.  MODE 1: rows 6, 7 also compute scores (they prime the
+    // 3-row NMS state).  MODE 2: steady state, emits output row y = ya + r - 8.  The steady state has a COMMON form (the
+    // row is neither the first nor the last row of its FAST cell: no masks, no cell bookkeeping) and a SPECIAL form taken
+    // when the countdown `ev` hits zero: cell-boundary rows (neighbour rows of another cell do not suppress), the cell's
+    // iniThFAST flags, the queue flush, and the distance to the next special row.
+    int ev = 0;                                                 // common rows left before the next special row
+#ifdef FWX_PLAIN_STORE
+#define FWX_STORE(a, m, t, has) if (has) asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(m), "r"(t) : "memory");
+#else
+#define FWX_STORE(a, m, t, has)                                                                                \
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}" \
+                 ::"r"(a), "r"(m), "r"(t), "r"(has) : "memory");
+#endif
+#define B2_FW_ROW(MODE)                                                                                        \
+    {                                                                                                           \
+        fs_cp_async4(ring_s + (((r + FS_PF) & (FW_RING - 1)) << 7), col0 + min(off, offmax));                  \
+        off += pitch;                                                                                           \
+        const unsigned R1 = fs_wait_lds(ring_s + ((r & (FW_RING - 1)) << 7));                                  \
+        const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);  \
+        const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);  \
+        const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);                    \
+        const unsigned Ep = __shfl_up_sync(0xFFFFFFFFu, E1, 1), n0 = __shfl_up_sync(0xFFFFFFFFu, O1, 1);      \
+        const unsigned n1 = __byte_perm(Ep, E1, 0x5432);       /* (x-2, x): the high half is this lane's own pixel, */ \
+        const unsigned n2 = __byte_perm(n0, O1, 0x5432);       /* (x-1, x+1)   so lane 0's last pixel gets a valid score */ \
+        if (MODE >= 1) {                                                                                        \
+            /* unit Q = pairs (2, 5, 3, 4), unit W = pairs (1, 6, 0, 7): every load asks for exactly what it uses */ \
+            const uint2 q1 = fw_lds64(a1), w1 = fw_lds64(a1 + 512);       /* dy +2: pairs 2,5 | 1,6 */         \
+            const uint4 w2 = fw_lds128(a2 + 512);                          /* dy +1: pairs 1,6,0,7 */           \
+            const uint2 q3 = fw_lds64(a3 + 8);                             /* dy  0: pairs 3,4 */               \
+            const uint4 w3 = fw_lds128(a3 + 512);                          /*        pairs 1,6,0,7 */           \
+            const uint4 w4 = fw_lds128(a4 + 512);                          /* dy -1 */                          \
+            const uint2 q5 = fw_lds64(a5), w5 = fw_lds64(a5 + 512);       /* dy -2 */                          \
+            const uint4 q6 = fw_lds128(a6);                                /* dy -3: pairs 2,5,3,4 */           \
+            unsigned bE, bO;                                                                                    \
+            {                                                                                                   \
+                const unsigned v[16] = {E1, O1, q1.y, w2.y, w3.y, w4.y, q5.y, q6.w,                            \
+                                        q6.z, q6.x, w5.x, w4.z, w3.z, w2.z, w1.x, n2};                         \
+                bE = fast_b_pair<NQ, NE>(v, q3.x);                                                              \
+            }                                                                                                   \
+            {                                                                                                   \
+                const unsigned v[16] = {O1, c2, w1.y, w2.w, w3.w, w4.w, w5.y, q6.y,                            \
+                                        q6.w, q6.z, q5.x, w4.x, w3.x, w2.x, q1.x, E1};                         \
+                bO = fast_b_pair<NQ, NE>(v, q3.y);                                                              \
+            }                                                                                                   \
+            const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1); \
+            const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;                                             \
+            const unsigned rE = bO & mrE;                                                                       \
+            const unsigned lO = bE & mlO;                                                                       \
+            const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;                                             \
+            const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);                                    \
+            if (MODE == 2) {                                                                                    \
+                unsigned nbE, nbO;                                                                              \
+                const bool special = ev == 0;                                                                   \
+                int cy = 0, yy = 0;                                                                             \
+                if (!special) {                                                                                 \
+                    --ev;                                                                                       \
+                    nbE = vmax3(rmE_a, rmE, vmax2(sdE_b, thr2_r));                                              \
+                    nbO = vmax3(rmO_a, rmO, vmax2(sdO_b, thr2_r));                                              \
+                } else {                                                                                        \
+                    yy = ya + r - 8;                            /* (not from meta: lane 0's x field is negative) */ \
+                    cy = yy - B2_EDGE - ci * hcell;                                                             \
+                    const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;                                             \
+                    const unsigned dn = (cy != hcell - 1 && yy != ylast) ? 0xFFFFFFFFu : 0u;                    \
+                    nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2_r));                                    \
+                    nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2_r));                                    \
+                }                                                                                               \
+                const unsigned oE = keep_if_greater_and(bE_b, nbE, inE), oO = keep_if_greater_and(bO_b, nbO, inO); \
+                const unsigned m4 = __byte_perm(oE, oO, 0x6240);                                                \
+                accE = vmax2(accE, oE); accO = vmax2(accO, oO);                                                 \
+                const int has = store_lane && m4 != 0;                                                          \
+                const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);                                           \
+                FWX_STORE(queue_s + 8u * (unsigned)(qn + __popc(bal & lt_mask)), m4, meta, has)                 \
+                qn += __popc(bal);                                                                              \
+                meta += 0x1000u;                                                                                \
+                if (special) {                                                                                  \
+                    int cyn = cy + 1;                           /* row of the NEXT output row inside its cell */ \
+                    if (cy == hcell - 1) { B2_FW_FLAGS() ++ci; meta += 0x1000000u; cyn = 0; }                   \
+                    if (qn > FS_QUEUE - 30 * FS_FLUSH) B2_FW_FLUSH()                                            \
+                    /* common rows before the next special one: the next row is special when it is the first row of a \
+                       cell; otherwise run until the last row of the cell / of the level, at most FS_FLUSH - 1 rows */ \
+                    ev = cyn == 0 ? 0 : min(min(hcell - 1 - cyn, ylast - (yy + 1)), FS_FLUSH - 1);              \
+                    ev = max(ev, 0);                                                                            \
+                }                                                                                               \
+            }                                                                                                   \
+            rmE_a = rmE_b; rmO_a = rmO_b;                                                                       \
+            rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;                                                     \
+            sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);                                                       \
+        }                                                                                                       \
+        fw_sts128(a6, n2, c2, E1, O1);          /* Q = pairs 2, 5, 3, 4 */                                      \
+        fw_sts128(a6 + 512, n1, c3, n0, E2);    /* W = pairs 1, 6, 0, 7 */                                      \
+        const unsigned tmp = a6;                                                                                \
+        a6 = a5; a5 = a4; a4 = a3; a3 = a2; a2 = a1; a1 = tmp;                                                  \
+    }
 
+    int r = 0;
+#pragma unroll 1
+    for (; r < 6; ++r) B2_FW_ROW(0)
+#pragma unroll 1
+    for (; r < 8; ++r) B2_FW_ROW(1)
     // two rows per trip: the scheduler interleaves the min/max trees of consecutive rows (more independent work per
     // warp beats a fifth CTA per SM: 9.41 -> 9.13 us/pair with 121 registers, 4 CTAs)
+#ifdef FWX_UNROLL1
+#pragma unroll 1
+#else
 #pragma unroll 2
-    for (int r = 0; r < nsteps; ++r) {
-        fs_cp_async4(ring_s + (((r + FS_PF) & (FW_RING - 1)) << 7), col0 + min(off, offmax));
-        off += pitch;
-        const unsigned R1 = fs_wait_lds(ring_s + ((r & (FW_RING - 1)) << 7));
-        const unsigned E1 = __byte_perm(R1, 0x64646464u, 0x4240), O1 = __byte_perm(R1, 0x64646464u, 0x4341);
-        const unsigned E2 = __shfl_down_sync(0xFFFFFFFFu, E1, 1), O2 = __shfl_down_sync(0xFFFFFFFFu, O1, 1);
-        const unsigned c2 = __byte_perm(E1, E2, 0x5432), c3 = __byte_perm(O1, O2, 0x5432);
-        const unsigned Ep = __shfl_up_sync(0xFFFFFFFFu, E1, 1), n0 = __shfl_up_sync(0xFFFFFFFFu, O1, 1);
-        const unsigned n1 = __byte_perm(Ep, E1, 0x5432);       // (x-2, x): the high half is this lane's own pixel,
-        const unsigned n2 = __byte_perm(n0, O1, 0x5432);       // (x-1, x+1)   so lane 0's last pixel gets a valid score
-        // new row's pairs: n0, n1, n2, E1, O1, c2, c3, E2  (P[0..7] of the register version)
-        if (r >= 6) {
-            // unit Q = pairs (2, 5, 3, 4), unit W = pairs (1, 6, 0, 7): every load asks for exactly what it uses
-            // (ptxas splits a partly used LDS.128 into scalar loads, 4-way bank conflicts at this lane stride)
-            const uint2 q1 = fw_lds64(a1), w1 = fw_lds64(a1 + 512);       // dy +2: pairs 2,5 | 1,6
-            const uint4 w2 = fw_lds128(a2 + 512);                          // dy +1: pairs 1,6,0,7
-            const uint2 q3 = fw_lds64(a3 + 8);                             // dy  0: pairs 3,4
-            const uint4 w3 = fw_lds128(a3 + 512);                          //        pairs 1,6,0,7
-            const uint4 w4 = fw_lds128(a4 + 512);                          // dy -1
-            const uint2 q5 = fw_lds64(a5), w5 = fw_lds64(a5 + 512);       // dy -2
-            const uint4 q6 = fw_lds128(a6);                                // dy -3: pairs 2,5,3,4
-            unsigned bE, bO;
-            {
-                const unsigned v[16] = {E1, O1, q1.y, w2.y, w3.y, w4.y, q5.y, q6.w,
-                                        q6.z, q6.x, w5.x, w4.z, w3.z, w2.z, w1.x, n2};
-                bE = fast_b_pair<NQ, NE>(v, q3.x);
-            }
-            {
-                const unsigned v[16] = {O1, c2, w1.y, w2.w, w3.w, w4.w, w5.y, q6.y,
-                                        q6.w, q6.z, q5.x, w4.x, w3.x, w2.x, q1.x, E1};
-                bO = fast_b_pair<NQ, NE>(v, q3.y);
-            }
-            const unsigned bOp = __shfl_up_sync(0xFFFFFFFFu, bO, 1), bEn = __shfl_down_sync(0xFFFFFFFFu, bE, 1);
-            const unsigned lE = __byte_perm(bOp, bO, 0x5432) & mlE;
-            const unsigned rE = bO & mrE;
-            const unsigned lO = bE & mlO;
-            const unsigned rO = __byte_perm(bE, bEn, 0x5432) & mrO;
-            const unsigned rmE = vmax3(lE, bE, rE), rmO = vmax3(lO, bO, rO);
-            if (r >= 8) {
-                const unsigned up = cy != 0 ? 0xFFFFFFFFu : 0u;
-                const unsigned dn = (cy != hcell1 && y != ylast) ? 0xFFFFFFFFu : 0u;
-                const unsigned nbE = vmax3(rmE_a & up, rmE & dn, vmax2(sdE_b, thr2_r));
-                const unsigned nbO = vmax3(rmO_a & up, rmO & dn, vmax2(sdO_b, thr2_r));
-                const unsigned oE = keep_if_greater(bE_b, nbE) & inE, oO = keep_if_greater(bO_b, nbO) & inO;
-                const unsigned m4 = __byte_perm(oE, oO, 0x6240);
-                accE |= oE + kini_r; accO |= oO + kini_r;
-                const bool has = store_lane && m4 != 0;
-                const unsigned bal = __ballot_sync(0xFFFFFFFFu, has);
-                if (has)
-                    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(queue_s + 8u * (unsigned)(qn + __popc(bal & lt_mask))),
-                                 "r"(m4), "r"(meta) : "memory");
-                qn += __popc(bal);
-                ++y;
-                meta += 0x1000u;
-                if (cy == hcell1) { B2_FW_FLAGS() cy = 0; ++ci; meta += 0x1000000u; } else ++cy;
-                if (++since_flush == FS_FLUSH) { B2_FW_FLUSH() since_flush = 0; }
-            }
-            rmE_a = rmE_b; rmO_a = rmO_b;
-            rmE_b = rmE; rmO_b = rmO; bE_b = bE; bO_b = bO;
-            sdE_b = vmax2(lE, rE); sdO_b = vmax2(lO, rO);
-        }
-        fw_sts128(a6, n2, c2, E1, O1);          // Q = pairs 2, 5, 3, 4
-        fw_sts128(a6 + 512, n1, c3, n0, E2);    // W = pairs 1, 6, 0, 7
-        const unsigned tmp = a6;
-        a6 = a5; a5 = a4; a4 = a3; a3 = a2; a2 = a1; a1 = tmp;
-    }
+#endif
+    for (; r < nsteps; ++r) B2_FW_ROW(2)
     B2_FW_FLUSH()
     B2_FW_FLAGS()
+#undef B2_FW_ROW
 #undef B2_FW_FLAGS
 #undef B2_FW_FLUSH
 }

@@ -16,7 +16,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2orb.so")
+# B2ORB_LIB: harness-only override to load the experiment build (csrc `make variants` -> libb2orb_variants.so)
+LIB_PATH = os.environ.get("B2ORB_LIB") or os.path.join(_HERE, "libb2orb.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])

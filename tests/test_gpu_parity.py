@@ -87,6 +87,7 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth):
 
 
 @pytest.mark.parametrize("opt", [("fast_band", 0), ("fast_band", 1), ("fast_band", 2), ("fast_band", 3), ("blur_band", 0), ("blur_band", 1),
+                                 ("blur_band", 16), ("blur_band", 17),   # TMA-staged blur: only in the variants build
                                  ("fork_max", 0), ("pdl", 0),
                                  ("pdl", 1), ("export_max", 0)], ids=lambda o: f"{o[0]}={o[1]}")
 def test_launch_time_choices_agree_with_oracle(opt, fe, oracle, synth):
