@@ -52,8 +52,20 @@ def gather_blocks(local, rank, world, dist=None, device="cpu"):
     if world == 1:
         return local
     import torch
-    names = sorted(local)
-    n_local = len(local[names[0]]) if names else 0
+    # every rank must run the same collectives, also one whose block is empty (world > nframes): take the slab names,
+    # dtypes and trailing shapes from the first rank that has any
+    mine = {k: (np.asarray(v).dtype.descr if np.asarray(v).dtype.names else np.asarray(v).dtype.str,
+                tuple(np.asarray(v).shape[1:])) for k, v in local.items()} if local else None
+    schemas = [None] * world
+    dist.all_gather_object(schemas, mine)
+    schema = next((s for s in schemas if s), None)
+    if schema is None:
+        return {} if rank == 0 else None
+    names = sorted(schema)
+    if not local:
+        local = {k: np.zeros((0,) + tuple(shp), np.dtype([tuple(f) for f in dt]) if isinstance(dt, list) else np.dtype(dt))
+                 for k, (dt, shp) in schema.items()}
+    n_local = len(local[names[0]])
     counts = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
     dist.all_gather(counts, torch.tensor([n_local], dtype=torch.int64, device=device))
     counts = [int(c.item()) for c in counts]
@@ -61,7 +73,8 @@ def gather_blocks(local, rank, world, dist=None, device="cpu"):
     out = {}
     for k in names:
         a = np.ascontiguousarray(local[k])
-        raw = a.view(np.uint8).reshape(n_local, -1) if a.dtype.names else a.reshape(n_local, -1)
+        row = int(np.prod(a.shape[1:], dtype=np.int64)) * (a.dtype.itemsize if a.dtype.names else 1)
+        raw = a.view(np.uint8).reshape(n_local, row) if a.dtype.names else a.reshape(n_local, row)
         padded = np.zeros((cap, raw.shape[1]), raw.dtype)
         padded[:n_local] = raw
         t = torch.from_numpy(padded).to(device)

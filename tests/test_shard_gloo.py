@@ -43,17 +43,17 @@ class FakeFrontend:
         return {"n_match": sig.astype(np.int32), "n_circ": circ.astype(np.int32), "kp": kp}
 
 
-def sequential():
+def sequential(nframes=NFRAMES):
     shard = pkg("shard")
-    return shard.run_block(FakeFrontend(), load, NFRAMES, 0, 1, batch=4, temporal=True)
+    return shard.run_block(FakeFrontend(), load, nframes, 0, 1, batch=4, temporal=True)
 
 
-def worker(rank, world, port, q):
+def worker(rank, world, port, q, nframes=NFRAMES):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     shard = pkg("shard")
     fe = FakeFrontend()
-    local = shard.run_block(fe, load, NFRAMES, rank, world, batch=4, temporal=True, reset=fe.reset)
+    local = shard.run_block(fe, load, nframes, rank, world, batch=4, temporal=True, reset=fe.reset)
     out = shard.gather_blocks(local, rank, world, dist)
     if rank == 0:
         q.put({k: v.tobytes() for k, v in out.items()})
@@ -75,13 +75,15 @@ def test_frame_blocks_partition_the_sequence():
     assert shard.local_range(100, 1, 4, False) == (25, 25, 50)
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_sharded_equals_sequential_over_gloo(world):
-    ref = sequential()
+@pytest.mark.parametrize("world,nframes", [(2, NFRAMES), (3, NFRAMES), (3, 2)], ids=["world2", "world3", "world3_more_ranks_than_frames"])
+def test_sharded_equals_sequential_over_gloo(world, nframes):
+    """The last case leaves a rank without frames: it must still run every collective of the gather (it used to skip
+    them, and the other ranks hung)."""
+    ref = sequential(nframes)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000 + world
-    procs = [ctx.Process(target=worker, args=(r, world, port, q)) for r in range(world)]
+    port = 29500 + os.getpid() % 2000 + world + 7 * nframes
+    procs = [ctx.Process(target=worker, args=(r, world, port, q, nframes)) for r in range(world)]
     for p in procs:
         p.start()
     got = q.get(timeout=120)
