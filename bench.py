@@ -550,6 +550,28 @@ def main():
                    "what": "b2orb_stereo_frontend, 1 pair per call, pinned host images in -> keypoints, descriptors, "
                            "matches on the host; wall clock around the call"}
         hl.close()
+        # The UNCHANGED-caller path: what the reference's own call sequence costs with nothing fused —
+        # two extractor instances (the two std::threads of src/feature-tracker.cpp:153-156 = two handles, async), PAGEABLE
+        # images, then BFMatcher.match on host descriptors, then the host filter loops as b2orb_stereo_filter.
+        if rank == 0 and rect_maps is None:
+            hL, hR = mk_handle(1), mk_handle(1)
+            lat_u = []
+            for k in range(min(args.latency_calls, 100) + 10):
+                i = k % pool
+                il, ir = ls[i], rs[i]                               # pageable numpy arrays, tight rows
+                t0 = time.perf_counter()
+                hL.extract_async(il); hR.extract_async(ir)
+                kl_, dl_ = hL.extract_wait(); kr_, dr_ = hR.extract_wait()
+                ti_, di_ = hL.match(dl_, dr_)
+                hL.stereo_filter(ti_, di_, kl_, dl_, kr_, dr_)
+                lat_u.append((time.perf_counter() - t0) * 1e3)
+            lat_u = sorted(lat_u[10:])
+            latency["unchanged_caller"] = {
+                "p50_ms": round(lat_u[len(lat_u) // 2], 4), "p95_ms": round(lat_u[int(len(lat_u) * 0.95)], 4),
+                "what": "the reference's own call sequence, nothing fused: b2orb_extract_async on two handles (pageable images) + "
+                        "_wait, b2orb_match (host descriptors in, host lists out), b2orb_stereo_filter; through the ctypes binding, "
+                        "which allocates and copies its result arrays per call"}
+            hL.close(); hR.close()
 
     # ---------------- parity spot checks of what was just timed (the oracle is the checker, never the thing measured) --------
     verified = None
