@@ -240,6 +240,13 @@ def other_configs(fe, synth, device, peak, dbg, checker):
         b_pair, _ = algorithmic_bytes(level_sizes(w, h), nfeat, temporal)
         res = {"workload": f"{name} {w}x{h}, {nfeat} feats", "pairs_per_step": npairs, "steps": steps, "value": round(value, 1),
                "unit": UNIT, "frac_of_hbm_peak": round(b_pair * value / 1e9 / peak, 4)}
+        hd.profile_enable(True)                                  # per-kernel device time of this shape (CUDA events between launches)
+        for _ in range(2):
+            run()
+        hd.sync()
+        prof = hd.profile_read()
+        hd.profile_enable(False)
+        res["kernel_us_per_pair"] = {k: round(v[0] * 1e3 / (2 * npairs), 3) for k, v in prof.items() if v[1]}
         if checker:
             from oracle import oracle as orc
             o = hd.stereo_download(npairs, hd.alloc_stereo_out(npairs))
@@ -554,7 +561,7 @@ def main():
         # two extractor instances (the two std::threads of src/feature-tracker.cpp:153-156 = two handles, async), PAGEABLE
         # images, then BFMatcher.match on host descriptors, then the host filter loops as b2orb_stereo_filter.
         if rank == 0 and rect_maps is None:
-            hL, hR = mk_handle(1), mk_handle(1)
+            hL, hR = mk_handle(2), mk_handle(2)
             lat_u = []
             for k in range(min(args.latency_calls, 100) + 10):
                 i = k % pool
