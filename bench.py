@@ -213,12 +213,25 @@ def other_configs(fe, synth, device, peak, dbg, checker):
     the cfsd shape the paced trigger of config 3 (one frame every 5 ms = the 200 Hz IMU rate, config/cfsd.yml:76)."""
     import torch
     out = {}
-    plan = {"euroc": (64, 6), "cfsd": (64, 6), "kitti_yml": (32, 6), "4k": (4, 4)}
+    plan = {"euroc": (64, 6), "cfsd": (64, 6), "kitti_yml": (32, 6), "4k": (4, 4), "real_cfsd": (64, 6), "real_kitti": (32, 6)}
+    real = {"real_cfsd": ("cfsd", [("cfsd360p_left", "cfsd360p_right"), ("cfsd_set_110_left", "cfsd_set_110_right")]),
+            "real_kitti": ("kitti_yml", [("kitti0", "kitti2")])}
     for name, (npairs, steps) in plan.items():
-        w, h, nfeat, ini, mn = synth.SHAPES[name]
+        w, h, nfeat, ini, mn = synth.SHAPES[real[name][0] if name in real else name]
         cfg = (nfeat, synth.SCALE_FACTOR, synth.N_LEVELS, ini, mn)
-        temporal = name.startswith("kitti")
-        ls, rs = synth.sequence(name, npairs, seed=11)
+        temporal = "kitti" in name
+        if name in real:
+            # REAL camera frames shipped with the reference (decoded once into tests/golden/real/*.npz): the synthetic texture
+            # is far denser in corners than any real frame, so this is the line that says what real input statistics cost
+            try:
+                fr = [(np.load(os.path.join(ROOT, "tests", "golden", "real", a + ".npz"))["image"],
+                       np.load(os.path.join(ROOT, "tests", "golden", "real", b_ + ".npz"))["image"]) for a, b_ in real[name][1]]
+            except OSError:
+                continue
+            ls = np.stack([fr[i % len(fr)][0] for i in range(npairs)]); rs = np.stack([fr[i % len(fr)][1] for i in range(npairs)])
+            assert ls.shape[1:] == (h, w)
+        else:
+            ls, rs = synth.sequence(name, npairs, seed=11)
         pitch = (w + 31) // 32 * 32
         d_l = torch.zeros((npairs, h, pitch), dtype=torch.uint8, device="cuda"); d_r = torch.zeros_like(d_l)
         d_l[:, :, :w] = torch.from_numpy(ls).cuda(); d_r[:, :, :w] = torch.from_numpy(rs).cuda()
@@ -258,6 +271,13 @@ def other_configs(fe, synth, device, peak, dbg, checker):
                 nl == len(kl) and nr == len(kr) and o["kp_l"][0, :nl].tobytes() == kl.tobytes() and np.array_equal(o["desc_l"][0, :nl], dl)
                 and o["kp_r"][0, :nr].tobytes() == kr.tobytes() and np.array_equal(o["desc_r"][0, :nr], dr)
                 and np.array_equal(o["train_idx"][0, :nl], ti) and np.array_equal(o["dist"][0, :nl], di))
+            # the reference's CPU implementation on the same frames: one round of min(pairs, host cores) pairs, one per thread
+            run_cpu, kind_cpu = cpu_runner(orc)
+            ncpu = min(npairs, os.cpu_count() or 1)
+            t0 = time.perf_counter()
+            run_cpu(cfg, ls[:ncpu], rs[:ncpu], synth.MATCH_RATIO, synth.MIN_MATCH_DIST, synth.MAX_VERTICAL_PIXEL_DIST, ncpu, 1, temporal)
+            res["cpu_baseline"] = {"value": round(ncpu / (time.perf_counter() - t0), 2), "unit": UNIT, "cores": ncpu, "kind": kind_cpu,
+                                   "sample": f"{ncpu} pairs, one per thread"}
         hd.close()
         # single-pair latency, pinned host images in, kept result set out
         hl = fe.Handle(*cfg, w, h, max_images=2, device=device)
