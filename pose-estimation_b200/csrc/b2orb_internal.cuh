@@ -147,8 +147,12 @@ void b2_launch_fast_vote(const B2Geom& g, const uint2* raw, const int* raw_cnt, 
                          int* cand_cnt, int nimg, cudaStream_t s);
 void b2_launch_octree(const B2Geom& g, const uint32_t* cand, const int* cand_cnt, unsigned short* pnode,
                       unsigned* scratch, uint32_t* sel, int* sel_cnt, int nimg, int force_legacy, cudaStream_t s);
+struct B2DescCache;   // describe.cu: tensor maps of a handle's slabs for the TMA-staged kernel (use_tma = 0: cp.async kernel)
+B2DescCache* b2_desc_cache_create();
+void b2_desc_cache_destroy(B2DescCache* c);
 void b2_launch_describe(const B2Geom& g, const B2Images& im, const uint32_t* sel, const int* sel_cnt,
-                        const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, cudaStream_t s);
+                        const unsigned* ic_table, void* kps, uint8_t* desc, int* n_out, int nimg, B2DescCache* cache,
+                        int use_tma, cudaStream_t s);
 #define B2_IC_WORDS (4 * 16 * 9 * 2)   // IC_Angle weight table, describe.cu
 void b2_launch_match(const B2MatchProblem* probs, int nprob, int max_nq, cudaStream_t s);
 // Problem table of a stereo batch, written on the device so that re-binding never synchronises the host.

@@ -157,7 +157,8 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im, int variant) {
     b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[BL_WARPS][BL_SLOTS * BL_ROWB];
     const int lane = threadIdx.x & 31;
-    const int task = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    const int wid = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);   // broadcast: the compiler then knows it is warp-uniform
+    const int task = blockIdx.x * BL_WARPS + wid;
     if (task >= g.total_blur_tasks[variant]) return;
     const int band_rows = B2_BLUR_BAND << (2 * variant);
     const int b = blockIdx.y;
@@ -175,7 +176,7 @@ blur_kernel(const __grid_constant__ B2Geom g, const B2Images im, int variant) {
 
     // a strip needs the border code if it touches column 0 or its last lane's halo reaches beyond w-1
     const bool edge = strip == 0 || strip * 128 + 128 + 3 > L.w - 1;
-    uint8_t* ring = s_ring[threadIdx.x >> 5];
+    uint8_t* ring = s_ring[wid];
     if (g.tap_sat) {   // warp-uniform (whole launch)
         if (edge) blur_task<true, true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
         else blur_task<false, true>(src, spitch, dst, L.pitch, L.w, L.h, x, y0, rows, lane, ring, g);
@@ -293,7 +294,7 @@ blur_tma_kernel(const __grid_constant__ B2Geom g, const B2Images im, int variant
     b2_pdl_wait();
     __shared__ __align__(128) uint8_t s_ring[BL_WARPS][BT_RING * BL_ROWB];
     __shared__ __align__(8) unsigned long long s_mbar[BL_WARPS][2];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wid = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);
     const int task = blockIdx.x * BL_WARPS + wid;
     if (task >= g.total_blur_tasks[variant]) return;
     const int band_rows = B2_BLUR_BAND << (2 * variant);

@@ -55,6 +55,7 @@ struct B2Tuning {
     int fast_band = -1;      // FAST band variant 0 / 1 / 2 / 3 (16 / 32 / 64 / 128 rows), -1 = by batch size
     int blur_band = -1;      // blur band variant 0 / 1 (32 / 128 rows), -1 = by batch size
     int octree_points = 0;   // 1 = quadtree by point passes only (the count-pyramid path's fallback)
+    int describe_tma = 1;    // 0 = descriptor windows staged by per-lane cp.async instead of TMA boxes
     int pipe_chunk = 64;     // pairs per chunk of the pipelined host path, 0 = off
     int pipe_lanes = 3;      // lanes (workspaces + streams) the chunks rotate over
     int pipe_trace = 0;      // per-chunk timeline on stderr
@@ -150,6 +151,7 @@ struct b2orb_handle {
     uint8_t* d_mask = nullptr;                           // [npair_cap][cap] _curFeatureMask
     // next row f3: device-resident feature pool (root handle) + host copies of the last pool track
     B2Pool* pool = nullptr;
+    B2DescCache* desc_cache = nullptr;   // tensor maps of this handle's slabs (describe.cu), created on first use
     int pool_max_age = 8;
     std::vector<int> trk_circ_hist;                      // trainIdx of the circular matches of the last pool track
     std::vector<unsigned long long> trk_ids;             // ... and the feature ids behind them (_matchedFeatureIDs)
@@ -544,7 +546,8 @@ int launch_extract(b2orb_handle* h, const B2Images& im, int nimg) {
         ++h->launches;
     }
     prof_mark(h, B2ORB_K_DESCRIBE);
-    b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_ic_table, h->d_kps, h->d_desc, h->d_nkp, nimg, s);
+    if (!h->desc_cache) h->desc_cache = b2_desc_cache_create();
+    b2_launch_describe(g, im, h->d_sel, h->d_sel_cnt, h->d_ic_table, h->d_kps, h->d_desc, h->d_nkp, nimg, h->desc_cache, tn.describe_tma, s);
     ++h->launches;
     prof_mark(h, -1);
     B2_CUDA(h, cudaGetLastError());
@@ -869,6 +872,7 @@ void b2orb_destroy(b2orb_handle* h) {
         if (h->d_map2[e]) cudaFree(h->d_map2[e]);
     }
     if (h->pool) b2_pool_destroy(h->pool);
+    if (h->desc_cache) b2_desc_cache_destroy(h->desc_cache);
     if (h->h_async_n) cudaFreeHost(h->h_async_n);
     if (h->d_packed) cudaFree(h->d_packed);
     if (h->d_tri_in) cudaFree(h->d_tri_in);
@@ -1794,6 +1798,7 @@ int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
     else if (k == "fast_band") t.fast_band = value;
     else if (k == "blur_band") t.blur_band = value;
     else if (k == "octree_points") t.octree_points = value ? 1 : 0;
+    else if (k == "describe_tma") t.describe_tma = value ? 1 : 0;
     else if (k == "pipe_trace") t.pipe_trace = value;
     else if (k == "pipe_chunk" || k == "pipe_lanes") {
         if (!h->lanes.empty()) return fail(h, B2ORB_ERR_INVALID, "pipeline options must be set before the first pipelined call");

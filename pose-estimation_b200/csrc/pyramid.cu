@@ -222,8 +222,8 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
               const short* __restrict__ yw) {
     b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
-    resize_task(g, im, blockIdx.y, level, band_rows, blockIdx.x * RS_WARPS + (threadIdx.x >> 5), xofs, xw, yofs, yw,
-                s_ring[threadIdx.x >> 5]);
+    const int wid = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);   // broadcast: warp-uniform for the compiler
+    resize_task(g, im, blockIdx.y, level, band_rows, blockIdx.x * RS_WARPS + wid, xofs, xw, yofs, yw, s_ring[wid]);
 }
 
 // cv::resize(INTER_LINEAR) to 2*half_w x dh -> cvtColor(BGR2GRAY) -> left / right halves, fused: one thread per output

@@ -89,10 +89,12 @@ def test_quadtree_paths_agree_with_oracle(mode, fe, oracle, synth):
 @pytest.mark.parametrize("opt", [("fast_band", 0), ("fast_band", 1), ("fast_band", 2), ("fast_band", 3), ("blur_band", 0), ("blur_band", 1),
                                  ("blur_band", 16), ("blur_band", 17),   # TMA-staged blur: only in the variants build
                                  ("fork_max", 0), ("pdl", 0),
-                                 ("pdl", 1), ("export_max", 0)], ids=lambda o: f"{o[0]}={o[1]}")
+                                 ("pdl", 1), ("export_max", 0),
+                                 ("describe_tma", 0), ("describe_tma", 1)],   # descriptor windows by cp.async / by TMA boxes
+                                ids=lambda o: f"{o[0]}={o[1]}")
 def test_launch_time_choices_agree_with_oracle(opt, fe, oracle, synth):
     """Every launch-time choice the library makes by batch size (FAST band length, side-stream blur, programmatic
-    launch chain, direct export) must give the oracle's bits: pinned one at a time with b2orb_debug_set on a
+    launch chain, direct export, how the descriptor windows are staged) must give the oracle's bits: pinned one at a time with b2orb_debug_set on a
     low-texture image (both FAST thresholds in play)."""
     w, h = 400, 300
     ls, rs = synth.sequence((w, h), 2, seed=21, passes=8)
