@@ -292,8 +292,8 @@ describe_kernel(const __grid_constant__ B2Geom g, const B2Images im, const uint3
 constexpr int WTA_ROWB = 48, WTB_ROWB = 64;          // box widths in bytes (multiples of 16; 31 + 15 and 37 + 15 are needed)
 constexpr int WTA_BYTES = 1536;                      // 31 rows x 48 B = 1488, padded to the 128-B alignment TMA wants
 constexpr int WTB_BYTES = 2432;                      // 37 rows x 64 B = 2368
-constexpr int WT_TX = WA_ROWS * WTA_ROWB + WB_ROWS * WTB_ROWB;   // bytes one keypoint's two boxes deliver
-constexpr int WT_SMEM = DS_WARPS * 2 * (WTA_BYTES + WTB_BYTES) + DS_WARPS * 2 * 8;
+constexpr int WT_BUF = WTB_BYTES;                    // one staging buffer holds either window; two per warp
+constexpr int WT_SMEM = DS_WARPS * 2 * WT_BUF + DS_WARPS * 2 * 8;
 
 struct DescMaps {
     CUtensorMap raw0[2];                 // level 0: left block (images < split), right block
@@ -341,15 +341,15 @@ describe_tma_kernel(const __grid_constant__ B2Geom g, const B2Images im, const D
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int wid = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);   // broadcast: warp-uniform for the compiler
-    const unsigned win_s = (unsigned)__cvta_generic_to_shared(s_dyn) + wid * 2 * (WTA_BYTES + WTB_BYTES);
-    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(s_dyn) + DS_WARPS * 2 * (WTA_BYTES + WTB_BYTES) + wid * 16;
+    const unsigned win_s = (unsigned)__cvta_generic_to_shared(s_dyn) + wid * 2 * WT_BUF;
+    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(s_dyn) + DS_WARPS * 2 * WT_BUF + wid * 16;
     if (lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s + 8));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();                                    // weight table + this warp's barriers
-    // per-level counts -> prefix (same for every keypoint of this image)
+    // per-level counts -> inclusive prefix in lanes 0..nlevels-1 (same for every keypoint of this image)
     int cnt_l = 0;
     if (lane < g.nlevels) cnt_l = max(sel_cnt[b * g.nlevels + lane], 0);
     int pre = cnt_l;
@@ -358,58 +358,59 @@ describe_tma_kernel(const __grid_constant__ B2Geom g, const B2Images im, const D
         const int v = __shfl_up_sync(0xFFFFFFFFu, pre, o);
         if (lane >= o) pre += v;
     }
-    const int total = __shfl_sync(0xFFFFFFFFu, pre, 15);
+    const int total = __shfl_sync(0xFFFFFFFFu, pre, 15);   // nlevels <= 12: lane 15 holds the sum
     if (blockIdx.x == 0 && threadIdx.x == 0) n_out[b] = min(total, g.kp_cap);
-    unsigned pk[8];
-    {
-        const uint4* pp = reinterpret_cast<const uint4*>(kPattern + lane * 32);
-        const uint4 p0 = pp[0], p1 = pp[1];
-        pk[0] = p0.x ^ 0x80808080u; pk[1] = p0.y ^ 0x80808080u; pk[2] = p0.z ^ 0x80808080u; pk[3] = p0.w ^ 0x80808080u;
-        pk[4] = p1.x ^ 0x80808080u; pk[5] = p1.y ^ 0x80808080u; pk[6] = p1.z ^ 0x80808080u; pk[7] = p1.w ^ 0x80808080u;
-    }
-    const int vv = lane - B2_HALF_PATCH;                // patch row of this lane (lane 31 has none)
-    const unsigned row_off = (unsigned)min(lane, 30) * WTA_ROWB;
-    const unsigned* tw_row = s_ic + (min(abs(vv), 15) * 9) * 2;   // + residue * 16 * 9 * 2 per keypoint
 
-    struct Kp { int slot, level, cx, cy; float response; bool valid; };
-    const auto fetch = [&](int it) {
-        Kp k;
-        k.slot = (blockIdx.x * DS_WARPS + wid) * kpw + it;
-        k.valid = it < kpw && k.slot < total && k.slot < g.kp_cap;
-        k.level = 0; k.cx = k.cy = 0; k.response = 0.f;
-        if (!k.valid) return k;
-        k.level = __popc(__ballot_sync(0xFFFFFFFFu, lane < g.nlevels && pre <= k.slot));
-        const int base = k.level ? __shfl_sync(0xFFFFFFFFu, pre, k.level - 1) : 0;
-        const uint32_t v = sel[(size_t)b * g.sel_total + g.lv[k.level].sel_base + (k.slot - base)];
-        k.cx = (int)(v & 0xFFF) + B2_BORDER;
-        k.cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
-        k.response = (float)(v >> 24);
+    // ---- lane i owns keypoint i of this warp's kpw consecutive output slots: level, position and response are looked up
+    // once, in parallel; the per-keypoint passes below fetch them by shuffle
+    const int slot0 = (blockIdx.x * DS_WARPS + wid) * kpw;
+    const int my_slot = slot0 + lane;
+    const bool my_valid = lane < kpw && my_slot < total && my_slot < g.kp_cap;
+    int my_level = 0, my_base = 0;
+    for (int l = 0; l < g.nlevels; ++l) {              // level = number of levels whose inclusive prefix is <= slot
+        const int p = __shfl_sync(0xFFFFFFFFu, pre, l);
+        if (p <= my_slot) { my_level = l + 1; my_base = p; }
+    }
+    my_level = min(my_level, g.nlevels - 1);
+    unsigned my_v = 0;
+    if (my_valid) my_v = sel[(size_t)b * g.sel_total + g.lv[my_level].sel_base + (my_slot - my_base)];
+    const int nv = __popc(__ballot_sync(0xFFFFFFFFu, my_valid));   // valid keypoints are a prefix of the lanes
+    if (nv == 0) return;
+
+    // box n of the warp: n < nv the un-blurred window of keypoint n, else the blurred window of keypoint n - nv; buffer n & 1
+    const auto issue = [&](int n) {
+        const int kp = n < nv ? n : n - nv;
+        const unsigned v = __shfl_sync(0xFFFFFFFFu, my_v, kp);
+        const int level = __shfl_sync(0xFFFFFFFFu, my_level, kp);
         if (lane == 0) {
-            const unsigned buf = win_s + (it & 1) * (WTA_BYTES + WTB_BYTES), bar = bar_s + (it & 1) * 8;
-            const CUtensorMap* ma = k.level ? &maps->raw[k.level] : &maps->raw0[b < im.split ? 0 : 1];
-            const int za = k.level ? b : (b < im.split ? b : b - im.split);
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(WT_TX) : "memory");
-            dt_load(buf, ma, bar, (k.cx - B2_HALF_PATCH) & ~15, k.cy - B2_HALF_PATCH, za);
-            dt_load(buf + WTA_BYTES, &maps->blur[k.level], bar, (k.cx - 18) & ~15, k.cy - 18, b);
+            const int cx = (int)(v & 0xFFF) + B2_BORDER, cy = (int)((v >> 12) & 0xFFF) + B2_BORDER;
+            const unsigned buf = win_s + (n & 1) * WT_BUF, bar = bar_s + (n & 1) * 8;
+            if (n < nv) {
+                const CUtensorMap* ma = level ? &maps->raw[level] : &maps->raw0[b < im.split ? 0 : 1];
+                const int za = level ? b : (b < im.split ? b : b - im.split);
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(WA_ROWS * WTA_ROWB) : "memory");
+                dt_load(buf, ma, bar, (cx - B2_HALF_PATCH) & ~15, cy - B2_HALF_PATCH, za);
+            } else {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(WB_ROWS * WTB_ROWB) : "memory");
+                dt_load(buf, &maps->blur[level], bar, (cx - 18) & ~15, cy - 18, b);
+            }
         }
-        return k;
     };
 
-    Kp nxt = fetch(0);
-    for (int it = 0; it < kpw; ++it) {
-        const Kp cur = nxt;
-        if (!cur.valid) break;
-        const int slot = cur.slot, level = cur.level, cx = cur.cx, cy = cur.cy;
-        const float response = cur.response;
-        const B2Level& L = g.lv[level];
-        __syncwarp();                                   // every lane is done with the buffer the next boxes land in
-        nxt = fetch(it + 1);                            // in flight during the math below
-        dt_wait(bar_s + (it & 1) * 8, (it >> 1) & 1);   // this keypoint's boxes have landed
-        const unsigned wa_s = win_s + (it & 1) * (WTA_BYTES + WTB_BYTES), wb_s = wa_s + WTA_BYTES;
-
-        // ---- IC_Angle (src/ORBextractor.cc:77-104): lane = patch row; the row's 31 bytes start at byte `ra` of the 48
+    // ---- pass 1: IC_Angle moments (src/ORBextractor.cc:77-104) of every keypoint; lane = patch row v = lane - 15
+    const int vv = lane - B2_HALF_PATCH;
+    const unsigned row_off = (unsigned)min(lane, 30) * WTA_ROWB;
+    const unsigned* tw_row = s_ic + (min(abs(vv), 15) * 9) * 2;   // + residue * 16 * 9 * 2 per keypoint
+    int my_m10 = 0, my_m01 = 0;
+    issue(0);
+    for (int n = 0; n < nv; ++n) {
+        __syncwarp();                                   // every lane is done with the buffer the next box lands in
+        issue(n + 1);                                   // (n + 1 == nv: the first blurred window) in flight during the math
+        dt_wait(bar_s + (n & 1) * 8, (n >> 1) & 1);
+        const unsigned wa_s = win_s + (n & 1) * WT_BUF;
+        const int cx = (int)(__shfl_sync(0xFFFFFFFFu, my_v, n) & 0xFFF) + B2_BORDER;
+        const int ra = (cx - B2_HALF_PATCH) & 15;       // the row's 31 bytes start at byte ra of the 48
         int m10 = 0, rs = 0;
-        const int ra = (cx - B2_HALF_PATCH) & 15, rb = (cx - 18) & 15;
         if (lane < 31) {
             const uint4 r0 = dt_lds128(wa_s + row_off), r1 = dt_lds128(wa_s + row_off + 16), r2 = dt_lds128(wa_s + row_off + 32);
             const unsigned W[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
@@ -427,12 +428,48 @@ describe_tma_kernel(const __grid_constant__ B2Geom g, const B2Images im, const D
             m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
             m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
         }
-        const float angle = fast_atan2_deg((float)m01, (float)m10);
+        if (lane == n) { my_m10 = m10; my_m01 = m01; }
+    }
 
-        // ---- descriptor on the blurred window: lane = output byte (src/ORBextractor.cc:108-147)
+    // ---- between the passes, one lane per keypoint: angle, its sine / cosine, and the keypoint record
+    // (:837-847, 1095-1101) — the scalar math runs once per keypoint instead of on all 32 lanes
+    float my_sn = 0.f, my_ca = 1.f;
+    if (my_valid) {
+        const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
         const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
-        float ca, sn;
-        glibc_sincosf(__fmul_rn(angle, factorPI), sn, ca);
+        glibc_sincosf(__fmul_rn(angle, factorPI), my_sn, my_ca);
+        const B2Level& L = g.lv[my_level];
+        KeyPointOut k;
+        k.x = (float)((int)(my_v & 0xFFF) + B2_BORDER);
+        k.y = (float)((int)((my_v >> 12) & 0xFFF) + B2_BORDER);
+        if (my_level != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }
+        k.size = L.kp_size;
+        k.angle = angle;
+        k.response = (float)(my_v >> 24);
+        k.octave = my_level;
+        k.class_id = -1;
+        kps[(size_t)b * g.kp_cap + my_slot] = k;
+    }
+
+    // ---- pass 2: descriptors on the blurred windows; lane = output byte (src/ORBextractor.cc:108-147)
+    // Rotated-BRIEF pattern: output byte `lane` uses the 32 coordinates kPattern[32 * lane ..], the same for every keypoint,
+    // kept in 8 registers as offset-128 bytes (PRMT into the mantissa of 1.5 * 2^23 + one FADD makes them floats, exactly)
+    unsigned pk[8];
+    {
+        const uint4* pp = reinterpret_cast<const uint4*>(kPattern + lane * 32);
+        const uint4 p0 = pp[0], p1 = pp[1];
+        pk[0] = p0.x ^ 0x80808080u; pk[1] = p0.y ^ 0x80808080u; pk[2] = p0.z ^ 0x80808080u; pk[3] = p0.w ^ 0x80808080u;
+        pk[4] = p1.x ^ 0x80808080u; pk[5] = p1.y ^ 0x80808080u; pk[6] = p1.z ^ 0x80808080u; pk[7] = p1.w ^ 0x80808080u;
+    }
+    for (int it = 0; it < nv; ++it) {
+        const int n = nv + it;
+        __syncwarp();
+        if (it + 1 < nv) issue(n + 1);
+        dt_wait(bar_s + (n & 1) * 8, (n >> 1) & 1);
+        const unsigned wb_s = win_s + (n & 1) * WT_BUF;
+        const float sn = __shfl_sync(0xFFFFFFFFu, my_sn, it), ca = __shfl_sync(0xFFFFFFFFu, my_ca, it);
+        const int cx = (int)(__shfl_sync(0xFFFFFFFFu, my_v, it) & 0xFFF) + B2_BORDER;
+        const int rb = (cx - 18) & 15;
         // address of window byte (18 + dy, rb + 18 + dx) with dy, dx still carrying the 1.5 * 2^23 rounding bias (0x4B400000)
         const unsigned centre = wb_s + 18 * WTB_ROWB + 18 + rb - 0x4B400000u * (unsigned)WTB_ROWB - 0x4B400000u;
         unsigned val = 0;
@@ -452,19 +489,7 @@ describe_tma_kernel(const __grid_constant__ B2Geom g, const B2Images im, const D
             }
             val |= (unsigned)(t[0] < t[1]) << j;
         }
-        desc[((size_t)b * g.kp_cap + slot) * 32 + lane] = (uint8_t)val;
-        if (lane == 0) {
-            KeyPointOut k;
-            k.x = (float)cx;
-            k.y = (float)cy;
-            if (level != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }
-            k.size = L.kp_size;
-            k.angle = angle;
-            k.response = response;
-            k.octave = level;
-            k.class_id = -1;
-            kps[(size_t)b * g.kp_cap + slot] = k;
-        }
+        desc[((size_t)b * g.kp_cap + slot0 + it) * 32 + lane] = (uint8_t)val;
     }
 }
 
