@@ -8,9 +8,8 @@
 // one WARP owns a 128-px wide strip (4 px per lane) and marches down a band of rows.  Per input row a lane
 // reads its own word and its two neighbours from a shared-memory ring the warp fills with cp.async (10 lanes
 // copy one 16-byte chunk each, BL_PF rows in flight), and computes the 4 horizontal sums with 10 IDP.4A (u8x4
-// dot products against shifted tap vectors — no byte unpacking at all).  The vertical pass keeps the last 7
-// horizontal rows in registers (7-phase unrolled rotation) and uses tap symmetry: 3 IADD + 4 IMAD per pixel,
-// which also balances the ALU and FMA pipes.  Results are packed with 3 PRMT and stored as one 32-bit word.
+// dot products against shifted tap vectors — no byte unpacking at all).  The vertical pass keeps the last rows as
+// 16-bit PAIRS in registers (6-phase unrolled rotation): 1 PRMT + 1 IMAD + 3 IDP.2A per pixel.  Results are packed with 3 PRMT and stored as one 32-bit word.
 // Image borders (reflect-101) are folded into per-lane PRMT selectors computed once per strip; interior strips
 // skip that code entirely.
 // One launch covers all levels of all images: blockIdx.x walks a flattened (level, band, strip) task list.
@@ -97,16 +96,27 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
     }
 
     // ---- row pipeline -------------------------------------------------------------------------
+    // Vertical pass: the horizontal sums are 16-bit (<= 255 * 257), so consecutive rows travel in PAIRS P_j = (H_j, H_j+1)
+    // and a pair meets two taps in one IDP.2A: out(r) = P_{r-6}.(t0,t1) + P_{r-4}.(t2,t3) + P_{r-2}.(t2,t1) + H_r * t0 + 2^15
+    // — 1 PRMT + 1 IMAD + 3 IDP.2A per pixel instead of 3 IADD + 4 IMAD.  Six pair slots, 6-phase unrolled rotation.
     const int nsteps = rows + 6;
-    int hw[7][4];
+    const unsigned T0123 = (unsigned)g.taps[0] | ((unsigned)g.taps[1] << 8) | ((unsigned)g.taps[2] << 16) | ((unsigned)g.taps[3] << 24);
+    const unsigned T21 = (unsigned)g.taps[2] | ((unsigned)g.taps[1] << 8);
+    const unsigned t0 = (unsigned)g.taps[0];
+    unsigned P[6][4];
+    unsigned Hp[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) P[i][j] = 0;
 #pragma unroll
     for (int i = 0; i < BL_PF; ++i) {
         if (i < nsteps && copier) cp_async16(cdst + i * BL_ROWB, csrc + (size_t)reflect101_once(y0 - 3 + i, h) * spitch);
         cp_async_commit();
     }
-    for (int base = 0; base < nsteps; base += 7) {
+    for (int base = 0; base < nsteps; base += 6) {
 #pragma unroll
-        for (int p = 0; p < 7; ++p) {
+        for (int p = 0; p < 6; ++p) {
             const int r = base + p;
             if (r < nsteps) {
                 // prefetch row r + BL_PF (always commit, possibly an empty group, so the wait count stays fixed)
@@ -125,27 +135,33 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
                     W2 = __byte_perm(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
                 }
                 // horizontal pass: 4 pixels, 10 dot products
-                hw[p][0] = __dp4a(W1, g.tapv[1], __dp4a(W0, g.tapv[0], 0u));
-                hw[p][1] = __dp4a(W2, g.tapv[4], __dp4a(W1, g.tapv[3], __dp4a(W0, g.tapv[2], 0u)));
-                hw[p][2] = __dp4a(W2, g.tapv[7], __dp4a(W1, g.tapv[6], __dp4a(W0, g.tapv[5], 0u)));
-                hw[p][3] = __dp4a(W2, g.tapv[9], __dp4a(W1, g.tapv[8], 0u));
+                unsigned H[4];
+                H[0] = __dp4a(W1, g.tapv[1], __dp4a(W0, g.tapv[0], 0u));
+                H[1] = __dp4a(W2, g.tapv[4], __dp4a(W1, g.tapv[3], __dp4a(W0, g.tapv[2], 0u)));
+                H[2] = __dp4a(W2, g.tapv[7], __dp4a(W1, g.tapv[6], __dp4a(W0, g.tapv[5], 0u)));
+                H[3] = __dp4a(W2, g.tapv[9], __dp4a(W1, g.tapv[8], 0u));
                 if (r >= 6) {
                     // vertical pass for output row y0 + r - 6 (window rows r-6 .. r, centre r-3)
                     unsigned o[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const int e0 = hw[p][j] + hw[(p + 1) % 7][j];
-                        const int e1 = hw[(p + 6) % 7][j] + hw[(p + 2) % 7][j];
-                        const int e2 = hw[(p + 5) % 7][j] + hw[(p + 3) % 7][j];
-                        o[j] = (unsigned)(g.taps[0] * e0 + g.taps[1] * e1 + g.taps[2] * e2 + g.taps[3] * hw[(p + 4) % 7][j] + 32768);
+                        unsigned acc = H[j] * t0 + 32768u;
+                        acc = __dp2a_lo(P[p][j], T0123, acc);                  // rows r-6, r-5
+                        acc = __dp2a_hi(P[(p + 2) % 6][j], T0123, acc);        // rows r-4, r-3
+                        acc = __dp2a_lo(P[(p + 4) % 6][j], T21, acc);          // rows r-2, r-1
                         // taps summing to more than 256 (OpenCV 3.2 rounds the sigma-2 kernel to a sum of 257) can push
                         // the rounded value past 255: saturate_cast<uchar>, as FixedPtCastEx does
-                        if (SAT) o[j] = min(o[j], 0x00FFFFFFu);
+                        o[j] = SAT ? min(acc, 0x00FFFFFFu) : acc;
                     }
                     // bits 16..23 of each accumulator are the result (never above 255 when the taps sum to <= 256)
                     const unsigned lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
                     const unsigned packed = __byte_perm(lo, hi, 0x5410);
                     if (x < w) *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * dpitch + x) = packed;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    P[(p + 5) % 6][j] = __byte_perm(Hp[j], H[j], 0x5410);      // P_{r-1} = (H_{r-1}, H_r); its slot held P_{r-7}
+                    Hp[j] = H[j];
                 }
             }
         }

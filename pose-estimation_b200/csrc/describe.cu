@@ -106,7 +106,10 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned
 }
 
 
-constexpr int DS_KPW = 16;           // keypoints per warp in large batches (amortises the weight-table copy); 4 when latency counts
+#ifndef DS_KPW_N
+#define DS_KPW_N 16
+#endif
+constexpr int DS_KPW = DS_KPW_N;          // keypoints per warp in large batches (amortises the weight-table copy); 4 when latency counts
 constexpr int WA_ROWS = 31, WA_WORDS = 9;    // un-blurred window: rows cy-15..cy+15, 36 bytes from (cx-15) & ~3
 constexpr int WB_ROWS = 37, WB_WORDS = 10;   // blurred window:    rows cy-18..cy+18, 40 bytes from (cx-18) & ~3
 
