@@ -19,6 +19,6 @@ $P > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpur
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${TAG}_launches.csv $P > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu list rc=$?"
 # 16 of our launches per step (+ the one-off bind kernel): skip bind + two steps, capture one whole step
-KR='regex:(resize|fast_score_win|fast_vote|octree|blur|describe|match_tc|stereo_filter|circular|bind)_kernel'
+KR='regex:(resize|fast_score_win|fast_vote|octree|blur|describe|describe_tma|match_tc|stereo_filter|circular|bind)_kernel'
 ncu --set full --clock-control none --import-source on -k "$KR" -s 33 -c 16 -f -o gpurun_out/${TAG}_prof $P > gpurun_out/${TAG}_ncu2.log 2>&1
 echo "ncu full rc=$?"; tail -2 gpurun_out/${TAG}_ncu2.log

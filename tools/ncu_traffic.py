@@ -9,7 +9,7 @@ import subprocess
 import sys
 
 TAGS = {"resize_kernel": "resize", "fast_score_kernel": "fast", "fast_score_win_kernel": "fast", "match_tc_kernel": "match_stereo", "fast_vote_kernel": "fast_cells", "octree_kernel": "octree",
-        "blur_kernel": "blur", "describe_kernel": "describe", "match_kernel": "match_stereo",
+        "blur_kernel": "blur", "describe_kernel": "describe", "describe_tma_kernel": "describe", "match_kernel": "match_stereo",
         "stereo_filter_kernel": "stereo_filter", "circular_kernel": "circular", "repack_kernel": "ingest"}
 
 
