@@ -135,6 +135,9 @@ void b2_launch_remap(const uint8_t* src, int step, size_t stride, const void* ma
 void b2_launch_ingest_bgra(const uint8_t* frames, int sstep, size_t sstride, int sw, int sh, const int* xofs, const short* xw,
                            const int* yofs, const short* yw, uint8_t* dst_l, uint8_t* dst_r, int dpitch, size_t dstride,
                            int half_w, int dh, int count, cudaStream_t s);
+// src0 (and src1, optional) = device-visible addresses of pinned HOST images; false when the shape is out of its range
+bool b2_launch_ingest_host(const uint8_t* src0, const uint8_t* src1, int step, uint8_t* dst, int dpitch, size_t dstride,
+                           int w, int h, cudaStream_t s);
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,
                       int h, int count, cudaStream_t s);
 void b2_launch_blur(const B2Geom& g, const B2Images& im, int nimg, int forced_band, cudaStream_t s);

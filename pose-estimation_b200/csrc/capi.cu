@@ -56,6 +56,7 @@ struct B2Tuning {
     int blur_band = -1;      // blur band variant 0 / 1 (32 / 128 rows), -1 = by batch size
     int octree_points = 0;   // 1 = quadtree by point passes only (the count-pyramid path's fallback)
     int describe_tma = 1;    // 0 = descriptor windows staged by per-lane cp.async instead of TMA boxes
+    int ingest_host = 1;     // 0 = one-pair calls copy pinned host images by DMA + repack instead of reading them in the kernel
     int pipe_chunk = 64;     // pairs per chunk of the pipelined host path, 0 = off
     int pipe_lanes = 3;      // lanes (workspaces + streams) the chunks rotate over
     int pipe_trace = 0;      // per-chunk timeline on stderr
@@ -624,8 +625,33 @@ int upload_repack(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt
     prof_mark(h, -1);
     return B2ORB_OK;
 }
+// Device-visible address of a pinned host buffer (cudaHostAlloc / cudaHostRegister / b2orb_host_alloc), else nullptr.
+const uint8_t* pinned_devptr(const void* host) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return static_cast<const uint8_t*>(a.devicePointer);
+}
+// Latency path: one image per eye, pinned host memory, no rectification -> ONE kernel reads the image(s) over the bus and
+// writes the pitched staging slots slot0 (and slot0 + 1 for src_r).  false = not applicable, use upload().
+bool upload_zero_copy(b2orb_handle* h, const uint8_t* src_l, const uint8_t* src_r, int w, int hgt, int step, int slot0) {
+    if (!h->root->tune.ingest_host || rectifying(h, w, hgt, 0)) return false;
+    // rows that already have the staging pitch go straight in by DMA: nothing to re-pitch, nothing to gain
+    if (upload_path(h, w, hgt, step, (size_t)step * hgt, false) == UP_PITCHED) return false;
+    const uint8_t* dl = pinned_devptr(src_l);
+    const uint8_t* dr = src_r ? pinned_devptr(src_r) : nullptr;
+    if (!dl || (src_r && !dr)) return false;
+    b2_pdl_on = pdl_for(h, 2);
+    prof_mark(h, B2ORB_K_INGEST);
+    const bool ok = b2_launch_ingest_host(dl, dr, step, h->d_stage + (size_t)slot0 * h->stage_img_bytes, h->stage_pitch,
+                                          h->stage_img_bytes, w, hgt, h->stream);
+    if (ok) ++h->launches;
+    prof_mark(h, -1);
+    return ok;
+}
 int upload(b2orb_handle* h, const uint8_t* src, int count, int w, int hgt, int step, size_t image_stride, int slot0,
            bool on_device = false, int eye = -1) {
+    if (!on_device && count == 1 && eye < 0 && upload_zero_copy(h, src, nullptr, w, hgt, step, slot0)) return B2ORB_OK;
     if (!on_device)
         if (int rc = upload_copy(h, src, count, w, hgt, step, image_stride, slot0, h->stream, eye)) return rc;
     return upload_repack(h, src, count, w, hgt, step, image_stride, slot0, on_device, eye);
@@ -1185,8 +1211,10 @@ int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_
     if (rc) return rc;
     if ((rc = bind_problems(h, npairs))) return rc;
     cudaEventRecord(h->ev0, h->stream);
-    if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0, false, 0))) return rc;
-    if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs, false, 1))) return rc;
+    if (!(npairs == 1 && upload_zero_copy(h, images_l, images_r, width, height, step, 0))) {
+        if ((rc = upload(h, images_l, npairs, width, height, step, image_stride, 0, false, 0))) return rc;
+        if ((rc = upload(h, images_r, npairs, width, height, step, image_stride, npairs, false, 1))) return rc;
+    }
     B2Images im = make_images(h, h->d_stage, h->d_stage + (size_t)npairs * h->stage_img_bytes, npairs,
                               h->stage_img_bytes, h->stage_pitch);
     if ((rc = launch_stereo(h, im, npairs, temporal))) return rc;
@@ -1799,6 +1827,7 @@ int b2orb_debug_set(b2orb_handle* h, const char* key, int value) {
     else if (k == "blur_band") t.blur_band = value;
     else if (k == "octree_points") t.octree_points = value ? 1 : 0;
     else if (k == "describe_tma") t.describe_tma = value ? 1 : 0;
+    else if (k == "ingest_host") t.ingest_host = value ? 1 : 0;
     else if (k == "pipe_trace") t.pipe_trace = value;
     else if (k == "pipe_chunk" || k == "pipe_lanes") {
         if (!h->lanes.empty()) return fail(h, B2ORB_ERR_INVALID, "pipeline options must be set before the first pipelined call");

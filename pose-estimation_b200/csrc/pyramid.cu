@@ -180,6 +180,46 @@ repack_kernel(const uint8_t* __restrict__ src, int step, size_t stride, uint8_t*
     *reinterpret_cast<uint32_t*>(dst + blockIdx.y * dstride + (size_t)y * dpitch + xw) = v;
 }
 
+// Latency-path ingest: the image(s) of a one-pair call are read by the kernel straight out of the caller's PINNED host
+// memory and written to the pitched staging area — one pass over the bus instead of a DMA copy into a raw buffer followed
+// by the re-pitching kernel (one KITTI pair: 21 us of copies + 16 us of repack launches -> one launch bound by the link).
+// A CTA owns IH_ROWS rows: their source bytes are one contiguous range (rows are `step` apart), fetched with aligned
+// 16-byte non-coherent loads into shared memory (every source byte crosses the bus once; a 16-byte chunk never crosses a
+// page, so the aligned over-read at both ends stays inside mapped memory), then re-pitched from shared memory.
+constexpr int IH_ROWS = 8;
+constexpr int IH_MAX_STEP = 4096;
+__global__ void __launch_bounds__(256)
+ingest_host_kernel(const uint8_t* __restrict__ src0, const uint8_t* __restrict__ src1, int step, uint8_t* __restrict__ dst,
+                   int dpitch, size_t dstride, int w, int h) {
+    b2_pdl_wait();
+    __shared__ __align__(16) uint8_t s_rows[IH_ROWS * IH_MAX_STEP + 32];
+    const uint8_t* src = blockIdx.y ? src1 : src0;
+    const int y0 = blockIdx.x * IH_ROWS, ny = min(IH_ROWS, h - y0);
+    const uintptr_t first = (uintptr_t)src + (size_t)y0 * step;
+    const uintptr_t a0 = first & ~(uintptr_t)15;
+    const int skew = (int)(first - a0);
+    const int nbytes = (ny - 1) * step + w;
+    const int nchunk = (skew + nbytes + 15) >> 4;
+    for (int c = threadIdx.x; c < nchunk; c += 256) {
+        uint4 v;
+        asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                     : "l"(a0 + (size_t)c * 16));
+        reinterpret_cast<uint4*>(s_rows)[c] = v;
+    }
+    __syncthreads();
+    const int words = dpitch >> 2;
+    uint8_t* d = dst + blockIdx.y * dstride + (size_t)y0 * dpitch;
+    for (int i = threadIdx.x; i < words * ny; i += 256) {
+        const int r = i / words, xw = (i - r * words) * 4;
+        const uint8_t* s = s_rows + skew + r * step + xw;
+        uint32_t v = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (xw + k < w) v |= (uint32_t)s[k] << (8 * k);
+        *reinterpret_cast<uint32_t*>(d + (size_t)r * dpitch + xw) = v;
+    }
+}
+
 // Rectification in front of the pyramid — cv::remap(gray, img, rmap[eye][0], rmap[eye][1], INTER_LINEAR),
 // src/feature-tracker.cpp:75-76 (maps: include/cfsd/camera-model.hpp:76-77, CV_16SC2 + CV_16UC1).  map1 = (sx, sy),
 // map2 = fx | fy << 5 in 1/32 px; OpenCV's fixed-point weights are exact multiples of 32 that sum to 32768, so
@@ -300,6 +340,14 @@ void b2_launch_resize(const B2Geom& g, const B2Images& im, int level, const int*
     const int tasks = strips * ((L.h + band - 1) / band);
     dim3 grid((tasks + RS_WARPS - 1) / RS_WARPS, nimg);
     b2_launch_pdl(resize_kernel, dim3(grid), dim3(RS_WARPS * 32), 0, s, g, im, level, band, xofs, xw, yofs, yw);
+}
+
+bool b2_launch_ingest_host(const uint8_t* src0, const uint8_t* src1, int step, uint8_t* dst, int dpitch, size_t dstride,
+                           int w, int h, cudaStream_t s) {
+    if (step > IH_MAX_STEP || w < 1 || h < 1) return false;
+    dim3 grid((h + IH_ROWS - 1) / IH_ROWS, src1 ? 2 : 1);
+    b2_launch_pdl(ingest_host_kernel, dim3(grid), dim3(256), 0, s, src0, src1, step, dst, dpitch, dstride, w, h);
+    return true;
 }
 
 void b2_launch_repack(const uint8_t* src, int step, size_t stride, uint8_t* dst, int dpitch, size_t dstride, int w,

@@ -398,3 +398,50 @@ def test_error_codes(fe):
         hd.extract_batch(np.zeros((3, 100, 100), np.uint8))  # more than max_images
     assert e.value.code == fe.ERR_CAPACITY
     hd.close()
+
+
+@pytest.mark.parametrize("shape", ["kitti", (401, 300), (640, 480)], ids=["kitti_1241", "odd_401", "even_640"])
+def test_pinned_host_images_read_by_the_ingest_kernel(shape, fe, synth):
+    """One-pair calls whose images sit in PINNED host memory are read by a kernel straight over the bus (no DMA copy + repack);
+    the result must be the one of the DMA path (pageable images, or b2orb_debug_set(h, "ingest_host", 0)): odd and even
+    widths, image bases that are not 16-byte aligned (image 1 of a pinned stack of odd-sized images), rows with a pitch
+    larger than the width, and b2orb_extract on a single pinned image."""
+    import ctypes as C
+    if isinstance(shape, str):
+        w, h, nf, ini, mn = synth.SHAPES[shape]
+    else:
+        (w, h), nf, ini, mn = shape, 600, 20, 7
+    ls, rs = synth.sequence(shape, 2, seed=33)
+    hd = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2)
+    ref = fe.Handle(nf, 1.2, 8, ini, mn, w, h, max_images=2).debug_set("ingest_host", 0)
+    pl = fe.pinned_empty(ls.shape); pl[...] = ls
+    pr = fe.pinned_empty(rs.shape); pr[...] = rs
+    keys = ("n_l", "n_r", "n_match", "kp_l", "kp_r", "desc_l", "desc_r", "match_l", "match_r")
+    for i in range(2):                                    # i = 1: base address = i * w * h, odd for odd shapes
+        want = ref.stereo_frontend(ls[i], rs[i])
+        l0 = hd.launch_count
+        got = hd.stereo_frontend(pl[i], pr[i])
+        if i:                                             # (call 0 also launches the one-off problem-table kernel)
+            # one ingest launch instead of two re-pitching launches (rows that already have the staging pitch: plain DMA)
+            assert hd.launch_count - l0 == ref_launches(ref, ls[i], rs[i]) - (1 if w % 32 else 0)
+        for k in keys:
+            assert np.array_equal(got[k], want[k]), (i, k)
+    # pitched pinned rows (step > width), through the C ABI directly
+    step = w + 37
+    pp = fe.pinned_empty((2, h, step)); pp[...] = 0xAB
+    pp[0, :, :w] = ls[0]; pp[1, :, :w] = rs[0]
+    out = hd.alloc_stereo_out(1)
+    hd.check(hd.L.b2orb_stereo_frontend(hd.h, pp[0].ctypes.data, pp[1].ctypes.data, 1, w, h, step, step * h, 0, C.byref(out[1])))
+    want = ref.stereo_frontend(ls[0], rs[0])
+    for k in keys:
+        assert np.array_equal(out[0][k], want[k]), ("pitched", k)
+    # single image
+    k1, d1 = hd.extract(pl[1]); k0, d0 = ref.extract(ls[1])
+    assert k1.tobytes() == k0.tobytes() and np.array_equal(d1, d0)
+    hd.close(); ref.close()
+
+
+def ref_launches(hd, l, r):
+    l0 = hd.launch_count
+    hd.stereo_frontend(l, r)
+    return hd.launch_count - l0
