@@ -172,9 +172,14 @@ void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_
                              int* match_r, int* n_match, uint8_t* cur_l, uint8_t* cur_r, double* pix_l, double* pix_r,
                              int npairs, cudaStream_t s);   // left image slot = p, right image slot = npairs + p;
                                                             // pix_* (optional) = kept pixels as cv::Point2d
+// circular_kernel's optional tail for one-pair calls with temporal = 1: copy the pair's kept rows into the history slot
+struct B2HistHandover {
+    uint8_t* dst_l; uint8_t* dst_r; const uint8_t* src_l; const uint8_t* src_r; int* n_dst;
+};
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
                         const int* n_hist, int hist_stride, int cap, float ratio, float min_match, int* circ_cur,
-                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s);
+                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s,
+                        const B2HistHandover* handover = nullptr);
 // ---- f3: device-resident feature pool (pool.cu) ---------------------------------------------------------------
 struct B2Pool;
 B2Pool* b2_pool_create();

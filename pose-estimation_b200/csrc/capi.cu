@@ -707,15 +707,19 @@ int launch_stereo(b2orb_handle* h, const B2Images& im, int np, int temporal) {
         b2_launch_match(h->d_probs + np, 2 * np, g.kp_cap, s);
         ++h->launches;
         prof_mark(h, B2ORB_K_CIRCULAR);
+        // the last pair of this call becomes the history of the next call (slot 0): for one pair the circular kernel does it
+        // in its tail (its only CTA has read the old count by then), else three device-to-device copies
+        const B2HistHandover ho = {h->d_cur_l, h->d_cur_r, h->d_cur_l + row, h->d_cur_r + row, h->d_nmatch};
         b2_launch_circular(h->d_tti_l, h->d_tdi_l, h->d_tti_r, h->d_tdi_r, h->d_nmatch + 1, h->d_nmatch, 1, g.kp_cap,
                            h->cfg.match_ratio, h->cfg.min_match_dist, h->d_circ_cur, h->d_circ_hist, h->d_ncirc,
-                           h->d_nleft, h->d_nright, h->d_mask, np, s);
+                           h->d_nleft, h->d_nright, h->d_mask, np, s, np == 1 ? &ho : nullptr);
         ++h->launches;
         prof_mark(h, -1);
-        // the last pair of this call becomes the history of the next call (slot 0)
-        B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, h->d_cur_l + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
-        B2_CUDA(h, cudaMemcpyAsync(h->d_cur_r, h->d_cur_r + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
-        B2_CUDA(h, cudaMemcpyAsync(h->d_nmatch, h->d_nmatch + np, sizeof(int), cudaMemcpyDeviceToDevice, s));
+        if (np > 1) {
+            B2_CUDA(h, cudaMemcpyAsync(h->d_cur_l, h->d_cur_l + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
+            B2_CUDA(h, cudaMemcpyAsync(h->d_cur_r, h->d_cur_r + (size_t)np * row, row, cudaMemcpyDeviceToDevice, s));
+            B2_CUDA(h, cudaMemcpyAsync(h->d_nmatch, h->d_nmatch + np, sizeof(int), cudaMemcpyDeviceToDevice, s));
+        }
         B2_CUDA(h, cudaEventRecord(h->ev_hist, s));
         h->root->hist_owner = h;
     }
@@ -748,7 +752,24 @@ export_kernel(const __grid_constant__ B2ExportPlan plan) {
     const int words = (int)(bytes >> 2);
     const unsigned* s4 = reinterpret_cast<const unsigned*>(src);
     unsigned* d4 = reinterpret_cast<unsigned*>(dst);
-    for (int i = blockIdx.z * 256 + threadIdx.x; i < words; i += 256 * gridDim.z) d4[i] = s4[i];
+    int w0 = 0;
+    if (!((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15)) {
+        // the large arrays (keypoints, descriptors: 50-130 KB) as 16-byte vectors, four loads in flight per thread: the copy
+        // is a chain of L2 round trips per thread, not a bandwidth problem
+        const int quads = words >> 2;
+        const uint4* s16 = reinterpret_cast<const uint4*>(src);
+        uint4* d16 = reinterpret_cast<uint4*>(dst);
+        const int stride = 256 * gridDim.z;
+        for (int i = blockIdx.z * 256 + threadIdx.x; i < quads; i += 4 * stride) {
+            uint4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (i + k * stride < quads) v[k] = s16[i + k * stride];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (i + k * stride < quads) d16[i + k * stride] = v[k];
+        }
+        w0 = quads << 2;
+    }
+    for (int i = w0 + blockIdx.z * 256 + threadIdx.x; i < words; i += 256 * gridDim.z) d4[i] = s4[i];
     if (blockIdx.z == 0 && threadIdx.x < (int)(bytes & 3)) dst[(words << 2) + threadIdx.x] = src[(words << 2) + threadIdx.x];
 }
 

@@ -51,6 +51,7 @@ struct KeyPointIn {
 };
 
 // One CTA per stereo pair.  Image slots: left = p, right = npairs + p.
+constexpr int SF_B = 4;   // rows per thread whose loads are in flight together
 __global__ void __launch_bounds__(SF_THREADS)
 stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restrict__ desc, const int* __restrict__ n_kp,
                      const int* __restrict__ train_idx, const int* __restrict__ dist, int cap, float ratio,
@@ -70,17 +71,40 @@ stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restri
         if (threadIdx.x == 0) n_match[p] = 0;
         return;
     }
+    // A latency chain, not a throughput problem (one CTA, ~2000 rows): every thread first issues ALL its independent loads
+    // (distance, train index, left row coordinate of up to SF_B rows per batch), then the dependent right-row loads, and
+    // only then meets the block-wide min — three memory round trips in total instead of one per row and step.
     int mn = 0x7fffffff;
-    for (int i = threadIdx.x; i < nl; i += SF_THREADS) mn = min(mn, di[i]);
+    unsigned long long dyok = 0;                     // bit k: row k * SF_THREADS + tid passes the row test (:208-209)
+    const bool bits_ok = nl <= 64 * SF_THREADS;      // (larger sets: the test is redone in pass 2)
+    for (int k0 = 0; k0 * SF_THREADS < nl; k0 += SF_B) {
+        int d[SF_B], t[SF_B];
+        float yl[SF_B];
+#pragma unroll
+        for (int k = 0; k < SF_B; ++k) {
+            const int i = (k0 + k) * SF_THREADS + threadIdx.x;
+            const bool in = i < nl;
+            d[k] = in ? di[i] : 0x7fffffff;
+            t[k] = in ? ti[i] : 0;
+            yl[k] = in ? kl[i].y : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < SF_B; ++k) {
+            const int i = (k0 + k) * SF_THREADS + threadIdx.x;
+            mn = min(mn, d[k]);
+            if (i < nl && bits_ok && fabsf(__fsub_rn(yl[k], kr[t[k]].y)) < max_dy) dyok |= 1ull << (k0 + k);
+        }
+    }
     mn = block_min(mn, s_red);
     const float thr = fmaxf(__fmul_rn(ratio, (float)mn), min_match);
     int base = 0;
-    for (int i0 = 0; i0 < nl; i0 += SF_THREADS) {
+    for (int i0 = 0, k = 0; i0 < nl; i0 += SF_THREADS, ++k) {
         const int i = i0 + threadIdx.x;
         int keep = 0, t = 0;
         if (i < nl) {
             t = ti[i];
-            keep = ((float)di[i] < thr) && (fabsf(__fsub_rn(kl[i].y, kr[t].y)) < max_dy);
+            const bool row_ok = bits_ok ? ((dyok >> k) & 1ull) != 0 : fabsf(__fsub_rn(kl[i].y, kr[t].y)) < max_dy;
+            keep = ((float)di[i] < thr) && row_ok;
         }
         int tot;
         const int off = block_scan_flag(keep, s_red, &tot);
@@ -92,8 +116,9 @@ stereo_filter_kernel(const KeyPointIn* __restrict__ kps, const uint8_t* __restri
             const uint4* sr = reinterpret_cast<const uint4*>(desc + ((size_t)(np + p) * cap + t) * 32);
             uint4* dl = reinterpret_cast<uint4*>(cur_l + ((size_t)p * cap + m) * 32);
             uint4* dr = reinterpret_cast<uint4*>(cur_r + ((size_t)p * cap + m) * 32);
-            dl[0] = sl[0]; dl[1] = sl[1];
-            dr[0] = sr[0]; dr[1] = sr[1];
+            const uint4 l0 = sl[0], l1 = sl[1], r0 = sr[0], r1 = sr[1];
+            dl[0] = l0; dl[1] = l1;
+            dr[0] = r0; dr[1] = r1;
             if (pix_l) {   // _curPixelsL/R.push_back(keypoint.pt): Point2f widened to Point2d (:214-215)
                 pix_l[(size_t)p * cap + m] = make_double2((double)kl[i].x, (double)kl[i].y);
                 pix_r[(size_t)p * cap + m] = make_double2((double)kr[t].x, (double)kr[t].y);
@@ -110,7 +135,7 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
                 const int* __restrict__ di_r, const int* __restrict__ n_cur, const int* __restrict__ n_hist,
                 int hist_stride, int cap, float ratio, float min_match, int* __restrict__ circ_cur,
                 int* __restrict__ circ_hist, int* __restrict__ n_circ, int* __restrict__ n_left, int* __restrict__ n_right,
-                uint8_t* __restrict__ mask) {
+                uint8_t* __restrict__ mask, B2HistHandover ho) {
     b2_pdl_wait();
     __shared__ int s_red[SF_THREADS / 32];
     const int p = blockIdx.x;
@@ -118,31 +143,41 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
     if (nc == 0 || nh == 0) {   // :237-240 early-out on an empty pool; empty cur set -> nothing to match
         if (threadIdx.x == 0) { n_circ[p] = 0; if (n_left) n_left[p] = 0; if (n_right) n_right[p] = 0; }
         if (mask) for (int i = threadIdx.x; i < nc; i += SF_THREADS) mask[(size_t)p * cap + i] = 1;   // _curFeatureMask all true
-        return;
+    } else {
+        const int* tl = ti_l + (size_t)p * cap; const int* dl = di_l + (size_t)p * cap;
+        const int* tr = ti_r + (size_t)p * cap; const int* dr = di_r + (size_t)p * cap;
+        int mnl = 0x7fffffff, mnr = 0x7fffffff;
+        for (int i = threadIdx.x; i < nc; i += SF_THREADS) { mnl = min(mnl, dl[i]); mnr = min(mnr, dr[i]); }
+        mnl = block_min(mnl, s_red);
+        mnr = block_min(mnr, s_red);
+        const float thl = fmaxf(__fmul_rn(ratio, (float)mnl), min_match);
+        const float thr = fmaxf(__fmul_rn(ratio, (float)mnr), min_match);
+        int base = 0, cl = 0, cr = 0;
+        for (int i0 = 0; i0 < nc; i0 += SF_THREADS) {
+            const int i = i0 + threadIdx.x;
+            int okl = 0, okr = 0, t = -1;
+            if (i < nc) { okl = (float)dl[i] < thl; okr = (float)dr[i] < thr; t = tl[i]; }
+            const int keep = okl && okr && t == (i < nc ? tr[i] : -2);
+            int tot;
+            const int off = block_scan_flag(keep, s_red, &tot);
+            if (keep) { circ_cur[(size_t)p * cap + base + off] = i; circ_hist[(size_t)p * cap + base + off] = t; }
+            if (mask && i < nc) mask[(size_t)p * cap + i] = keep ? 0 : 1;   // _curFeatureMask[m.queryIdx] = false (:319)
+            base += tot;
+            cl += __syncthreads_count(okl);                                  // sizes of the two filtered lists (:259, :304)
+            cr += __syncthreads_count(okr);
+        }
+        if (threadIdx.x == 0) { n_circ[p] = base; if (n_left) n_left[p] = cl; if (n_right) n_right[p] = cr; }
     }
-    const int* tl = ti_l + (size_t)p * cap; const int* dl = di_l + (size_t)p * cap;
-    const int* tr = ti_r + (size_t)p * cap; const int* dr = di_r + (size_t)p * cap;
-    int mnl = 0x7fffffff, mnr = 0x7fffffff;
-    for (int i = threadIdx.x; i < nc; i += SF_THREADS) { mnl = min(mnl, dl[i]); mnr = min(mnr, dr[i]); }
-    mnl = block_min(mnl, s_red);
-    mnr = block_min(mnr, s_red);
-    const float thl = fmaxf(__fmul_rn(ratio, (float)mnl), min_match);
-    const float thr = fmaxf(__fmul_rn(ratio, (float)mnr), min_match);
-    int base = 0, cl = 0, cr = 0;
-    for (int i0 = 0; i0 < nc; i0 += SF_THREADS) {
-        const int i = i0 + threadIdx.x;
-        int okl = 0, okr = 0;
-        if (i < nc) { okl = (float)dl[i] < thl; okr = (float)dr[i] < thr; }
-        const int keep = okl && okr && tl[i] == tr[i];
-        int tot, t2;
-        const int off = block_scan_flag(keep, s_red, &tot);
-        if (keep) { circ_cur[(size_t)p * cap + base + off] = i; circ_hist[(size_t)p * cap + base + off] = tl[i]; }
-        if (mask && i < nc) mask[(size_t)p * cap + i] = keep ? 0 : 1;   // _curFeatureMask[m.queryIdx] = false (:319)
-        base += tot;
-        block_scan_flag(okl, s_red, &t2); cl += t2;
-        block_scan_flag(okr, s_red, &t2); cr += t2;
+    // One-pair calls of the consecutive-frame mode: this pair's kept descriptor rows become the history of the next call
+    // (three device-to-device copies on the stream otherwise).  Nothing reads the history slot after the temporal matcher,
+    // which has completed before this kernel started; the count was read above by every thread.
+    if (ho.dst_l && p == gridDim.x - 1) {
+        __syncthreads();
+        const uint4* sl = reinterpret_cast<const uint4*>(ho.src_l); const uint4* sr = reinterpret_cast<const uint4*>(ho.src_r);
+        uint4* dl4 = reinterpret_cast<uint4*>(ho.dst_l); uint4* dr4 = reinterpret_cast<uint4*>(ho.dst_r);
+        for (int i = threadIdx.x; i < 2 * nc; i += SF_THREADS) { dl4[i] = sl[i]; dr4[i] = sr[i]; }
+        if (threadIdx.x == 0) *ho.n_dst = nc;
     }
-    if (threadIdx.x == 0) { n_circ[p] = base; if (n_left) n_left[p] = cl; if (n_right) n_right[p] = cr; }
 }
 
 }  // namespace
@@ -382,7 +417,10 @@ void b2_launch_stereo_filter(const void* kps, const uint8_t* desc, const int* n_
 
 void b2_launch_circular(const int* ti_l, const int* di_l, const int* ti_r, const int* di_r, const int* n_cur,
                         const int* n_hist, int hist_stride, int cap, float ratio, float min_match, int* circ_cur,
-                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s) {
+                        int* circ_hist, int* n_circ, int* n_left, int* n_right, uint8_t* mask, int nprob, cudaStream_t s,
+                        const B2HistHandover* handover) {
+    B2HistHandover ho = {};
+    if (handover) ho = *handover;
     b2_launch_pdl(circular_kernel, dim3(nprob), dim3(SF_THREADS), 0, s, ti_l, di_l, ti_r, di_r, n_cur, n_hist, hist_stride, cap, ratio,
-                  min_match, circ_cur, circ_hist, n_circ, n_left, n_right, mask);
+                  min_match, circ_cur, circ_hist, n_circ, n_left, n_right, mask, ho);
 }

@@ -2,6 +2,7 @@
 import ctypes as C, importlib, sys, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import os as _os
 fe = importlib.import_module("pose-estimation_b200.frontend"); synth = importlib.import_module("pose-estimation_b200.synth")
 shape = sys.argv[1] if len(sys.argv) > 1 else "kitti"
 w, h, nf, ini, mn = synth.SHAPES[shape]
