@@ -175,7 +175,8 @@ typedef struct b2orb_stereo_out {
  * Calls of up to 4 pairs whose output arrays are all pinned host memory (b2orb_host_alloc, cudaHostAlloc,
  * cudaHostRegister) return their results through one kernel that writes entries [0, n) of every array directly
  * into the caller's buffers; otherwise whole arrays are copied back.  Either way only entries [0, n) are defined.
- * b2orb_debug_set(h, "export_max", 0) forces the copy path. */
+ * b2orb_debug_set(h, "export_max", 0) forces the copy path.  One-pair calls whose INPUT images are pinned host memory with
+ * rows that need re-pitching (width not a multiple of 32) are read by the ingest kernel directly over the bus. */
 int b2orb_stereo_frontend(b2orb_handle* h, const uint8_t* images_l, const uint8_t* images_r, int npairs, int width,
                           int height, int step, size_t image_stride, int temporal, const b2orb_stereo_out* out);
 
@@ -274,8 +275,10 @@ int b2orb_debug_get_candidates(b2orb_handle* h, int slot, int level, uint32_t* d
  * read from the environment; two handles on two threads may differ).  Keys: "pdl" (-1 auto / 0 / 1 programmatic
  * dependent launch), "fork_max" (blur on a side stream for calls of at most this many images), "export_max" (direct
  * export into pinned outputs for calls of at most this many pairs), "fast_band" (-1 auto, 0 / 1 / 2 / 3 = 16 / 32 / 64 / 128-row
- * FAST bands), "blur_band" (-1 auto, 0 / 1 = 32 / 128-row blur bands), "octree_points" (1 = quadtree by point passes only), "pipe_chunk" / "pipe_lanes" (pipelined host path,
- * before its first use), "pipe_trace". */
+ * FAST bands), "blur_band" (-1 auto, 0 / 1 = 32 / 128-row blur bands), "octree_points" (1 = quadtree by point passes only),
+ * "describe_tma" (1 default: descriptor windows fetched as TMA boxes; 0 = per-lane cp.async), "ingest_host" (1 default:
+ * one-pair calls read pinned host images in the ingest kernel; 0 = DMA copy + re-pitching kernel), "pipe_chunk" /
+ * "pipe_lanes" (pipelined host path, before its first use), "pipe_trace". */
 int b2orb_debug_set(b2orb_handle* h, const char* key, int value);
 
 /* Quadtree levels (since the library was loaded, on the handle's device) whose keypoints were so clustered that the
