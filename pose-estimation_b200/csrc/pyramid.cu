@@ -35,7 +35,7 @@ __device__ __forceinline__ void rs_wait() { asm volatile("cp.async.wait_group %0
 // One task = (band, strip) of `level` of image b, run by the calling warp with its private ring.
 __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im, int b, int level, int band_rows, int task,
                                             const int* __restrict__ xofs, const short* __restrict__ xw,
-                                            const int* __restrict__ yofs, const short* __restrict__ yw, uint8_t* ring) {
+                                            const int* __restrict__ yofs, const short* __restrict__ yw, uint8_t* ring, uint4* vtab) {
     const B2Level& L = g.lv[level];
     const int lane = threadIdx.x & 31;
     const int strips = (L.w + 127) >> 7;
@@ -96,26 +96,33 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
         gsrc += sp;
         ++issued;
     }
-    unsigned H0[4] = {0, 0, 0, 0}, H1[4] = {0, 0, 0, 0};
+    unsigned HA[4] = {0, 0, 0, 0}, HB[4] = {0, 0, 0, 0};
     uint8_t* dptr = dst + (size_t)dy0 * dpitch + dx0;                     // next output row of this lane
     int store = dx0 < L.w;
     asm volatile("" : "+r"(store));
-    // vertical table of the band in registers: lane i holds (source row, weights) of output row dy0 + 32 * blk + i and
-    // hands them out by shuffle — no dependent global loads or 64-bit pointer arithmetic in the emit loop
-    int ty = 0;
-    unsigned tw = 0;
+    // vertical table of the band in shared memory: entry e = (source row, b0 << 16, b1 << 16) of output row dy0 + e, one
+    // LDS.128 per output row (lane e fills entry e; bands have at most 32 rows)
+    const unsigned vt_s = (unsigned)__cvta_generic_to_shared(vtab);
     {
         const int dy = min(dy0 + lane, dy1 - 1);
-        ty = yofs[dy];
-        tw = *reinterpret_cast<const unsigned*>(yw + 2 * dy);
+        const unsigned w2 = *reinterpret_cast<const unsigned*>(yw + 2 * dy);
+        vtab[lane] = make_uint4((unsigned)yofs[dy], w2 << 16, w2 & 0xFFFF0000u, 0u);
     }
+    __syncwarp();
     int left = dy1 - dy0;                                                 // output rows still to emit
-    int e = 0;                                                            // index of the next output row in the band
-    int sy = __shfl_sync(0xFFFFFFFFu, ty, 0);                             // source row of the next output row
-    unsigned wcur = __shfl_sync(0xFFFFFFFFu, tw, 0);
-    unsigned b0 = wcur << 16, b1 = wcur & 0xFFFF0000u;
+    unsigned vt_next = vt_s;                                              // address of the next output row's entry
+    int sy; unsigned b0, b1;
+    const auto next_row = [&]() {
+        unsigned x, y, z, w_;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w_) : "r"(vt_next));
+        sy = (int)x; b0 = y; b1 = z;
+        vt_next += 16;
+    };
+    next_row();
     unsigned slot = 0;                                                    // ring byte offset of source row s
-    for (int s = s_first; s <= s_last; ++s) {
+    // one source row: stage the next one, interpolate this one horizontally into Hc, emit the output rows whose source
+    // pair is (s - 1, s) from (Hp, Hc).  Called with the two register sets swapped on alternate rows: no copies.
+    const auto step = [&](int s, unsigned (&Hp)[4], unsigned (&Hc)[4]) {
         if (issued < nrows && copier) rs_cp_async16(cdst_r + ((slot + RS_PF * RS_ROWB) & (RS_SLOTS * RS_ROWB - 1)), gsrc);
         rs_commit();
         gsrc += sp;
@@ -125,16 +132,12 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
         const unsigned wa0 = rs_lds(o01 + slot), wa1 = rs_lds(o01 + slot + 4);
         const unsigned wb0 = rs_lds(o23 + slot), wb1 = rs_lds(o23 + slot + 4);
         slot = (slot + RS_ROWB) & (RS_SLOTS * RS_ROWB - 1);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) H0[j] = H1[j];
-        H1[0] = __dp2a_lo(A[0], __byte_perm(wa0, wa1, sel[0]), 0u) >> 4;
-        H1[1] = __dp2a_lo(A[1], __byte_perm(wa0, wa1, sel[1]), 0u) >> 4;
-        H1[2] = __dp2a_lo(A[2], __byte_perm(wb0, wb1, sel[2]), 0u) >> 4;
-        H1[3] = __dp2a_lo(A[3], __byte_perm(wb0, wb1, sel[3]), 0u) >> 4;
-        // emit the output rows whose source pair is (s-1, s); on the last source row of the level also those clamped
-        // to (s, s) (their second weight is 0): rows come in ascending source order, so once sy == s the pair (s-1, s)
-        // is no longer needed and H0 simply becomes H1
-        const auto emit = [&]() {
+        Hc[0] = __dp2a_lo(A[0], __byte_perm(wa0, wa1, sel[0]), 0u) >> 4;
+        Hc[1] = __dp2a_lo(A[1], __byte_perm(wa0, wa1, sel[1]), 0u) >> 4;
+        Hc[2] = __dp2a_lo(A[2], __byte_perm(wb0, wb1, sel[2]), 0u) >> 4;
+        Hc[3] = __dp2a_lo(A[3], __byte_perm(wb0, wb1, sel[3]), 0u) >> 4;
+        // rows come in ascending source order, so once sy == s the pair (s-1, s) is no longer needed
+        const auto emit = [&](const unsigned (&H0)[4], const unsigned (&H1)[4]) {
             unsigned u[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) u[j] = (__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) * 64u;   // byte 1 = (..) >> 2
@@ -142,24 +145,18 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
             if (store) *reinterpret_cast<unsigned*>(dptr) = __byte_perm(lo, hi, 0x5410);
             dptr += dpitch;
             --left;
-            ++e;
-            if ((e & 31) == 0 && left > 0) {                              // bands longer than a warp: next block of rows
-                const int dy = min(dy0 + e + lane, dy1 - 1);
-                ty = yofs[dy];
-                tw = *reinterpret_cast<const unsigned*>(yw + 2 * dy);
-            }
-            sy = __shfl_sync(0xFFFFFFFFu, ty, e & 31);
-            wcur = __shfl_sync(0xFFFFFFFFu, tw, e & 31);
-            b0 = wcur << 16;
-            b1 = wcur & 0xFFFF0000u;
+            next_row();                                                   // (one entry past the band is read, never used)
         };
-        while (left > 0 && sy == s - 1) emit();
-        if (s == sh1) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) H0[j] = H1[j];
-            while (left > 0 && sy == s) emit();
-        }
+        while (left > 0 && sy == s - 1) emit(Hp, Hc);
+        if (s == sh1)                                                     // last source row of the level: rows clamped to
+            while (left > 0 && sy == s) emit(Hc, Hc);                     // (s, s), their second weight is 0
+    };
+    int s = s_first;
+    for (; s + 1 <= s_last; s += 2) {
+        step(s, HA, HB);
+        step(s + 1, HB, HA);
     }
+    if (s <= s_last) step(s, HA, HB);
 }
 
 // Level-0 ingest: images with arbitrary row step (e.g. tight 1241-byte rows) -> staging area whose rows start on
@@ -262,8 +259,9 @@ resize_kernel(const __grid_constant__ B2Geom g, const B2Images im, int level, in
               const short* __restrict__ yw) {
     b2_pdl_wait();
     __shared__ __align__(16) uint8_t s_ring[RS_WARPS][RS_SLOTS * RS_ROWB];
+    __shared__ uint4 s_vtab[RS_WARPS][33];                                  // (one entry past a 32-row band is read)
     const int wid = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);   // broadcast: warp-uniform for the compiler
-    resize_task(g, im, blockIdx.y, level, band_rows, blockIdx.x * RS_WARPS + wid, xofs, xw, yofs, yw, s_ring[wid]);
+    resize_task(g, im, blockIdx.y, level, band_rows, blockIdx.x * RS_WARPS + wid, xofs, xw, yofs, yw, s_ring[wid], s_vtab[wid]);
 }
 
 // cv::resize(INTER_LINEAR) to 2*half_w x dh -> cvtColor(BGR2GRAY) -> left / right halves, fused: one thread per output
