@@ -35,6 +35,12 @@ __device__ __forceinline__ void cp_async16(unsigned smem_addr, const void* gmem)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// PRMT with a run-time selector (__byte_perm first masks the selector with 0x7777: one more instruction per use)
+__device__ __forceinline__ unsigned bl_prmt(unsigned a, unsigned b, unsigned sel) {
+    unsigned d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
 
 __device__ __forceinline__ int reflect101_once(int i, int n) {
     // BORDER_REFLECT_101: -i -> i, (n-1)+i -> (n-1)-i.  One bounce is exact for n >= 4 (halo is 3); smaller
@@ -130,9 +136,9 @@ __device__ __forceinline__ void blur_task(const uint8_t* __restrict__ src, int s
                 const unsigned R0 = rw[-1], R1 = rw[0], R2 = rw[1];
                 unsigned W0 = R0, W1 = R1, W2 = R2;
                 if (EDGE) {
-                    W0 = __byte_perm(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
-                    W1 = __byte_perm(R0, R1, s1);
-                    W2 = __byte_perm(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
+                    W0 = bl_prmt(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
+                    W1 = bl_prmt(R0, R1, s1);
+                    W2 = bl_prmt(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
                 }
                 // horizontal pass: 4 pixels, 10 dot products
                 unsigned H[4];
@@ -279,9 +285,9 @@ __device__ __forceinline__ void blur_task_tma(const CUtensorMap* map, int z, uin
                 const unsigned R0 = rw[-1], R1 = rw[0], R2 = rw[1];
                 unsigned W0 = R0, W1 = R1, W2 = R2;
                 if (EDGE) {
-                    W0 = __byte_perm(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
-                    W1 = __byte_perm(R0, R1, s1);
-                    W2 = __byte_perm(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
+                    W0 = bl_prmt(w0_hi ? R1 : R0, w0_hi ? R2 : R1, s0);
+                    W1 = bl_prmt(R0, R1, s1);
+                    W2 = bl_prmt(w2_lo ? R0 : R1, w2_lo ? R1 : R2, s2);
                 }
                 hw[p][0] = __dp4a(W1, g.tapv[1], __dp4a(W0, g.tapv[0], 0u));
                 hw[p][1] = __dp4a(W2, g.tapv[4], __dp4a(W1, g.tapv[3], __dp4a(W0, g.tapv[2], 0u)));

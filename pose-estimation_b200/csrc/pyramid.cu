@@ -24,6 +24,12 @@ __device__ __forceinline__ unsigned rs_lds(unsigned smem_addr) {
 __device__ __forceinline__ void rs_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void rs_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// PRMT with a run-time selector (__byte_perm first masks the selector with 0x7777: one more instruction per use)
+__device__ __forceinline__ unsigned rs_prmt(unsigned a, unsigned b, unsigned sel) {
+    unsigned d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
 
 // One WARP owns a 128-px wide strip of the destination level (4 px per lane) and walks down RS_BAND output rows.
 // The source rows it needs are streamed through a cp.async shared-memory ring (deep, in-order prefetch).
@@ -132,10 +138,10 @@ __device__ __forceinline__ void resize_task(const B2Geom& g, const B2Images& im,
         const unsigned wa0 = rs_lds(o01 + slot), wa1 = rs_lds(o01 + slot + 4);
         const unsigned wb0 = rs_lds(o23 + slot), wb1 = rs_lds(o23 + slot + 4);
         slot = (slot + RS_ROWB) & (RS_SLOTS * RS_ROWB - 1);
-        Hc[0] = __dp2a_lo(A[0], __byte_perm(wa0, wa1, sel[0]), 0u) >> 4;
-        Hc[1] = __dp2a_lo(A[1], __byte_perm(wa0, wa1, sel[1]), 0u) >> 4;
-        Hc[2] = __dp2a_lo(A[2], __byte_perm(wb0, wb1, sel[2]), 0u) >> 4;
-        Hc[3] = __dp2a_lo(A[3], __byte_perm(wb0, wb1, sel[3]), 0u) >> 4;
+        Hc[0] = __dp2a_lo(A[0], rs_prmt(wa0, wa1, sel[0]), 0u) >> 4;
+        Hc[1] = __dp2a_lo(A[1], rs_prmt(wa0, wa1, sel[1]), 0u) >> 4;
+        Hc[2] = __dp2a_lo(A[2], rs_prmt(wb0, wb1, sel[2]), 0u) >> 4;
+        Hc[3] = __dp2a_lo(A[3], rs_prmt(wb0, wb1, sel[3]), 0u) >> 4;
         // rows come in ascending source order, so once sy == s the pair (s-1, s) is no longer needed
         const auto emit = [&](const unsigned (&H0)[4], const unsigned (&H1)[4]) {
             unsigned u[4];
