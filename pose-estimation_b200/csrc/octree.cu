@@ -195,15 +195,20 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
     if (!partial) {
         for (int c = tid; c < n_cand; c += OT_THREADS) { const int i = epre[c]; rank[i] = c; order[c] = i; }
     } else {
+        // rank = number of candidates that come first: larger node, or equal size and earlier in the list (the candidate
+        // list is in list order, so "earlier" is the smaller candidate index).  O(n_cand^2) broadcast reads: the sizes are
+        // staged densely in `flag` (free until step 5) so the inner loop is one independent shared-memory load per step.
+        for (int c = tid; c < n_cand; c += OT_THREADS) flag[c] = cur[epre[c]].cnt;
+        __syncthreads();
         for (int c = tid; c < n_cand; c += OT_THREADS) {
-            const int i = epre[c];
-            const unsigned ci = cur[i].cnt;
+            const unsigned ci = flag[c];
             unsigned r = 0;
-            for (int d = 0; d < n_cand; ++d) {
-                const int j = epre[d];
-                const unsigned cj = cur[j].cnt;
-                r += (cj > ci || (cj == ci && j < i)) ? 1u : 0u;
-            }
+            int d = 0;
+#pragma unroll 4
+            for (; d < c; ++d) r += flag[d] >= ci ? 1u : 0u;            // earlier in the list: ties count
+#pragma unroll 4
+            for (d = c + 1; d < n_cand; ++d) r += flag[d] > ci ? 1u : 0u;
+            const int i = epre[c];
             rank[i] = r;
             order[r] = i;
         }
