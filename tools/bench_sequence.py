@@ -28,8 +28,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--pairs", type=int, default=10000)
     ap.add_argument("--workload", default="euroc")
-    ap.add_argument("--batch", type=int, default=128)
-    ap.add_argument("--pool", type=int, default=128, help="distinct synthetic pairs (>= batch); frame i = pool[i % pool]")
+    ap.add_argument("--batch", type=int, default=512, help="pairs per C-ABI call (pipelined in 64-pair chunks inside the call)")
+    ap.add_argument("--pool", type=int, default=512, help="distinct synthetic pairs (>= batch); frame i = pool[i % pool]")
     ap.add_argument("--check", type=int, default=0, help="verify the first N frames against an unsharded run (rank 0)")
     args = ap.parse_args()
     import torch
