@@ -184,9 +184,11 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
 
 // =================================================================================================
 // tcgen05 matcher: the same contraction on the 5th-generation tensor cores.
-//   popcount(q xor t) = |q| + sum_k (2 q_k - 1)(-t_k)      (signed 8-bit operands: q' in {+1,-1}, t' in {0,-1}),
-// so the accumulator alone orders the candidates of a query row (|q| is added once at the end) and the epilogue is
-// a running min of (accumulator, column) keys.
+//   popcount(q xor t) = |q| + sum_k (2 q_k - 1)(-t_k)      (signed 8-bit operands: q' in {+1,-1}, t' in {0,-128}),
+// so the accumulator alone orders the candidates of a query row (|q| is added once at the end).  The train side carries
+// -128 instead of -1 and a ninth K slice holds (1, 0, ...) on the query side and (column, 0, ...) on the train side, so the
+// accumulator IS the key 128 * (distance - |q|) + column: the epilogue is a plain running min over TMEM values (BFMatcher's
+// strict '<' in ascending train order == lexicographic min), no per-column arithmetic.
 // One CTA = 128 query rows (TMEM lane = query row = thread).  Bits are expanded to bytes in registers (shift, PRMT
 // sign-replicate: 0x00 / 0xFF = 0 / -1 for the train side, one more LOP3 makes +-1 on the query side) and stored to shared memory in the canonical K-major no-swizzle UMMA layout:
 //   byte (row r, k) of a 128 x 256 operand tile at  (k / 16) * 2048 + r * 16 + k % 16
@@ -196,7 +198,8 @@ circular_kernel(const int* __restrict__ ti_l, const int* __restrict__ di_l, cons
 // the previous one overlap the tensor pipe.  k order inside a row is free (both operands use the same one):
 // byte 32 s + 4 j + i is bit 8 i + j of 32-bit word s.
 constexpr int TC_ROWS = 128;                       // M and N of one MMA
-constexpr int TC_TILE = TC_ROWS * 256;             // bytes of one expanded operand tile
+constexpr int TC_KS = 9;                           // K slices of 32 bytes: 8 of descriptor bits + 1 that carries the column index
+constexpr int TC_TILE = TC_ROWS * 32 * TC_KS;      // bytes of one expanded operand tile
 constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((TC_ROWS >> 3) << 17) | ((TC_ROWS >> 4) << 24);
 //                             D = s32     A = s8      B = s8       N >> 3                  M >> 4        (K-major A, B)
 
@@ -215,7 +218,7 @@ __device__ __forceinline__ unsigned tc_sign_bytes(unsigned x) {
 }
 
 // one descriptor row (8 words) -> 256 bytes of +-1 at row r of the tile at generic address `tile`
-// QUERY: bit 1 -> +1, bit 0 -> -1;  train: bit 1 -> -1, bit 0 -> 0.  Rows beyond the set are all-zero words.
+// QUERY: bit 1 -> +1, bit 0 -> -1;  train: bit 1 -> -128, bit 0 -> 0.  Rows beyond the set are all-zero words.
 // One thread expands HALF a row: words 4*half .. 4*half+3 of row r.
 template <bool QUERY>
 __device__ __forceinline__ void tc_expand_half(uint8_t* tile, int r, int half, const uint4& q) {
@@ -224,9 +227,10 @@ __device__ __forceinline__ void tc_expand_half(uint8_t* tile, int r, int half, c
     for (int s = 0; s < 4; ++s) {
         unsigned e[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {   // bit 8i + j -> msb of byte i -> 0x00 / 0xFF
-            const unsigned m = tc_sign_bytes(w[s] << (7 - j));
-            e[j] = QUERY ? (~m | 0x01010101u) : m;       // query: 0xFF -> 0x01, 0x00 -> 0xFF
+        for (int j = 0; j < 8; ++j) {   // bit 8i + j -> msb of byte i
+            const unsigned m = w[s] << (7 - j);
+            // query: msb replicated (0x00 / 0xFF), then 0xFF -> 0x01, 0x00 -> 0xFF (+1 / -1); train: the msb alone (0 / -128)
+            e[j] = QUERY ? (~tc_sign_bytes(m) | 0x01010101u) : (m & 0x80808080u);
         }
         uint8_t* dst = tile + (size_t)(2 * (4 * half + s)) * 2048 + r * 16;
         *reinterpret_cast<uint4*>(dst) = make_uint4(e[0], e[1], e[2], e[3]);
@@ -239,10 +243,10 @@ __device__ __forceinline__ void tc_mbar_wait(uint32_t mbar, uint32_t parity) {
                  "@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}" ::"r"(mbar), "r"(parity) : "memory");
 }
 
-// 8 MMAs (K = 256) of one 128 x 128 tile into TMEM columns [tmem_d, tmem_d + 128), then commit -> mbarrier
+// TC_KS MMAs (K = 288) of one 128 x 128 tile into TMEM columns [tmem_d, tmem_d + 128), then commit -> mbarrier
 __device__ __forceinline__ void tc_issue_tile(uint32_t tmem_d, uint32_t sa, uint32_t sb, uint32_t mbar) {
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
+    for (int s = 0; s < TC_KS; ++s) {
         const uint64_t da = tc_smem_desc(sa + s * 4096), db = tc_smem_desc(sb + s * 4096);
         const uint32_t acc = s > 0, zero = 0;
         asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -290,6 +294,13 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
         if (grp == 1) s_pop[r] = __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);
         else s_key[r] = __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);   // read back by the same thread below
     }
+    {   // ninth K slice (constant): query byte 0 = 1, train byte 0 = row (= accumulator column) of the tile, rest 0
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        const size_t o = (size_t)(16 + grp) * 2048 + r * 16;
+        *reinterpret_cast<uint4*>(sA + o) = grp ? z : make_uint4(1u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(sB + o) = grp ? z : make_uint4((unsigned)r, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(sB + TC_TILE + o) = grp ? z : make_uint4((unsigned)r, 0u, 0u, 0u);
+    }
     const uint4* tp = reinterpret_cast<const uint4*>(P.t);
     const int ntiles = (nt + TC_ROWS - 1) / TC_ROWS;
     // This thread's half row of the next two train tiles lives in registers (two sets, the loop below is unrolled by
@@ -310,7 +321,7 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
     if (tid == 0) tc_issue_tile(tmem, sa, sb, mb0);
     const int qpop_half = s_key[r];                              // (group 0: own value; group 1: unused)
 
-    // running min over (accumulator << 12 | column): strict-'<' ascending scan of BFMatcher == lexicographic min
+    // running min over 128 * accumulator + column: strict-'<' ascending scan of BFMatcher == lexicographic min
     int best_key = 0x7FFFFFFF, best_t0 = 0;
     // one tile step: cur = registers holding tile i+1's half row, nxt = registers to refill with tile i+2's
     const auto step = [&](int i, const uint4& cur, uint4& nxt) {
@@ -341,10 +352,9 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
                            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                          : "r"(taddr + cc * 32));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            // key = acc * 4096 + column-in-tile (acc in [-256, 256]); padded train rows (last tile) never win
-            int key[32];
-#pragma unroll
-            for (int k = 0; k < 32; ++k) key[k] = v[k] * 4096 + (col0 + k);
+            // v = 128 * acc + column-in-tile (acc in [-256, 256]) straight from the tensor core; padded train rows (last
+            // tile) never win
+            int (&key)[32] = v;
             if (nvalid < TC_ROWS) {
 #pragma unroll
                 for (int k = 0; k < 32; ++k)
@@ -355,7 +365,7 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
             for (int k = 1; k < 31; k += 2) cm = __vimin3_s32(cm, key[k], key[k + 1]);
             cm = min(cm, key[31]);
             // compare accumulators across chunks and tiles (a later one wins only with a strictly smaller distance)
-            if ((cm >> 12) < (best_key >> 12)) { best_key = cm; best_t0 = t0; }
+            if ((cm >> 7) < (best_key >> 7)) { best_key = cm; best_t0 = t0; }
         }
     };
     for (int i = 0; i < ntiles; i += 2) {
@@ -369,8 +379,8 @@ match_tc_kernel(const B2MatchProblem* __restrict__ probs) {
     if (grp == 0 && row < nq) {
         // merge with the other group's columns: smaller distance, then smaller train index
         const int ok = s_key[r], ot = s_t0[r];
-        const int da = best_key >> 12, db = ok >> 12;
-        const int ia = best_t0 + (best_key & 0xFFF), ib = ot + (ok & 0xFFF);
+        const int da = best_key >> 7, db = ok >> 7;
+        const int ia = best_t0 + (best_key & 127), ib = ot + (ok & 127);
         const bool other = db < da || (db == da && ib < ia);
         P.train_idx[row] = other ? ib : ia;
         P.dist[row] = (other ? db : da) + qpop_half + s_pop[r];
