@@ -323,6 +323,63 @@ __device__ void ot_round(bool partial, int N, const uint32_t* __restrict__ pts, 
     __syncthreads();
 }
 
+// A FULL expansion round on the count pyramid (every multi-point node splits, :594-672): the same new list as
+// ot_round<true>(false, ...), with ONE block scan instead of three.  Candidate r (in list order) contributes e_r non-empty
+// children, a surviving node contributes itself; both running sums travel in one word (children in the low half, survivors
+// in the high half), so a node knows its new position from its own prefix: children of candidate r at
+// t_children - (sum_{t<r} e_t + e_r) .. (pushed to the front, last child first), survivors behind all children in list order.
+__device__ void ot_round_full_pyr(B2Node* cur, B2Node* nxt, unsigned* flag, int node_cap, OtShared& sh, const unsigned* pyr,
+                                  int n_ini, int D) {
+    const int tid = threadIdx.x;
+    const int lsz = sh.lsz;
+    if (tid == 0) sh.n_multi = 0;
+    for (int i = tid; i < lsz; i += OT_THREADS) {
+        const B2Node nd = cur[i];
+        unsigned v = 1u << 16;
+        if (nd.cnt > 1) {
+            if ((int)node_depth(nd) >= D) sh.too_deep = 1;   // its children are below the pyramid
+            else {
+                const unsigned* c = pyr + pyr_off(n_ini, (int)node_depth(nd) + 1) + (node_path(nd) << 2);
+                v = (c[0] != 0) + (c[1] != 0) + (c[2] != 0) + (c[3] != 0);
+            }
+        }
+        flag[i] = v;
+    }
+    __syncthreads();
+    if (sh.too_deep) return;
+    const unsigned total = block_scan_excl(flag, lsz, sh);
+    const int t_children = (int)(total & 0xFFFFu), n_keep = (int)(total >> 16);
+    const int new_lsz = t_children + n_keep;
+    if (new_lsz > node_cap) {           // cannot happen (see b2orb_capi.cu sizing); never corrupt memory
+        if (tid == 0) sh.lsz = -1;
+        __syncthreads();
+        return;
+    }
+    int multi = 0;
+    for (int i = tid; i < lsz; i += OT_THREADS) {
+        const B2Node nd = cur[i];
+        const unsigned pre = flag[i];
+        if (nd.cnt > 1) {
+            const unsigned* c = pyr + pyr_off(n_ini, (int)node_depth(nd) + 1) + (node_path(nd) << 2);
+            const unsigned cs[4] = {c[0], c[1], c[2], c[3]};
+            const int e_r = (cs[0] != 0) + (cs[1] != 0) + (cs[2] != 0) + (cs[3] != 0);
+            int pos = t_children - ((int)(pre & 0xFFFFu) + e_r);
+#pragma unroll
+            for (int q = 3; q >= 0; --q)
+                if (cs[q]) {
+                    nxt[pos++] = child_rect(nd, q, cs[q]);
+                    multi += cs[q] > 1;
+                }
+        } else {
+            nxt[t_children + (int)(pre >> 16)] = nd;
+        }
+    }
+    if (multi) atomicAdd(&sh.n_multi, multi);
+    __syncthreads();
+    if (tid == 0) sh.lsz = new_lsz;
+    __syncthreads();
+}
+
 // The main loop of DistributeOctTree (:592-739) on whichever source of child counts; leaves the final list in `cur`
 // (returned through the reference) and its size in sh.lsz (-1 = workspace guard tripped).  With PYR it may stop early
 // with sh.too_deep set.
@@ -340,7 +397,8 @@ __device__ void ot_main_loop(int N, const uint32_t* pts, unsigned short* pnode, 
     while (!finish) {
         int prev = sh.lsz;
         OT_RMARK();
-        ot_round<PYR>(false, N, pts, pnode, M, cur, nxt, cc, ccn, cpos, newpos, rank, order, epre, flag, Q, sh, pyr, n_ini, D);
+        if (PYR && Q <= 16000) ot_round_full_pyr(cur, nxt, flag, Q, sh, pyr, n_ini, D);   // (both packed sums stay below 2^16)
+        else ot_round<PYR>(false, N, pts, pnode, M, cur, nxt, cc, ccn, cpos, newpos, rank, order, epre, flag, Q, sh, pyr, n_ini, D);
         if (PYR && sh.too_deep) return;
         { B2Node* t = cur; cur = nxt; nxt = t; unsigned* u = cc; cc = ccn; ccn = u; }
         int lsz = sh.lsz;
