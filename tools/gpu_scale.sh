@@ -20,8 +20,8 @@ run 8 --e2e-out kept
 run 4 --e2e-out kept
 run 2 --e2e-out kept
 run 8 --e2e-out full
-run 8 --e2e-out kept --e2e-threads 1
-run 8 --e2e-out kept --e2e-threads 2
+[ "${PROBE:-0}" = 1 ] && run 8 --e2e-out kept --e2e-threads 1
+[ "${PROBE:-0}" = 1 ] && run 8 --e2e-out kept --e2e-threads 2
 python - <<PY
 import json
 for l in open('gpurun_out/${TAG}_scale.jsonl'):
